@@ -1,0 +1,302 @@
+"""autograd.Functions over the C ABI (include/b2c.h).
+
+Mirrors the torch functional API the reference calls (SURVEY.md §8(b) Face 1):
+``F.conv3d`` / ``F.conv_transpose3d`` (stylegan.py:168-170), and the fused
+BatchNorm3d / LayerNorm / activation epilogues of dcgan.py:45-70,158-182,
+utils.py:47-132, FID_ResNet.py:65-102.
+
+Tensors cross this layer as logical NCDHW of any stride; internally everything
+is dense NDHWC (torch ``channels_last_3d``), bf16 under autocast / bf16 inputs
+and fp32 otherwise.  Every FLOP runs in libb2c.so; there is no torch/cuDNN
+compute fallback.
+"""
+import ctypes as C
+
+import torch
+from torch.autograd import Function
+
+from . import _lib
+from ._lib import (ACT_IDS, ACT_NONE, ALGO_AUTO, BF16, F32, PASS_DGRAD,
+                   PASS_FWD, PASS_WGRAD, ConvDesc, Fusion, check)
+
+_force_algo = [ALGO_AUTO]     # tests / profiling: force DIRECT or TC
+
+
+def set_algo(algo):
+    _force_algo[0] = int(algo)
+
+
+# ----------------------------------------------------------------- helpers
+def _dt(dtype):
+    if dtype == torch.bfloat16:
+        return BF16
+    if dtype == torch.float32:
+        return F32
+    raise TypeError("b200conv3d supports bf16 and fp32 compute, got %s" % dtype)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream(t):
+    if _lib.is_host():
+        return None
+    return C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _check_device(t):
+    host = _lib.is_host()
+    if host and t.is_cuda:
+        raise RuntimeError("b200conv3d is bound to the host oracle; got a CUDA tensor")
+    if not host and not t.is_cuda:
+        raise RuntimeError(
+            "b200conv3d ops run only on CUDA (sm_100a) tensors; got a %s tensor — "
+            "there is no CPU fallback" % t.device)
+
+
+class _dev:
+    """Make the tensor's device current while launching (DataParallel threads)."""
+
+    def __init__(self, t):
+        self.g = None if _lib.is_host() else torch.cuda.device(t.device)
+
+    def __enter__(self):
+        if self.g is not None:
+            self.g.__enter__()
+
+    def __exit__(self, *a):
+        if self.g is not None:
+            self.g.__exit__(*a)
+
+
+def compute_dtype(x):
+    """bf16 under any autocast (the reference asks for fp16 autocast,
+    trainer.py:213; the B200 path computes in bf16 — BASELINE config 2) or for
+    bf16 inputs; fp32 otherwise."""
+    kind = "cpu" if _lib.is_host() else "cuda"
+    if torch.is_autocast_enabled(kind):
+        return torch.bfloat16
+    if x.dtype in (torch.bfloat16, torch.float16):
+        return torch.bfloat16
+    return torch.float32
+
+
+def _ws(nbytes, like):
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=like.device)
+
+
+def cast(x, dtype):
+    """Dense elementwise dtype conversion through b2c_cast."""
+    if x.dtype == dtype:
+        return x
+    if x.dtype not in (torch.bfloat16, torch.float32):
+        x = x.float()                      # fp16/fp64 plumbing only
+    assert x.is_contiguous()
+    out = torch.empty_like(x, dtype=dtype)
+    with _dev(x):
+        check(_lib.lib().b2c_cast(_ptr(x), _ptr(out), x.numel(), _dt(x.dtype), _dt(dtype),
+                                  _stream(x)), "cast")
+    return out
+
+
+def to_ndhwc(x, dtype):
+    """logical [N,C,D,H,W] (any stride/dtype) -> dense [N,D,H,W,C] of `dtype`."""
+    _check_device(x)
+    if x.dim() != 5:
+        raise ValueError("expected a 5-D NCDHW tensor, got shape %s" % (tuple(x.shape),))
+    p = x.permute(0, 2, 3, 4, 1)
+    if p.is_contiguous():
+        return p if x.dtype == dtype else cast(p, dtype)
+    if x.dtype not in (torch.bfloat16, torch.float32):
+        x = x.float()
+    xs = x if x.is_contiguous() else x.contiguous()
+    n, c, d, h, w = xs.shape
+    out = torch.empty((n, d, h, w, c), dtype=dtype, device=x.device)
+    with _dev(x):
+        check(_lib.lib().b2c_transpose(_ptr(xs), _ptr(out), n, c, d * h * w, _dt(xs.dtype),
+                                       _dt(dtype), _stream(x)), "transpose")
+    return out
+
+
+def from_ndhwc(buf):
+    """dense [N,D,H,W,C] -> logical NCDHW view (channels_last_3d strides)."""
+    return buf.permute(0, 4, 1, 2, 3)
+
+
+def _triple(v):
+    if isinstance(v, (list, tuple)):
+        if len(v) == 1:
+            return (int(v[0]),) * 3
+        if len(v) != 3:
+            raise ValueError("expected an int or 3 ints, got %r" % (v,))
+        return tuple(int(i) for i in v)
+    return (int(v),) * 3
+
+
+class Geom:
+    """Static geometry of one conv / conv-transpose call."""
+    __slots__ = ("transposed", "k", "stride", "pad", "dil", "out_pad")
+
+    def __init__(self, transposed, k, stride, pad, dil, out_pad=(0, 0, 0)):
+        self.transposed, self.k = bool(transposed), tuple(k)
+        self.stride, self.pad, self.dil = _triple(stride), _triple(pad), _triple(dil)
+        self.out_pad = _triple(out_pad)
+
+    def out_spatial(self, sp):
+        o = []
+        for i in range(3):
+            if not self.transposed:
+                v = (sp[i] + 2 * self.pad[i] - self.dil[i] * (self.k[i] - 1) - 1) // self.stride[i] + 1
+            else:
+                v = ((sp[i] - 1) * self.stride[i] - 2 * self.pad[i]
+                     + self.dil[i] * (self.k[i] - 1) + self.out_pad[i] + 1)
+            if v <= 0:
+                raise RuntimeError("conv3d: computed output size %d is too small" % v)
+            o.append(v)
+        return o
+
+
+def _desc(g, xshape, cout, dtype, algo):
+    """xshape = (N, D, H, W, Cin) of the NDHWC forward input."""
+    d = ConvDesc()
+    n, dd, hh, ww, cin = xshape
+    od, oh, ow = g.out_spatial((dd, hh, ww))
+    d.x.n, d.x.c, d.x.d, d.x.h, d.x.w = n, cin, dd, hh, ww
+    d.y.n, d.y.c, d.y.d, d.y.h, d.y.w = n, cout, od, oh, ow
+    for i in range(3):
+        d.k[i], d.stride[i], d.pad[i], d.dil[i] = g.k[i], g.stride[i], g.pad[i], g.dil[i]
+    d.transposed, d.io_dtype, d.algo = int(g.transposed), _dt(dtype), int(algo)
+    return d
+
+
+def _packed_filter(w, desc, pas, dtype):
+    """bf16/fp32 streaming copy of a torch-layout filter, cached on the tensor
+    object and invalidated by its version counter (optimizer steps bump it;
+    spectral-norm weights are fresh tensors every forward, utils.py:13)."""
+    key = (pas, dtype, w.data_ptr(), w._version, desc.transposed)
+    cache = getattr(w, "_b2c_pack", None)
+    if cache is not None and cache[0] == key[2:4] and (pas, dtype) in cache[1]:
+        return cache[1][(pas, dtype)]
+    wf = w.detach()
+    if wf.dtype != torch.float32:
+        wf = wf.float()
+    if not wf.is_contiguous():
+        wf = wf.contiguous()
+    L = _lib.lib()
+    nbytes = L.b2c_filter_packed_bytes(C.byref(desc), pas)
+    out = torch.empty(nbytes // (2 if dtype == torch.bfloat16 else 4), dtype=dtype, device=w.device)
+    with _dev(w):
+        check(L.b2c_filter_pack(C.byref(desc), pas, _ptr(wf), _ptr(out), _stream(w)), "filter_pack")
+    try:
+        if cache is None or cache[0] != key[2:4]:
+            cache = (key[2:4], {})
+            w._b2c_pack = cache
+        cache[1][(pas, dtype)] = out
+    except AttributeError:
+        pass
+    return out
+
+
+# ------------------------------------------------------------------- conv
+class _ConvFn(Function):
+    """conv3d / conv_transpose3d with fused bias + activation.
+
+    forward : b2c_conv3d_fwd ; backward: b2c_conv3d_dgrad / b2c_conv3d_wgrad,
+    each only when the corresponding input requires grad — the freeze pattern
+    of trainer.py:209-210,249-250,255-256 decides which passes run."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, g, act, slope):
+        _check_device(x)
+        cd = compute_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        cout = w.shape[1] if g.transposed else w.shape[0]
+        cin_w = w.shape[0] if g.transposed else w.shape[1]
+        if cin_w != xb.shape[4]:
+            raise RuntimeError("conv3d: expected input with %d channels, got %d (groups != 1 "
+                               "is not supported on this path)" % (cin_w, xb.shape[4]))
+        desc = _desc(g, tuple(xb.shape), cout, cd, _force_algo[0])
+        L = _lib.lib()
+        wp = _packed_filter(w, desc, PASS_FWD, cd)
+        y = torch.empty((desc.y.n, desc.y.d, desc.y.h, desc.y.w, desc.y.c), dtype=cd, device=x.device)
+        bf = None
+        if bias is not None:
+            bf = bias.detach()
+            bf = bf if bf.dtype == torch.float32 else bf.float()
+        fu = Fusion(_ptr(bf), int(act), float(slope))
+        ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_FWD), x)
+        with _dev(x):
+            check(L.b2c_conv3d_fwd(C.byref(desc), _ptr(xb), _ptr(wp), _ptr(y), C.byref(fu),
+                                   _ptr(ws), ws.numel(), _stream(x)), "conv3d_fwd")
+        ctx.g, ctx.act, ctx.slope, ctx.cd = g, int(act), float(slope), cd
+        ctx.x_dtype, ctx.has_bias = x.dtype, bias is not None
+        ctx.save_for_backward(xb, w, y if act != ACT_NONE else None)
+        return from_ndhwc(y)
+
+    @staticmethod
+    def backward(ctx, gy):
+        xb, w, y = ctx.saved_tensors
+        g, cd = ctx.g, ctx.cd
+        L = _lib.lib()
+        cout = w.shape[1] if g.transposed else w.shape[0]
+        desc = _desc(g, tuple(xb.shape), cout, cd, _force_algo[0])
+        gyb = to_ndhwc(gy, cd)
+        if ctx.act != ACT_NONE:
+            gz = torch.empty_like(gyb)
+            with _dev(gyb):
+                check(L.b2c_act_bwd(_ptr(y), _ptr(gyb), _ptr(gz), gyb.numel(), _dt(cd), ctx.act,
+                                    ctx.slope, _stream(gyb)), "act_bwd")
+            gyb = gz
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            wp = _packed_filter(w, desc, PASS_DGRAD, cd)
+            dxb = torch.empty_like(xb)
+            ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_DGRAD), xb)
+            with _dev(xb):
+                check(L.b2c_conv3d_dgrad(C.byref(desc), _ptr(gyb), _ptr(wp), _ptr(dxb), _ptr(ws),
+                                         ws.numel(), _stream(xb)), "conv3d_dgrad")
+            dx = from_ndhwc(dxb)
+            if ctx.x_dtype == torch.float32 and cd != torch.float32:
+                dx = from_ndhwc(cast(dxb, torch.float32))
+        need_w = ctx.needs_input_grad[1]
+        need_b = ctx.has_bias and ctx.needs_input_grad[2]
+        if need_w or need_b:
+            dw = torch.empty(w.shape, dtype=torch.float32, device=w.device) if need_w else None
+            db = torch.empty(cout, dtype=torch.float32, device=w.device) if need_b else None
+            ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_WGRAD), xb)
+            with _dev(xb):
+                check(L.b2c_conv3d_wgrad(C.byref(desc), _ptr(xb), _ptr(gyb), _ptr(dw), _ptr(db),
+                                         _ptr(ws), ws.numel(), _stream(xb)), "conv3d_wgrad")
+            if dw is not None and w.dtype != torch.float32:
+                dw = dw.to(w.dtype)
+        return dx, dw, db, None, None, None
+
+
+def _act_id(act):
+    if isinstance(act, int):
+        return act
+    return ACT_IDS[act]
+
+
+def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=None, slope=0.0):
+    """Drop-in for ``torch.nn.functional.conv3d`` (stylegan.py:168, nn.Conv3d.forward)
+    with an optional fused activation epilogue."""
+    if groups != 1:
+        raise NotImplementedError("b200conv3d.conv3d: groups=%d is not supported (only the dense "
+                                  "path is built; no cuDNN fallback)" % groups)
+    if isinstance(padding, str):
+        raise NotImplementedError("b200conv3d.conv3d: string padding %r is not supported" % padding)
+    g = Geom(False, tuple(weight.shape[2:]), stride, padding, dilation)
+    return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+
+
+def conv_transpose3d(x, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1,
+                     dilation=1, act=None, slope=0.0):
+    """Drop-in for ``torch.nn.functional.conv_transpose3d`` (stylegan.py:170,
+    nn.ConvTranspose3d.forward).  Computed as a stride-decomposed sub-pixel
+    convolution inside the library, never by zero insertion."""
+    if groups != 1:
+        raise NotImplementedError("b200conv3d.conv_transpose3d: groups=%d is not supported" % groups)
+    g = Geom(True, tuple(weight.shape[2:]), stride, padding, dilation, output_padding)
+    return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)

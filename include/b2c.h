@@ -1,0 +1,204 @@
+/*
+ * b2c.h — C ABI of the B200-native conv3d hot path (libb2c.so).
+ *
+ * This is the drop-in boundary ("Face 2" of SURVEY.md §8(b)).  The reference
+ * (julschoen/3D-GAN) has no FFI of its own: every op on its hot path is a
+ * PyTorch layer call.  Each entry point below therefore cites the reference
+ * call site whose PyTorch op it replaces.  The Python host side
+ * (3d-gan_b200/b200conv3d) binds these with ctypes and mirrors the torch
+ * nn.Module / functional API ("Face 1").
+ *
+ * Rules of the ABI
+ *   - extern "C", plain pointers and sizes, no torch types.
+ *   - All activation tensors are physically NDHWC (torch channels_last_3d),
+ *     dense.  Filters arrive in torch layout (fp32) and are re-packed by
+ *     b2c_filter_pack into the layout the kernels stream.
+ *   - The caller owns every buffer (device memory); the library allocates no
+ *     device memory, launches on the given stream and never synchronises.
+ *   - Return value: 0 = OK, negative = B2C_ERR_*.  b2c_strerror() maps a code
+ *     to a static string.  No C++ exception crosses the ABI.
+ *   - Re-entrant: the only global state is a mutex-guarded cache of TMA
+ *     descriptors encoder entry point and device attributes.
+ */
+#ifndef B2C_H_
+#define B2C_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* cudaStream_t without pulling in cuda_runtime.h for C callers. */
+typedef void* b2c_stream;
+
+/* ---- error codes ---------------------------------------------------- */
+#define B2C_OK                 0
+#define B2C_ERR_INVALID       -1   /* bad argument / inconsistent shapes     */
+#define B2C_ERR_UNSUPPORTED   -2   /* legal torch config we do not implement */
+#define B2C_ERR_WORKSPACE     -3   /* workspace too small                    */
+#define B2C_ERR_CUDA          -4   /* a CUDA runtime / driver call failed    */
+#define B2C_ERR_NO_DEVICE     -5   /* no sm_100 device / driver available    */
+
+/* ---- dtypes --------------------------------------------------------- */
+#define B2C_BF16 0
+#define B2C_F32  2
+
+/* ---- activations (epilogues the reference models use) ---------------
+ * dcgan.py:49-68 ReLU/Tanh, dcgan.py:163 LeakyReLU(0.2), dcgan.py:121
+ * LeakyReLU(0.1), utils.py:68 ReLU, stylegan.py:103-113 lrelu.           */
+#define B2C_ACT_NONE  0
+#define B2C_ACT_RELU  1
+#define B2C_ACT_LRELU 2
+#define B2C_ACT_TANH  3
+
+/* ---- passes --------------------------------------------------------- */
+#define B2C_PASS_FWD   0
+#define B2C_PASS_DGRAD 1
+#define B2C_PASS_WGRAD 2
+
+/* ---- kernel selection (for tests / profiling; AUTO in production) --- */
+#define B2C_ALGO_AUTO   0
+#define B2C_ALGO_DIRECT 1   /* CUDA-core direct conv, fp32 accumulate        */
+#define B2C_ALGO_TC     2   /* tcgen05 implicit GEMM (bf16 only)             */
+
+typedef struct { int32_t n, c, d, h, w; } b2c_shape;   /* logical NCDHW extents */
+
+/* Describes one nn.Conv3d (transposed=0) or nn.ConvTranspose3d
+ * (transposed=1) layer call.  x is the layer's forward input, y its forward
+ * output, whichever pass is being computed.
+ *   conv : y.d = (x.d + 2*pad - dil*(k-1) - 1)/stride + 1
+ *   convT: y.d = (x.d-1)*stride - 2*pad + dil*(k-1) + output_padding + 1
+ * Filter (torch layout, fp32): conv [y.c, x.c, kD,kH,kW];
+ *                              convT [x.c, y.c, kD,kH,kW].   groups must be 1
+ * (depthwise FIR of stylegan.py:197 has its own entry point).              */
+typedef struct {
+  b2c_shape x, y;
+  int32_t   k[3], stride[3], pad[3], dil[3];
+  int32_t   transposed;
+  int32_t   io_dtype;      /* B2C_BF16 or B2C_F32; accumulation is fp32     */
+  int32_t   algo;          /* B2C_ALGO_*                                    */
+} b2c_conv_desc;
+
+/* Epilogue fused into the forward kernels. */
+typedef struct {
+  const float* bias;       /* [y.c] fp32 or NULL                            */
+  int32_t      act;        /* B2C_ACT_*                                     */
+  float        slope;      /* LeakyReLU negative slope                      */
+} b2c_fusion;
+
+/* ---- library ------------------------------------------------------- */
+int         b2c_version(void);
+const char* b2c_strerror(int code);
+/* Last kernel family chosen by b2c_conv3d_* on this thread (B2C_ALGO_*). */
+int         b2c_last_algo(void);
+/* Number of kernel launches issued by this library since process start.  */
+uint64_t    b2c_launch_count(void);
+
+/* ---- filters ------------------------------------------------------- *
+ * Re-pack a torch-layout fp32 filter into the streaming layout of `pass`:
+ *   [tap][n_out][k_in] with k_in contiguous, dtype = desc->io_dtype, where
+ *   (n_out,k_in) = (y.c,x.c) for the pass that produces y and (x.c,y.c) for
+ *   the pass that produces dx.  Replaces the implicit weight handling of
+ *   nn.Conv3d / nn.ConvTranspose3d (dcgan.py:47-67,161-181, utils.py:8-14,
+ *   FID_ResNet.py:9-16,70-75,119-125, stylegan.py:164-170).               */
+size_t b2c_filter_packed_bytes(const b2c_conv_desc*, int pass);
+int    b2c_filter_pack(const b2c_conv_desc*, int pass, const float* w_torch,
+                       void* w_packed, b2c_stream);
+
+/* ---- convolution --------------------------------------------------- *
+ * fwd  : y  = act(conv(x, w) + bias)     F.conv3d / F.conv_transpose3d
+ * dgrad: dx = conv_backward_input(dy, w)  (autograd of the same calls)
+ * wgrad: dw (torch layout, fp32, overwritten) and optional dbias [y.c].
+ * Workspace: b2c_conv3d_workspace(desc, pass) bytes (may be 0).
+ * Call sites replaced: dcgan.py:45-70,158-182; utils.py:8-14,47-132;
+ * biggan.py:42,78; FID_ResNet.py:65-102,119-125; stylegan.py:164-170.     */
+size_t b2c_conv3d_workspace(const b2c_conv_desc*, int pass);
+int b2c_conv3d_fwd  (const b2c_conv_desc*, const void* x, const void* w_packed,
+                     void* y, const b2c_fusion*, void* ws, size_t ws_bytes,
+                     b2c_stream);
+int b2c_conv3d_dgrad(const b2c_conv_desc*, const void* dy, const void* w_packed,
+                     void* dx, void* ws, size_t ws_bytes, b2c_stream);
+int b2c_conv3d_wgrad(const b2c_conv_desc*, const void* x, const void* dy,
+                     float* dw_torch, float* dbias, void* ws, size_t ws_bytes,
+                     b2c_stream);
+
+/* ---- layout -------------------------------------------------------- *
+ * dst[b][j][i] = (dst_dtype) src[b][i][j]   (src is [batch][rows][cols]).
+ * NCDHW -> NDHWC is rows=C, cols=D*H*W; the inverse swaps them.  Also used
+ * to permute LayerNorm's [C,D,H,W] affine (dcgan.py:162-178).             */
+int b2c_transpose(const void* src, void* dst, int64_t batch, int64_t rows,
+                  int64_t cols, int src_dtype, int dst_dtype, b2c_stream);
+/* dst[i] = (dst_dtype) src[i] */
+int b2c_cast(const void* src, void* dst, int64_t n, int src_dtype,
+             int dst_dtype, b2c_stream);
+
+/* ---- statistics ---------------------------------------------------- *
+ * x is [rows][C] (NDHWC flattened).  per-channel: sum[c], sqsum[c] over
+ * rows (BatchNorm3d, dcgan.py:48-64, utils.py:62-65, FID_ResNet.py:71-76).
+ * Deterministic two-stage reduction; ws from b2c_stats_workspace.         */
+size_t b2c_stats_workspace(int64_t rows, int64_t C);
+int b2c_channel_stats(const void* x, int64_t rows, int64_t C, int dtype,
+                      float* sum, float* sqsum, void* ws, size_t ws_bytes,
+                      b2c_stream);
+/* BatchNorm3d training-mode finalize (momentum update exactly like torch:
+ * running = (1-m)*running + m*batch, unbiased var for running, biased for
+ * normalisation).  Writes mean[C], invstd[C], scale[C]=gamma*invstd,
+ * shift[C]=beta-mean*scale.  running_* may be NULL.                        */
+int b2c_bn_finalize(const float* sum, const float* sqsum, int64_t count,
+                    int64_t C, float eps, float momentum, const float* gamma,
+                    const float* beta, float* mean, float* invstd,
+                    float* scale, float* shift, float* running_mean,
+                    float* running_var, b2c_stream);
+/* y = act(x*scale[c] + shift[c] (+ residual))  — BN apply + ReLU (+ the
+ * Bottleneck residual add, FID_ResNet.py:97-100) in one HBM pass.          */
+int b2c_bn_act_fwd(const void* x, void* y, const void* residual, int64_t rows,
+                   int64_t C, int dtype, const float* scale,
+                   const float* shift, int act, float slope, b2c_stream);
+/* Backward of the above. Step 1 reduces per channel
+ *   s1[c] = sum g, s2[c] = sum g*xhat   with g = dy*act'(z), z the
+ *   pre-activation recomputed from x (and residual), xhat=(x-mean)*invstd.
+ * Step 2 writes dx = scale*(g - s1/M - xhat*s2/M) and, when dres != NULL,
+ * dres = g (gradient of the residual branch).  dgamma = s2, dbeta = s1.     */
+int b2c_bn_act_bwd_reduce(const void* x, const void* dy, const void* residual,
+                          int64_t rows, int64_t C, int dtype,
+                          const float* mean, const float* invstd,
+                          const float* scale, const float* shift, int act,
+                          float slope, float* s1, float* s2, void* ws,
+                          size_t ws_bytes, b2c_stream);
+int b2c_bn_act_bwd_apply(const void* x, const void* dy, const void* residual,
+                         void* dx, void* dres, int64_t rows, int64_t C,
+                         int dtype, const float* mean, const float* invstd,
+                         const float* scale, const float* shift,
+                         const float* s1, const float* s2, int act,
+                         float slope, b2c_stream);
+
+/* ---- LayerNorm([C,D,H,W]) + LeakyReLU  (dcgan.py:162-179) ---------- *
+ * x is [N][L] with L = D*H*W*C (NDHWC); gamma/beta are [L] fp32 already
+ * permuted to NDHWC order (b2c_transpose).  Per-sample mean/rstd [N].      */
+size_t b2c_ln_workspace(int64_t N, int64_t L);
+int b2c_ln_act_fwd(const void* x, void* y, int64_t N, int64_t L, int dtype,
+                   const float* gamma, const float* beta, float eps, int act,
+                   float slope, float* mean, float* rstd, void* ws,
+                   size_t ws_bytes, b2c_stream);
+/* dgamma/dbeta [L] fp32 in NDHWC order (may be NULL when the affine is
+ * frozen, trainer.py:278-279); dx may be NULL when x needs no grad.         */
+int b2c_ln_act_bwd(const void* x, const void* dy, void* dx, int64_t N,
+                   int64_t L, int dtype, const float* gamma, const float* beta,
+                   const float* mean, const float* rstd, int act, float slope,
+                   float* dgamma, float* dbeta, void* ws, size_t ws_bytes,
+                   b2c_stream);
+
+/* ---- pointwise ------------------------------------------------------ *
+ * y = act(x); dx = dy * act'(.) evaluated from the OUTPUT y (valid for
+ * relu/lrelu with slope>0/tanh — all in-place-safe, dcgan.py:49,163,68).   */
+int b2c_act_fwd(const void* x, void* y, int64_t n, int dtype, int act,
+                float slope, b2c_stream);
+int b2c_act_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype,
+                int act, float slope, b2c_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2C_H_ */

@@ -1,0 +1,479 @@
+/*
+ * b2c_oracle.c — TEST INFRASTRUCTURE ONLY.  CPU restatement (plain C) of the
+ * arithmetic on the reference's conv3d hot path, exported under the SAME C ABI
+ * as the product library (include/b2c.h) but operating on HOST pointers.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load this library; the product package
+ * (3d-gan_b200/b200conv3d) never does.
+ *
+ * Where the algorithm lives: the reference (julschoen/3D-GAN) has no arithmetic
+ * of its own on this path; every FLOP is a PyTorch layer call:
+ *   nn.Conv3d / F.conv3d              dcgan.py:161-181, utils.py:8-14,
+ *                                     FID_ResNet.py:9-16,70-75,119-125,
+ *                                     stylegan.py:168-170
+ *   nn.ConvTranspose3d                dcgan.py:47-67, stylegan.py:170
+ *   nn.BatchNorm3d (training mode)    dcgan.py:48-64, utils.py:62-65,
+ *                                     FID_ResNet.py:71-76,127
+ *   nn.LayerNorm([C,D,H,W])           dcgan.py:162-178
+ *   ReLU / LeakyReLU / Tanh           dcgan.py:49,68,163, utils.py:68
+ * The dependency is torch (unpinned by the reference; torch 2.11.0+cu128 in
+ * this image).  This file restates torch's documented definitions of those
+ * ops.  Parity pinning: the reference ships NO tests or golden vectors
+ * (SURVEY.md §4), so this oracle is pinned against outputs of the reference's
+ * own modules imported in the build container (tests/golden/*.npz, generated
+ * by oracle/make_golden.py) and against torch CPU fp32 ops
+ * (tests/test_oracle.py).
+ *
+ * Accumulation is in double so the oracle is order-independent.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include "../include/b2c.h"
+
+typedef uint16_t bf16_t;
+
+static inline float bf16_to_f(bf16_t v) {
+  uint32_t u = ((uint32_t)v) << 16; float f; memcpy(&f, &u, 4); return f;
+}
+static inline bf16_t f_to_bf16(float f) {          /* round-to-nearest-even */
+  uint32_t u; memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (bf16_t)((u >> 16) | 0x40);
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (bf16_t)(u >> 16);
+}
+static inline double ld(const void* p, int64_t i, int dt) {
+  return dt == B2C_BF16 ? (double)bf16_to_f(((const bf16_t*)p)[i])
+                        : (double)((const float*)p)[i];
+}
+static inline void st(void* p, int64_t i, int dt, double v) {
+  if (dt == B2C_BF16) ((bf16_t*)p)[i] = f_to_bf16((float)v);
+  else ((float*)p)[i] = (float)v;
+}
+static inline int esize(int dt) { return dt == B2C_BF16 ? 2 : 4; }
+static inline int dt_ok(int dt) { return dt == B2C_BF16 || dt == B2C_F32; }
+
+static inline double act_f(double z, int act, double slope) {
+  switch (act) {
+    case B2C_ACT_RELU:  return z > 0 ? z : 0.0;
+    case B2C_ACT_LRELU: return z > 0 ? z : slope * z;
+    case B2C_ACT_TANH:  return tanh(z);
+    default:            return z;
+  }
+}
+/* derivative w.r.t. the pre-activation z */
+static inline double act_dz(double z, int act, double slope) {
+  switch (act) {
+    case B2C_ACT_RELU:  return z > 0 ? 1.0 : 0.0;
+    case B2C_ACT_LRELU: return z > 0 ? 1.0 : slope;
+    case B2C_ACT_TANH:  { double t = tanh(z); return 1.0 - t * t; }
+    default:            return 1.0;
+  }
+}
+/* derivative expressed from the output y = act(z) */
+static inline double act_dy(double y, int act, double slope) {
+  switch (act) {
+    case B2C_ACT_RELU:  return y > 0 ? 1.0 : 0.0;
+    case B2C_ACT_LRELU: return y > 0 ? 1.0 : slope;
+    case B2C_ACT_TANH:  return 1.0 - y * y;
+    default:            return 1.0;
+  }
+}
+
+int b2c_version(void) { return 100; }
+int b2c_last_algo(void) { return B2C_ALGO_DIRECT; }
+uint64_t b2c_launch_count(void) { return 0; }
+const char* b2c_strerror(int c) {
+  switch (c) {
+    case B2C_OK: return "ok";
+    case B2C_ERR_INVALID: return "invalid argument";
+    case B2C_ERR_UNSUPPORTED: return "unsupported configuration";
+    case B2C_ERR_WORKSPACE: return "workspace too small";
+    case B2C_ERR_CUDA: return "CUDA error";
+    case B2C_ERR_NO_DEVICE: return "no sm_100 device";
+    default: return "unknown error";
+  }
+}
+
+/* ---- descriptor validation (same rules as the product library) ------- */
+static int out_extent(int in, int k, int s, int p, int d) {
+  return (in + 2 * p - d * (k - 1) - 1) / s + 1;
+}
+static int check_desc(const b2c_conv_desc* c) {
+  if (!c || !dt_ok(c->io_dtype)) return B2C_ERR_INVALID;
+  const int xs[3] = {c->x.d, c->x.h, c->x.w}, ys[3] = {c->y.d, c->y.h, c->y.w};
+  if (c->x.n != c->y.n || c->x.n <= 0 || c->x.c <= 0 || c->y.c <= 0) return B2C_ERR_INVALID;
+  for (int i = 0; i < 3; i++) {
+    if (c->k[i] <= 0 || c->stride[i] <= 0 || c->dil[i] <= 0 || c->pad[i] < 0) return B2C_ERR_INVALID;
+    if (xs[i] <= 0 || ys[i] <= 0) return B2C_ERR_INVALID;
+    if (!c->transposed) {
+      if (out_extent(xs[i], c->k[i], c->stride[i], c->pad[i], c->dil[i]) != ys[i]) return B2C_ERR_INVALID;
+    } else {
+      int base = (xs[i] - 1) * c->stride[i] - 2 * c->pad[i] + c->dil[i] * (c->k[i] - 1) + 1;
+      int op = ys[i] - base;                 /* output_padding */
+      if (op < 0 || (op >= c->stride[i] && op >= c->dil[i])) return B2C_ERR_INVALID;
+    }
+  }
+  return B2C_OK;
+}
+static inline int ntaps(const b2c_conv_desc* c) { return c->k[0] * c->k[1] * c->k[2]; }
+
+/* ---- filter packing -------------------------------------------------- */
+size_t b2c_filter_packed_bytes(const b2c_conv_desc* c, int pass) {
+  (void)pass;
+  if (check_desc(c)) return 0;
+  return (size_t)ntaps(c) * c->x.c * c->y.c * esize(c->io_dtype);
+}
+/* torch filter is [A][B][taps]; packed is [tap][n_out][k_in].
+ * n_out is the channel count of the tensor the pass produces.            */
+int b2c_filter_pack(const b2c_conv_desc* c, int pass, const float* w, void* wp, b2c_stream s) {
+  (void)s;
+  int rc = check_desc(c); if (rc) return rc;
+  if (pass != B2C_PASS_FWD && pass != B2C_PASS_DGRAD) return B2C_ERR_INVALID;
+  const int T = ntaps(c);
+  const int A = c->transposed ? c->x.c : c->y.c;   /* torch dim 0 */
+  const int B = c->transposed ? c->y.c : c->x.c;   /* torch dim 1 */
+  const int n_out = pass == B2C_PASS_FWD ? c->y.c : c->x.c;
+  /* conv fwd / convT dgrad produce torch-dim-0 channels; the other two dim 1 */
+  const int out_is_A = (pass == B2C_PASS_FWD) != (c->transposed != 0);
+  const int k_in = out_is_A ? B : A;
+  for (int t = 0; t < T; t++)
+    for (int o = 0; o < n_out; o++)
+      for (int i = 0; i < k_in; i++) {
+        int a = out_is_A ? o : i, b = out_is_A ? i : o;
+        st(wp, ((int64_t)t * n_out + o) * k_in + i, c->io_dtype,
+           w[((int64_t)a * B + b) * T + t]);
+      }
+  return B2C_OK;
+}
+
+/* ---- convolution cores ----------------------------------------------- *
+ * "gather" form  (conv fwd, convT dgrad):
+ *    out[n,o,co] = sum_{k,ci} in[n, o*s + k*dil - p, ci] * Wp[k][co][ci]
+ * "scatter" form (convT fwd, conv dgrad), written as a gather over taps:
+ *    out[n,i,co] = sum_{k,ci} [s | (i+p-k*dil)] in[n,(i+p-k*dil)/s,ci] * Wp[k][co][ci]
+ * `small` is the tensor on the strided-down side of the layer, `big` the
+ * other one; the geometry (k,s,p,dil) always maps small index o to big
+ * index o*s + k*dil - p.                                                   */
+typedef struct { int n, c, d, h, w; } shp;
+static shp mk(b2c_shape s) { shp r = {s.n, s.c, s.d, s.h, s.w}; return r; }
+
+static void conv_gather(const b2c_conv_desc* c, shp big, shp small, const void* in /*big*/,
+                        const void* wp, void* out /*small*/, const b2c_fusion* f) {
+  const int dt = c->io_dtype, KD = c->k[0], KH = c->k[1], KW = c->k[2];
+  const int64_t vox = (int64_t)small.n * small.d * small.h * small.w;
+#pragma omp parallel for schedule(static)
+  for (int64_t v = 0; v < vox; v++) {
+    int ow = (int)(v % small.w); int64_t r = v / small.w;
+    int oh = (int)(r % small.h); r /= small.h;
+    int od = (int)(r % small.d); int n = (int)(r / small.d);
+    for (int co = 0; co < small.c; co++) {
+      double acc = 0.0;
+      for (int kd = 0; kd < KD; kd++) {
+        int id = od * c->stride[0] + kd * c->dil[0] - c->pad[0];
+        if (id < 0 || id >= big.d) continue;
+        for (int kh = 0; kh < KH; kh++) {
+          int ih = oh * c->stride[1] + kh * c->dil[1] - c->pad[1];
+          if (ih < 0 || ih >= big.h) continue;
+          for (int kw = 0; kw < KW; kw++) {
+            int iw = ow * c->stride[2] + kw * c->dil[2] - c->pad[2];
+            if (iw < 0 || iw >= big.w) continue;
+            int t = (kd * KH + kh) * KW + kw;
+            int64_t ib = ((((int64_t)n * big.d + id) * big.h + ih) * big.w + iw) * big.c;
+            int64_t wb = ((int64_t)t * small.c + co) * big.c;
+            for (int ci = 0; ci < big.c; ci++) acc += ld(in, ib + ci, dt) * ld(wp, wb + ci, dt);
+          }
+        }
+      }
+      if (f) {
+        if (f->bias) acc += (double)f->bias[co];
+        acc = act_f(acc, f->act, (double)f->slope);
+      }
+      st(out, v * small.c + co, dt, acc);
+    }
+  }
+}
+
+static void conv_scatter(const b2c_conv_desc* c, shp big, shp small, const void* in /*small*/,
+                         const void* wp, void* out /*big*/, const b2c_fusion* f) {
+  const int dt = c->io_dtype, KD = c->k[0], KH = c->k[1], KW = c->k[2];
+  const int64_t vox = (int64_t)big.n * big.d * big.h * big.w;
+#pragma omp parallel for schedule(static)
+  for (int64_t v = 0; v < vox; v++) {
+    int iw = (int)(v % big.w); int64_t r = v / big.w;
+    int ih = (int)(r % big.h); r /= big.h;
+    int id = (int)(r % big.d); int n = (int)(r / big.d);
+    for (int co = 0; co < big.c; co++) {
+      double acc = 0.0;
+      for (int kd = 0; kd < KD; kd++) {
+        int nd = id + c->pad[0] - kd * c->dil[0];
+        if (nd < 0 || nd % c->stride[0]) continue;
+        int od = nd / c->stride[0]; if (od >= small.d) continue;
+        for (int kh = 0; kh < KH; kh++) {
+          int nh = ih + c->pad[1] - kh * c->dil[1];
+          if (nh < 0 || nh % c->stride[1]) continue;
+          int oh = nh / c->stride[1]; if (oh >= small.h) continue;
+          for (int kw = 0; kw < KW; kw++) {
+            int nw = iw + c->pad[2] - kw * c->dil[2];
+            if (nw < 0 || nw % c->stride[2]) continue;
+            int ow = nw / c->stride[2]; if (ow >= small.w) continue;
+            int t = (kd * KH + kh) * KW + kw;
+            int64_t ib = ((((int64_t)n * small.d + od) * small.h + oh) * small.w + ow) * small.c;
+            int64_t wb = ((int64_t)t * big.c + co) * small.c;
+            for (int ci = 0; ci < small.c; ci++) acc += ld(in, ib + ci, dt) * ld(wp, wb + ci, dt);
+          }
+        }
+      }
+      if (f) {
+        if (f->bias) acc += (double)f->bias[co];
+        acc = act_f(acc, f->act, (double)f->slope);
+      }
+      st(out, v * big.c + co, dt, acc);
+    }
+  }
+}
+
+size_t b2c_conv3d_workspace(const b2c_conv_desc* c, int pass) { (void)c; (void)pass; return 0; }
+
+int b2c_conv3d_fwd(const b2c_conv_desc* c, const void* x, const void* wp, void* y,
+                   const b2c_fusion* f, void* ws, size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb; (void)s;
+  int rc = check_desc(c); if (rc) return rc;
+  if (!x || !wp || !y) return B2C_ERR_INVALID;
+  if (!c->transposed) conv_gather(c, mk(c->x), mk(c->y), x, wp, y, f);
+  else                conv_scatter(c, mk(c->y), mk(c->x), x, wp, y, f);
+  return B2C_OK;
+}
+
+int b2c_conv3d_dgrad(const b2c_conv_desc* c, const void* dy, const void* wp, void* dx,
+                     void* ws, size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb; (void)s;
+  int rc = check_desc(c); if (rc) return rc;
+  if (!dy || !wp || !dx) return B2C_ERR_INVALID;
+  if (!c->transposed) conv_scatter(c, mk(c->x), mk(c->y), dy, wp, dx, NULL);
+  else                conv_gather(c, mk(c->y), mk(c->x), dy, wp, dx, NULL);
+  return B2C_OK;
+}
+
+/* dW[a][b][k] = sum_{n,o} small[n,o,a] * big[n, o*s + k*dil - p, b]
+ * conv : small = dy (a = y.c), big = x  (b = x.c)  -> dW [y.c][x.c][k]
+ * convT: small = x  (a = x.c), big = dy (b = y.c)  -> dW [x.c][y.c][k]     */
+int b2c_conv3d_wgrad(const b2c_conv_desc* c, const void* x, const void* dy, float* dw,
+                     float* dbias, void* ws, size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb; (void)s;
+  int rc = check_desc(c); if (rc) return rc;
+  if (!x || !dy) return B2C_ERR_INVALID;
+  const int dt = c->io_dtype, KD = c->k[0], KH = c->k[1], KW = c->k[2], T = KD * KH * KW;
+  shp small = c->transposed ? mk(c->x) : mk(c->y), big = c->transposed ? mk(c->y) : mk(c->x);
+  const void* S = c->transposed ? x : dy; const void* Bg = c->transposed ? dy : x;
+  if (dw) {
+#pragma omp parallel for collapse(2) schedule(static)
+    for (int a = 0; a < small.c; a++)
+      for (int t = 0; t < T; t++) {
+        int kd = t / (KH * KW), kh = (t / KW) % KH, kw = t % KW;
+        double* acc = (double*)calloc(big.c, sizeof(double));
+        for (int n = 0; n < small.n; n++)
+          for (int od = 0; od < small.d; od++) {
+            int id = od * c->stride[0] + kd * c->dil[0] - c->pad[0];
+            if (id < 0 || id >= big.d) continue;
+            for (int oh = 0; oh < small.h; oh++) {
+              int ih = oh * c->stride[1] + kh * c->dil[1] - c->pad[1];
+              if (ih < 0 || ih >= big.h) continue;
+              for (int ow = 0; ow < small.w; ow++) {
+                int iw = ow * c->stride[2] + kw * c->dil[2] - c->pad[2];
+                if (iw < 0 || iw >= big.w) continue;
+                double sv = ld(S, ((((int64_t)n * small.d + od) * small.h + oh) * small.w + ow) * small.c + a, dt);
+                int64_t bb = ((((int64_t)n * big.d + id) * big.h + ih) * big.w + iw) * big.c;
+                for (int b = 0; b < big.c; b++) acc[b] += sv * ld(Bg, bb + b, dt);
+              }
+            }
+          }
+        for (int b = 0; b < big.c; b++) dw[((int64_t)a * big.c + b) * T + t] = (float)acc[b];
+        free(acc);
+      }
+  }
+  if (dbias) {
+    const int64_t vox = (int64_t)c->y.n * c->y.d * c->y.h * c->y.w;
+    for (int co = 0; co < c->y.c; co++) {
+      double a = 0.0;
+      for (int64_t v = 0; v < vox; v++) a += ld(dy, v * c->y.c + co, dt);
+      dbias[co] = (float)a;
+    }
+  }
+  return B2C_OK;
+}
+
+/* ---- layout ----------------------------------------------------------- */
+int b2c_transpose(const void* src, void* dst, int64_t batch, int64_t rows, int64_t cols,
+                  int sdt, int ddt, b2c_stream s) {
+  (void)s;
+  if (!src || !dst || !dt_ok(sdt) || !dt_ok(ddt) || batch < 0 || rows < 0 || cols < 0) return B2C_ERR_INVALID;
+#pragma omp parallel for schedule(static)
+  for (int64_t b = 0; b < batch; b++)
+    for (int64_t i = 0; i < rows; i++)
+      for (int64_t j = 0; j < cols; j++)
+        st(dst, (b * cols + j) * rows + i, ddt, ld(src, (b * rows + i) * cols + j, sdt));
+  return B2C_OK;
+}
+int b2c_cast(const void* src, void* dst, int64_t n, int sdt, int ddt, b2c_stream s) {
+  (void)s;
+  if (!src || !dst || !dt_ok(sdt) || !dt_ok(ddt) || n < 0) return B2C_ERR_INVALID;
+  for (int64_t i = 0; i < n; i++) st(dst, i, ddt, ld(src, i, sdt));
+  return B2C_OK;
+}
+
+/* ---- BatchNorm3d (training mode) -------------------------------------- */
+size_t b2c_stats_workspace(int64_t rows, int64_t C) { (void)rows; (void)C; return 0; }
+int b2c_channel_stats(const void* x, int64_t rows, int64_t C, int dt, float* sum, float* sq,
+                      void* ws, size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb; (void)s;
+  if (!x || !sum || !sq || !dt_ok(dt) || rows <= 0 || C <= 0) return B2C_ERR_INVALID;
+#pragma omp parallel for schedule(static)
+  for (int64_t c = 0; c < C; c++) {
+    double a = 0, b = 0;
+    for (int64_t r = 0; r < rows; r++) { double v = ld(x, r * C + c, dt); a += v; b += v * v; }
+    sum[c] = (float)a; sq[c] = (float)b;
+  }
+  return B2C_OK;
+}
+int b2c_bn_finalize(const float* sum, const float* sq, int64_t count, int64_t C, float eps,
+                    float momentum, const float* gamma, const float* beta, float* mean,
+                    float* invstd, float* scale, float* shift, float* rmean, float* rvar,
+                    b2c_stream s) {
+  (void)s;
+  if (!sum || !sq || !mean || !invstd || !scale || !shift || count <= 0 || C <= 0) return B2C_ERR_INVALID;
+  for (int64_t c = 0; c < C; c++) {
+    double m = (double)sum[c] / count;
+    double var = (double)sq[c] / count - m * m; if (var < 0) var = 0;
+    double is = 1.0 / sqrt(var + (double)eps);
+    double g = gamma ? gamma[c] : 1.0, b = beta ? beta[c] : 0.0;
+    mean[c] = (float)m; invstd[c] = (float)is;
+    scale[c] = (float)(g * is); shift[c] = (float)(b - m * g * is);
+    if (rmean) rmean[c] = (float)((1.0 - momentum) * rmean[c] + momentum * m);
+    if (rvar) {
+      double unb = count > 1 ? var * count / (double)(count - 1) : var;
+      rvar[c] = (float)((1.0 - momentum) * rvar[c] + momentum * unb);
+    }
+  }
+  return B2C_OK;
+}
+int b2c_bn_act_fwd(const void* x, void* y, const void* res, int64_t rows, int64_t C, int dt,
+                   const float* scale, const float* shift, int act, float slope, b2c_stream s) {
+  (void)s;
+  if (!x || !y || !scale || !shift || !dt_ok(dt)) return B2C_ERR_INVALID;
+#pragma omp parallel for schedule(static)
+  for (int64_t r = 0; r < rows; r++)
+    for (int64_t c = 0; c < C; c++) {
+      double z = ld(x, r * C + c, dt) * scale[c] + shift[c];
+      if (res) z += ld(res, r * C + c, dt);
+      st(y, r * C + c, dt, act_f(z, act, slope));
+    }
+  return B2C_OK;
+}
+int b2c_bn_act_bwd_reduce(const void* x, const void* dy, const void* res, int64_t rows, int64_t C,
+                          int dt, const float* mean, const float* invstd, const float* scale,
+                          const float* shift, int act, float slope, float* s1, float* s2,
+                          void* ws, size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb; (void)s;
+  if (!x || !dy || !mean || !invstd || !scale || !shift || !s1 || !s2 || !dt_ok(dt)) return B2C_ERR_INVALID;
+#pragma omp parallel for schedule(static)
+  for (int64_t c = 0; c < C; c++) {
+    double a = 0, b = 0;
+    for (int64_t r = 0; r < rows; r++) {
+      double xv = ld(x, r * C + c, dt);
+      double z = xv * scale[c] + shift[c]; if (res) z += ld(res, r * C + c, dt);
+      double g = ld(dy, r * C + c, dt) * act_dz(z, act, slope);
+      a += g; b += g * (xv - mean[c]) * invstd[c];
+    }
+    s1[c] = (float)a; s2[c] = (float)b;
+  }
+  return B2C_OK;
+}
+int b2c_bn_act_bwd_apply(const void* x, const void* dy, const void* res, void* dx, void* dres,
+                         int64_t rows, int64_t C, int dt, const float* mean, const float* invstd,
+                         const float* scale, const float* shift, const float* s1, const float* s2,
+                         int act, float slope, b2c_stream s) {
+  (void)s;
+  if (!x || !dy || !dx || !mean || !invstd || !scale || !shift || !s1 || !s2 || !dt_ok(dt)) return B2C_ERR_INVALID;
+#pragma omp parallel for schedule(static)
+  for (int64_t r = 0; r < rows; r++)
+    for (int64_t c = 0; c < C; c++) {
+      double xv = ld(x, r * C + c, dt);
+      double z = xv * scale[c] + shift[c]; if (res) z += ld(res, r * C + c, dt);
+      double g = ld(dy, r * C + c, dt) * act_dz(z, act, slope);
+      double xh = (xv - mean[c]) * invstd[c];
+      st(dx, r * C + c, dt, scale[c] * (g - s1[c] / (double)rows - xh * s2[c] / (double)rows));
+      if (dres) st(dres, r * C + c, dt, g);
+    }
+  return B2C_OK;
+}
+
+/* ---- LayerNorm over the whole sample + activation ---------------------- */
+size_t b2c_ln_workspace(int64_t N, int64_t L) { (void)N; (void)L; return 0; }
+int b2c_ln_act_fwd(const void* x, void* y, int64_t N, int64_t L, int dt, const float* gamma,
+                   const float* beta, float eps, int act, float slope, float* mean, float* rstd,
+                   void* ws, size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb; (void)s;
+  if (!x || !y || !mean || !rstd || !dt_ok(dt) || N <= 0 || L <= 0) return B2C_ERR_INVALID;
+#pragma omp parallel for schedule(static)
+  for (int64_t n = 0; n < N; n++) {
+    double a = 0, b = 0;
+    for (int64_t e = 0; e < L; e++) { double v = ld(x, n * L + e, dt); a += v; b += v * v; }
+    double m = a / L, var = b / L - m * m; if (var < 0) var = 0;
+    double rs = 1.0 / sqrt(var + (double)eps);
+    mean[n] = (float)m; rstd[n] = (float)rs;
+    for (int64_t e = 0; e < L; e++) {
+      double z = (ld(x, n * L + e, dt) - m) * rs;
+      z = z * (gamma ? gamma[e] : 1.0) + (beta ? beta[e] : 0.0);
+      st(y, n * L + e, dt, act_f(z, act, slope));
+    }
+  }
+  return B2C_OK;
+}
+int b2c_ln_act_bwd(const void* x, const void* dy, void* dx, int64_t N, int64_t L, int dt,
+                   const float* gamma, const float* beta, const float* mean, const float* rstd,
+                   int act, float slope, float* dgamma, float* dbeta, void* ws, size_t wsb,
+                   b2c_stream s) {
+  (void)ws; (void)wsb; (void)s;
+  if (!x || !dy || !mean || !rstd || !dt_ok(dt) || N <= 0 || L <= 0) return B2C_ERR_INVALID;
+  double* dg = dgamma ? (double*)calloc(L, sizeof(double)) : NULL;
+  double* db = dbeta ? (double*)calloc(L, sizeof(double)) : NULL;
+  for (int64_t n = 0; n < N; n++) {
+    double m = mean[n], rs = rstd[n], a = 0, b = 0;
+    for (int64_t e = 0; e < L; e++) {
+      double xh = (ld(x, n * L + e, dt) - m) * rs, ga = gamma ? gamma[e] : 1.0;
+      double z = xh * ga + (beta ? beta[e] : 0.0);
+      double g0 = ld(dy, n * L + e, dt) * act_dz(z, act, slope);
+      if (dg) dg[e] += g0 * xh;
+      if (db) db[e] += g0;
+      double g = g0 * ga; a += g; b += g * xh;
+    }
+    if (dx)
+      for (int64_t e = 0; e < L; e++) {
+        double xh = (ld(x, n * L + e, dt) - m) * rs, ga = gamma ? gamma[e] : 1.0;
+        double z = xh * ga + (beta ? beta[e] : 0.0);
+        double g = ld(dy, n * L + e, dt) * act_dz(z, act, slope) * ga;
+        st(dx, n * L + e, dt, rs * (g - a / L - xh * b / L));
+      }
+  }
+  if (dg) { for (int64_t e = 0; e < L; e++) dgamma[e] = (float)dg[e]; free(dg); }
+  if (db) { for (int64_t e = 0; e < L; e++) dbeta[e] = (float)db[e]; free(db); }
+  return B2C_OK;
+}
+
+/* ---- pointwise ---------------------------------------------------------- */
+int b2c_act_fwd(const void* x, void* y, int64_t n, int dt, int act, float slope, b2c_stream s) {
+  (void)s;
+  if (!x || !y || !dt_ok(dt) || n < 0) return B2C_ERR_INVALID;
+  for (int64_t i = 0; i < n; i++) st(y, i, dt, act_f(ld(x, i, dt), act, slope));
+  return B2C_OK;
+}
+int b2c_act_bwd(const void* y, const void* dy, void* dx, int64_t n, int dt, int act, float slope,
+                b2c_stream s) {
+  (void)s;
+  if (!y || !dy || !dx || !dt_ok(dt) || n < 0) return B2C_ERR_INVALID;
+  for (int64_t i = 0; i < n; i++) st(dx, i, dt, ld(dy, i, dt) * act_dy(ld(y, i, dt), act, slope));
+  return B2C_OK;
+}
