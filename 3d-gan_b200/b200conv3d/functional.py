@@ -300,3 +300,245 @@ def conv_transpose3d(x, weight, bias=None, stride=1, padding=0, output_padding=0
         raise NotImplementedError("b200conv3d.conv_transpose3d: groups=%d is not supported" % groups)
     g = Geom(True, tuple(weight.shape[2:]), stride, padding, dilation, output_padding)
     return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+
+
+# -------------------------------------------------------------- batch norm
+def _f32(t):
+    if t is None:
+        return None
+    t = t.detach()
+    return t if t.dtype == torch.float32 and t.is_contiguous() else t.float().contiguous()
+
+
+class _BNActFn(Function):
+    """BatchNorm3d (+ residual add) (+ activation) in training or eval mode.
+    dcgan.py:48-64, utils.py:62-86, biggan.py:40-41, FID_ResNet.py:71-100."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, rmean, rvar, training, momentum, eps, act, slope):
+        _check_device(x)
+        cd = compute_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        rb = to_ndhwc(residual.detach(), cd) if residual is not None else None
+        n, d, h, w, c = xb.shape
+        rows = n * d * h * w
+        L = _lib.lib()
+        dev = x.device
+        stats = torch.empty((6, c), dtype=torch.float32, device=dev)
+        s_sum, s_sq, mean, invstd, scale, shift = stats.unbind(0)
+        gf, bf = _f32(gamma), _f32(beta)
+        with _dev(x):
+            st = _stream(x)
+            if training:
+                ws = _ws(L.b2c_stats_workspace(rows, c), x)
+                check(L.b2c_channel_stats(_ptr(xb), rows, c, _dt(cd), _ptr(s_sum), _ptr(s_sq),
+                                          _ptr(ws), ws.numel(), st), "channel_stats")
+                check(L.b2c_bn_finalize(_ptr(s_sum), _ptr(s_sq), rows, c, float(eps),
+                                        float(momentum), _ptr(gf), _ptr(bf), _ptr(mean),
+                                        _ptr(invstd), _ptr(scale), _ptr(shift),
+                                        _ptr(rmean), _ptr(rvar), st), "bn_finalize")
+            else:
+                # eval mode: [C]-sized glue on the running statistics
+                mean.copy_(rmean)
+                invstd.copy_(torch.rsqrt(rvar.float() + eps))
+                scale.copy_(invstd if gf is None else gf * invstd)
+                shift.copy_((0 if bf is None else bf) - mean * scale)
+            y = torch.empty_like(xb)
+            check(L.b2c_bn_act_fwd(_ptr(xb), _ptr(y), _ptr(rb), rows, c, _dt(cd), _ptr(scale),
+                                   _ptr(shift), int(act), float(slope), st), "bn_act_fwd")
+        ctx.save_for_backward(xb, rb, stats)
+        ctx.training, ctx.act, ctx.slope, ctx.cd = bool(training), int(act), float(slope), cd
+        ctx.x_dtype = x.dtype
+        ctx.res_dtype = residual.dtype if residual is not None else None
+        ctx.affine = (gamma is not None, beta is not None)
+        return from_ndhwc(y)
+
+    @staticmethod
+    def backward(ctx, gy):
+        xb, rb, stats = ctx.saved_tensors
+        _, _, mean, invstd, scale, shift = stats.unbind(0)
+        cd = ctx.cd
+        n, d, h, w, c = xb.shape
+        rows = n * d * h * w
+        L = _lib.lib()
+        gyb = to_ndhwc(gy, cd)
+        s = torch.zeros((2, c), dtype=torch.float32, device=xb.device)
+        s1, s2 = s.unbind(0)
+        need_x = ctx.needs_input_grad[0]
+        need_res = rb is not None and ctx.needs_input_grad[3]
+        need_aff = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        dx = dres = None
+        with _dev(xb):
+            st = _stream(xb)
+            if ctx.training or need_aff:
+                ws = _ws(L.b2c_stats_workspace(rows, c), xb)
+                check(L.b2c_bn_act_bwd_reduce(_ptr(xb), _ptr(gyb), _ptr(rb), rows, c, _dt(cd),
+                                              _ptr(mean), _ptr(invstd), _ptr(scale), _ptr(shift),
+                                              ctx.act, ctx.slope, _ptr(s1), _ptr(s2), _ptr(ws),
+                                              ws.numel(), st), "bn_act_bwd_reduce")
+            if need_x or need_res:
+                dxb = torch.empty_like(xb)
+                drb = torch.empty_like(xb) if need_res else None
+                # eval mode: statistics are constants -> no mean-subtraction terms
+                a1, a2 = (s1, s2) if ctx.training else (torch.zeros_like(s1), torch.zeros_like(s2))
+                check(L.b2c_bn_act_bwd_apply(_ptr(xb), _ptr(gyb), _ptr(rb), _ptr(dxb), _ptr(drb),
+                                             rows, c, _dt(cd), _ptr(mean), _ptr(invstd),
+                                             _ptr(scale), _ptr(shift), _ptr(a1), _ptr(a2),
+                                             ctx.act, ctx.slope, st), "bn_act_bwd_apply")
+                if need_x:
+                    dx = from_ndhwc(cast(dxb, torch.float32) if ctx.x_dtype == torch.float32 else dxb)
+                if need_res:
+                    dres = from_ndhwc(cast(drb, torch.float32) if ctx.res_dtype == torch.float32 else drb)
+        dgamma = s2.clone() if (ctx.affine[0] and ctx.needs_input_grad[1]) else None
+        dbeta = s1.clone() if (ctx.affine[1] and ctx.needs_input_grad[2]) else None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None
+
+
+def batch_norm_act(x, gamma, beta, running_mean, running_var, training, momentum, eps,
+                   act=None, slope=0.0, residual=None):
+    use_batch = training or running_mean is None
+    return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, use_batch,
+                          0.0 if momentum is None else momentum, eps, _act_id(act), slope)
+
+
+# -------------------------------------------------------------- layer norm
+def _perm_affine(p, c, s, to_ndhwc_order):
+    """[C,D,H,W] fp32 <-> [D,H,W,C] fp32 through b2c_transpose."""
+    pf = _f32(p).reshape(-1)
+    out = torch.empty_like(pf)
+    rows, cols = (c, s) if to_ndhwc_order else (s, c)
+    with _dev(pf):
+        check(_lib.lib().b2c_transpose(_ptr(pf), _ptr(out), 1, rows, cols, F32, F32, _stream(pf)),
+              "transpose")
+    return out
+
+
+class _LNActFn(Function):
+    """nn.LayerNorm([C,D,H,W]) (+ LeakyReLU) of the DCGAN discriminator,
+    dcgan.py:162-179: per-sample statistics over C*D*H*W and a full-shape
+    elementwise affine."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps, act, slope):
+        _check_device(x)
+        cd = compute_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, c = xb.shape
+        Lh = d * h * w * c
+        L = _lib.lib()
+        gp = _perm_affine(gamma, c, d * h * w, True) if gamma is not None else None
+        bp = _perm_affine(beta, c, d * h * w, True) if beta is not None else None
+        mr = torch.empty((2, n), dtype=torch.float32, device=x.device)
+        y = torch.empty_like(xb)
+        ws = _ws(L.b2c_ln_workspace(n, Lh), x)
+        with _dev(x):
+            check(L.b2c_ln_act_fwd(_ptr(xb), _ptr(y), n, Lh, _dt(cd), _ptr(gp), _ptr(bp),
+                                   float(eps), int(act), float(slope), _ptr(mr[0]), _ptr(mr[1]),
+                                   _ptr(ws), ws.numel(), _stream(x)), "ln_act_fwd")
+        ctx.save_for_backward(xb, gp, bp, mr)
+        ctx.act, ctx.slope, ctx.cd, ctx.x_dtype = int(act), float(slope), cd, x.dtype
+        ctx.pshape = tuple(gamma.shape) if gamma is not None else None
+        return from_ndhwc(y)
+
+    @staticmethod
+    def backward(ctx, gy):
+        xb, gp, bp, mr = ctx.saved_tensors
+        cd = ctx.cd
+        n, d, h, w, c = xb.shape
+        Lh = d * h * w * c
+        L = _lib.lib()
+        gyb = to_ndhwc(gy, cd)
+        need_x = ctx.needs_input_grad[0]
+        need_g = gp is not None and ctx.needs_input_grad[1]
+        need_b = bp is not None and ctx.needs_input_grad[2]
+        dxb = torch.empty_like(xb) if need_x else None
+        dg = torch.empty(Lh, dtype=torch.float32, device=xb.device) if need_g else None
+        db = torch.empty(Lh, dtype=torch.float32, device=xb.device) if need_b else None
+        ws = _ws(L.b2c_ln_workspace(n, Lh), xb)
+        with _dev(xb):
+            check(L.b2c_ln_act_bwd(_ptr(xb), _ptr(gyb), _ptr(dxb), n, Lh, _dt(cd), _ptr(gp),
+                                   _ptr(bp), _ptr(mr[0]), _ptr(mr[1]), ctx.act, ctx.slope,
+                                   _ptr(dg), _ptr(db), _ptr(ws), ws.numel(), _stream(xb)),
+                  "ln_act_bwd")
+        dx = None
+        if need_x:
+            dx = from_ndhwc(cast(dxb, torch.float32) if ctx.x_dtype == torch.float32 else dxb)
+        dgamma = _perm_affine(dg, c, d * h * w, False).reshape(ctx.pshape) if need_g else None
+        dbeta = _perm_affine(db, c, d * h * w, False).reshape(ctx.pshape) if need_b else None
+        return dx, dgamma, dbeta, None, None, None
+
+
+def layer_norm_act(x, gamma, beta, eps, act=None, slope=0.0):
+    return _LNActFn.apply(x, gamma, beta, eps, _act_id(act), slope)
+
+
+# --------------------------------------------------------------- pointwise
+def _dense_flat(x):
+    """(flat dense view or None) for tensors whose storage is dense in some
+    permutation — elementwise kernels do not care about the order."""
+    if x.is_contiguous():
+        return x.view(-1)
+    if x.dim() == 5:
+        p = x.permute(0, 2, 3, 4, 1)
+        if p.is_contiguous():
+            return p.reshape(-1)
+    return None
+
+
+class _ActFn(Function):
+    """ReLU / LeakyReLU / Tanh (dcgan.py:49,68,163; utils.py:68; biggan.py:63)."""
+
+    @staticmethod
+    def forward(ctx, x, act, slope, inplace):
+        _check_device(x)
+        L = _lib.lib()
+        flat = _dense_flat(x) if x.dtype in (torch.bfloat16, torch.float32) else None
+        if inplace and flat is not None:
+            ctx.mark_dirty(x)
+            out, oflat = x, flat
+        else:
+            if flat is None:
+                xs = x.contiguous()
+                xs = xs if xs.dtype in (torch.bfloat16, torch.float32) else xs.float()
+                flat = xs.view(-1)
+                out = torch.empty_like(xs)
+                oflat = out.view(-1)
+            else:
+                out = torch.empty_like(x)      # preserves (dense) strides
+                oflat = _dense_flat(out)
+        with _dev(x):
+            check(L.b2c_act_fwd(_ptr(flat), _ptr(oflat), flat.numel(), _dt(flat.dtype), int(act),
+                                float(slope), _stream(x)), "act_fwd")
+        if inplace and out is not x:
+            x.copy_(out)
+            ctx.mark_dirty(x)
+            out = x
+        ctx.act, ctx.slope = int(act), float(slope)
+        ctx.save_for_backward(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, gy):
+        (y,) = ctx.saved_tensors
+        L = _lib.lib()
+        yf = _dense_flat(y)
+        if yf is None or y.dtype not in (torch.bfloat16, torch.float32):
+            y = y.contiguous()
+            y = y if y.dtype in (torch.bfloat16, torch.float32) else y.float()
+            yf = y.view(-1)
+        # bring gy to y's physical order and dtype
+        g = gy if gy.dtype == y.dtype else gy.to(y.dtype)
+        if g.stride() != y.stride() or _dense_flat(g) is None:
+            g2 = torch.empty_like(y)
+            g2.copy_(g)
+            g = g2
+        gf = _dense_flat(g)
+        dx = torch.empty_like(y)
+        with _dev(y):
+            check(L.b2c_act_bwd(_ptr(yf), _ptr(gf), _ptr(_dense_flat(dx)), yf.numel(),
+                                _dt(yf.dtype), ctx.act, ctx.slope, _stream(y)), "act_bwd")
+        return dx, None, None, None
+
+
+def activation(x, act, slope=0.0, inplace=False):
+    return _ActFn.apply(x, _act_id(act), slope, inplace)

@@ -1,0 +1,123 @@
+"""Drop-in ``torch.nn`` layer subclasses (Face 1).
+
+Each class subclasses the torch layer it replaces, so constructor signature,
+parameter / buffer names, shapes, dtypes and ``state_dict`` are identical, and
+``isinstance(m, nn.Conv3d)`` (biggan.py:49,105; FID_ResNet.py:140-142),
+``m.__class__.__name__.find('Conv')`` (dcgan.py:75-81) and
+``spectral_norm(module)`` (utils.py:13) keep working.  Only ``forward`` differs:
+it calls the sm_100a library through :mod:`b200conv3d.functional`.
+
+``fused_act`` / ``fused_slope`` are set by :func:`b200conv3d.patch.fuse` when the
+next module of an ``nn.Sequential`` is an activation; they are plain Python
+attributes, never parameters.
+"""
+import torch
+import torch.nn as tnn
+
+from . import functional as BF
+
+# the stock classes, captured before install() can rebind torch.nn.*
+_TConv3d = tnn.Conv3d
+_TConvTranspose3d = tnn.ConvTranspose3d
+_TBatchNorm3d = tnn.BatchNorm3d
+_TLayerNorm = tnn.LayerNorm
+_TReLU = tnn.ReLU
+_TLeakyReLU = tnn.LeakyReLU
+_TTanh = tnn.Tanh
+
+
+class Conv3d(_TConv3d):
+    """nn.Conv3d replacement (dcgan.py:161-181, utils.py:8-14,
+    FID_ResNet.py:9-16,70-75,119-125,157-162, stylegan.py:998-1038)."""
+    fused_act = None
+    fused_slope = 0.0
+
+    def forward(self, x):
+        if self.padding_mode != "zeros":
+            raise NotImplementedError("b200conv3d.Conv3d: padding_mode=%r is not supported"
+                                      % self.padding_mode)
+        return BF.conv3d(x, self.weight, self.bias, self.stride, self.padding, self.dilation,
+                         self.groups, act=self.fused_act, slope=self.fused_slope)
+
+
+class ConvTranspose3d(_TConvTranspose3d):
+    """nn.ConvTranspose3d replacement (dcgan.py:19-40,47-67)."""
+    fused_act = None
+    fused_slope = 0.0
+
+    def forward(self, x, output_size=None):
+        if self.padding_mode != "zeros":
+            raise NotImplementedError("b200conv3d.ConvTranspose3d: only zeros padding")
+        out_pad = self.output_padding
+        if output_size is not None:
+            out_pad = self._output_padding(x, output_size, self.stride, self.padding,
+                                           self.kernel_size, 3, self.dilation)
+        return BF.conv_transpose3d(x, self.weight, self.bias, self.stride, self.padding, out_pad,
+                                   self.groups, self.dilation, act=self.fused_act,
+                                   slope=self.fused_slope)
+
+
+class BatchNorm3d(_TBatchNorm3d):
+    """nn.BatchNorm3d replacement (dcgan.py:48-64, utils.py:62-65, biggan.py:40,
+    FID_ResNet.py:71-76,127,162).  Same momentum / running-stat semantics as
+    torch (including ``num_batches_tracked`` and ``momentum=None``)."""
+    fused_act = None
+    fused_slope = 0.0
+
+    def forward(self, x, residual=None):
+        self._check_input_dim(x)
+        eaf = 0.0 if self.momentum is None else self.momentum
+        if self.training and self.track_running_stats and self.num_batches_tracked is not None:
+            self.num_batches_tracked.add_(1)
+            if self.momentum is None:
+                eaf = 1.0 / float(self.num_batches_tracked)
+        bn_training = self.training or (self.running_mean is None and self.running_var is None)
+        rm = self.running_mean if (not self.training or self.track_running_stats) else None
+        rv = self.running_var if (not self.training or self.track_running_stats) else None
+        return BF.batch_norm_act(x, self.weight, self.bias, rm, rv, bn_training, eaf, self.eps,
+                                 act=self.fused_act, slope=self.fused_slope, residual=residual)
+
+
+class LayerNorm(_TLayerNorm):
+    """nn.LayerNorm replacement for the whole-sample form the DCGAN
+    discriminator uses, ``LayerNorm([C,D,H,W])`` on a 5-D input
+    (dcgan.py:162,166,170,174,178).  Any other use of nn.LayerNorm is not on
+    the reference's hot path and keeps torch's implementation."""
+    fused_act = None
+    fused_slope = 0.0
+
+    def forward(self, x):
+        if x.dim() == 5 and tuple(self.normalized_shape) == tuple(x.shape[1:]):
+            return BF.layer_norm_act(x, self.weight, self.bias, self.eps, act=self.fused_act,
+                                     slope=self.fused_slope)
+        if self.fused_act is not None:
+            raise RuntimeError("fused LayerNorm activation needs the whole-sample 5-D form")
+        return super().forward(x)
+
+
+class ReLU(_TReLU):
+    def forward(self, x):
+        return BF.activation(x, "relu", 0.0, self.inplace)
+
+
+class LeakyReLU(_TLeakyReLU):
+    def forward(self, x):
+        return BF.activation(x, "lrelu", self.negative_slope, self.inplace)
+
+
+class Tanh(_TTanh):
+    def forward(self, x):
+        return BF.activation(x, "tanh", 0.0, False)
+
+
+class FusedAway(tnn.Identity):
+    """Placeholder left where an activation was folded into the previous layer
+    by :func:`b200conv3d.patch.fuse`; keeps nn.Sequential indices (and thus
+    ``state_dict`` keys such as ``main.3.weight``) unchanged."""
+
+    def __init__(self, original):
+        super().__init__()
+        self.original_repr = repr(original)
+
+    def extra_repr(self):
+        return "fused: " + self.original_repr

@@ -1,0 +1,127 @@
+"""The single switch that turns the replacement on (SURVEY.md §5 "Config").
+
+* :func:`install` rebinds ``torch.nn.Conv3d / ConvTranspose3d / BatchNorm3d /
+  LayerNorm / ReLU / LeakyReLU / Tanh`` and ``torch.nn.functional.conv3d /
+  conv_transpose3d`` so that the reference's model files (dcgan.py, biggan.py,
+  utils.py, stylegan.py, FID_ResNet.py), which only say ``nn.Conv3d(...)``,
+  build B200 layers without being edited.
+* :func:`convert` retrofits an already-built model in place (class swap; the
+  parameters are untouched so ``state_dict`` round-trips both ways).
+* :func:`fuse` folds ``X -> activation`` pairs inside ``nn.Sequential``s into
+  X's epilogue without renaming anything.
+"""
+import torch
+import torch.nn as tnn
+import torch.nn.functional as TF
+
+from . import functional as BF
+from . import nn as BN
+
+_CLASS_MAP = {
+    "Conv3d": (BN._TConv3d, BN.Conv3d),
+    "ConvTranspose3d": (BN._TConvTranspose3d, BN.ConvTranspose3d),
+    "BatchNorm3d": (BN._TBatchNorm3d, BN.BatchNorm3d),
+    "LayerNorm": (BN._TLayerNorm, BN.LayerNorm),
+    "ReLU": (BN._TReLU, BN.ReLU),
+    "LeakyReLU": (BN._TLeakyReLU, BN.LeakyReLU),
+    "Tanh": (BN._TTanh, BN.Tanh),
+}
+_stock_functional = {"conv3d": TF.conv3d, "conv_transpose3d": TF.conv_transpose3d}
+_installed = [False]
+
+
+def _f_conv3d(input, weight, bias=None, stride=1, padding=0, dilation=1, groups=1):
+    return BF.conv3d(input, weight, bias, stride, padding, dilation, groups)
+
+
+def _f_conv_transpose3d(input, weight, bias=None, stride=1, padding=0, output_padding=0,
+                        groups=1, dilation=1):
+    return BF.conv_transpose3d(input, weight, bias, stride, padding, output_padding, groups,
+                               dilation)
+
+
+def install():
+    """Rebind the torch layer names the reference uses.  Idempotent."""
+    for name, (_, ours) in _CLASS_MAP.items():
+        setattr(tnn, name, ours)
+    TF.conv3d = _f_conv3d
+    TF.conv_transpose3d = _f_conv_transpose3d
+    _installed[0] = True
+
+
+def uninstall():
+    for name, (stock, _) in _CLASS_MAP.items():
+        setattr(tnn, name, stock)
+    TF.conv3d = _stock_functional["conv3d"]
+    TF.conv_transpose3d = _stock_functional["conv_transpose3d"]
+    _installed[0] = False
+
+
+def is_installed():
+    return _installed[0]
+
+
+def _swap_class(m):
+    cls = type(m)
+    for stock, ours in _CLASS_MAP.values():
+        if cls is stock:
+            m.__class__ = ours
+            return True
+        # spectral_norm & co. give each module its own "Parametrized<Cls>" class
+        if cls.__name__.startswith("Parametrized") and cls.__bases__ == (stock,):
+            cls.__bases__ = (ours,)
+            return True
+    return False
+
+
+def convert(model):
+    """Swap stock torch layers inside ``model`` for B200 layers, in place."""
+    n = 0
+    for m in model.modules():
+        n += bool(_swap_class(m))
+    return n
+
+
+def _act_of(m):
+    if isinstance(m, BN._TLeakyReLU):
+        return "lrelu", float(m.negative_slope)
+    if isinstance(m, BN._TReLU):
+        return "relu", 0.0
+    if isinstance(m, BN._TTanh):
+        return "tanh", 0.0
+    return None
+
+
+def _fusable(m):
+    if isinstance(m, (BN.Conv3d, BN.ConvTranspose3d, BN.BatchNorm3d)):
+        return m.fused_act is None
+    if isinstance(m, BN.LayerNorm):
+        return m.fused_act is None and len(m.normalized_shape) == 4
+    return False
+
+
+def fuse(model):
+    """Fold ``layer -> ReLU/LeakyReLU/Tanh`` pairs of every nn.Sequential into
+    the layer's epilogue (dcgan.py:45-70: ConvT-BN-ReLU, ConvT-Tanh;
+    dcgan.py:117-182: Conv-LN-LeakyReLU, Conv-LeakyReLU).  Returns the number
+    of activations folded.  Indices, names and parameters do not change."""
+    n = 0
+    for seq in model.modules():
+        if not isinstance(seq, tnn.Sequential):
+            continue
+        for i in range(len(seq) - 1):
+            a, b = seq[i], seq[i + 1]
+            act = _act_of(b)
+            if act is not None and _fusable(a):
+                a.fused_act, a.fused_slope = act
+                seq[i + 1] = BN.FusedAway(b)
+                n += 1
+    return n
+
+
+def prepare(model, do_fuse=True):
+    """convert + fuse; returns the model."""
+    convert(model)
+    if do_fuse:
+        fuse(model)
+    return model

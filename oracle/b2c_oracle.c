@@ -21,7 +21,7 @@
  * this image).  This file restates torch's documented definitions of those
  * ops.  Parity pinning: the reference ships NO tests or golden vectors
  * (SURVEY.md §4), so this oracle is pinned against outputs of the reference's
- * own modules imported in the build container (tests/golden/*.npz, generated
+ * own modules imported in the build container (tests/golden/ npz files, generated
  * by oracle/make_golden.py) and against torch CPU fp32 ops
  * (tests/test_oracle.py).
  *
