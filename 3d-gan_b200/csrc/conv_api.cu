@@ -1,0 +1,136 @@
+// conv_api.cu — b2c_conv3d_{workspace,fwd,dgrad,wgrad}: validation and dispatch
+// between the tcgen05 implicit-GEMM path (bf16) and the direct CUDA-core path
+// (fp32, or shapes the tensor-core path does not take).
+#include "direct_conv.cuh"
+#include "tc_conv.cuh"
+
+using namespace b2c;
+
+namespace {
+
+bool tc_allowed(const b2c_conv_desc* c) { return c->io_dtype == B2C_BF16 && c->algo != B2C_ALGO_DIRECT; }
+
+// ConvTranspose3d on a 1x1x1 input with stride-independent geometry (dcgan.py:47,
+// z -> 4^3): every output voxel sees exactly one tap, so the layer is the plain
+// GEMM  y[n, (tap,co)] = x[n,:] . Wp[tap][co][:]  — a 1x1x1 conv with taps*Cout
+// output channels over the SAME packed filter memory.
+bool is_point_convT(const b2c_conv_desc* c) {
+  if (!c->transposed) return false;
+  if (c->x.d != 1 || c->x.h != 1 || c->x.w != 1) return false;
+  for (int i = 0; i < 3; i++) if (c->pad[i] != 0) return false;
+  return c->y.d == c->dil[0] * (c->k[0] - 1) + 1 && c->y.h == c->dil[1] * (c->k[1] - 1) + 1 &&
+         c->y.w == c->dil[2] * (c->k[2] - 1) + 1 && c->dil[0] == 1 && c->dil[1] == 1 && c->dil[2] == 1;
+}
+
+int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w, void* out, const float* bias,
+             int act, float slope, cudaStream_t st) {
+  const Geo g = make_geo(c);
+  if (tc_allowed(c)) {
+    ConvPlan plan;
+    int rc;
+    int bias_mod = 0;
+    if (scatter && c->transposed && is_point_convT(c)) {
+      Geo pg = g;                       // small = y viewed as 1^3 with taps*Cout channels, big = x
+      const int T = g.taps();
+      pg.sc = T * c->y.c; pg.sd = pg.sh = pg.sw = 1;
+      pg.bc = c->x.c; pg.bd = pg.bh = pg.bw = 1;
+      for (int i = 0; i < 3; i++) { pg.k[i] = 1; pg.s[i] = 1; pg.p[i] = 0; pg.dl[i] = 1; }
+      rc = plan_gather(pg, &plan);
+      bias_mod = c->y.c;
+    } else {
+      rc = scatter ? plan_scatter(g, &plan) : plan_gather(g, &plan);
+    }
+    if (rc == B2C_OK) {
+      t_last_algo = B2C_ALGO_TC;
+      return tc_conv_launch(plan, in, w, out, bias, bias_mod, act, slope, st);
+    }
+    if (c->algo == B2C_ALGO_TC) return B2C_ERR_UNSUPPORTED;
+  } else if (c->algo == B2C_ALGO_TC) {
+    return B2C_ERR_UNSUPPORTED;
+  }
+  t_last_algo = B2C_ALGO_DIRECT;
+  return scatter ? direct_scatter(g, c->io_dtype, in, w, out, bias, act, slope, st)
+                 : direct_gather(g, c->io_dtype, in, w, out, bias, act, slope, st);
+}
+
+}  // namespace
+
+extern "C" size_t b2c_conv3d_workspace(const b2c_conv_desc* c, int pass) {
+  if (check_desc(c)) return 0;
+  if (pass == B2C_PASS_WGRAD && tc_allowed(c)) return tc_wgrad_workspace(make_geo(c));
+  return 0;
+}
+
+extern "C" int b2c_conv3d_fwd(const b2c_conv_desc* c, const void* x, const void* wp, void* y, const b2c_fusion* f,
+                              void* ws, size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb;
+  int rc = check_desc(c);
+  if (rc) return rc;
+  if (!x || !wp || !y) return B2C_ERR_INVALID;
+  const float* bias = f ? f->bias : nullptr;
+  const int act = f ? f->act : B2C_ACT_NONE;
+  const float slope = f ? f->slope : 0.f;
+  if (act < B2C_ACT_NONE || act > B2C_ACT_TANH) return B2C_ERR_INVALID;
+  return fwd_like(c, c->transposed != 0, x, wp, y, bias, act, slope, static_cast<cudaStream_t>(s));
+}
+
+extern "C" int b2c_conv3d_dgrad(const b2c_conv_desc* c, const void* dy, const void* wp, void* dx, void* ws,
+                                size_t wsb, b2c_stream s) {
+  (void)ws; (void)wsb;
+  int rc = check_desc(c);
+  if (rc) return rc;
+  if (!dy || !wp || !dx) return B2C_ERR_INVALID;
+  // dgrad of a conv is the scatter form; dgrad of a convT is the gather form.
+  b2c_conv_desc d = *c;
+  // fwd_like() reads geometry only through make_geo(), which is pass-independent.
+  const Geo g = make_geo(&d);
+  const bool scatter = !c->transposed;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (tc_allowed(c)) {
+    ConvPlan plan;
+    rc = scatter ? plan_scatter(g, &plan) : plan_gather(g, &plan);
+    if (rc == B2C_OK) {
+      t_last_algo = B2C_ALGO_TC;
+      return tc_conv_launch(plan, dy, wp, dx, nullptr, 0, B2C_ACT_NONE, 0.f, st);
+    }
+    if (c->algo == B2C_ALGO_TC) return B2C_ERR_UNSUPPORTED;
+  } else if (c->algo == B2C_ALGO_TC) {
+    return B2C_ERR_UNSUPPORTED;
+  }
+  t_last_algo = B2C_ALGO_DIRECT;
+  return scatter ? direct_scatter(g, c->io_dtype, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, st)
+                 : direct_gather(g, c->io_dtype, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, st);
+}
+
+extern "C" int b2c_conv3d_wgrad(const b2c_conv_desc* c, const void* x, const void* dy, float* dw, float* dbias,
+                                void* ws, size_t wsb, b2c_stream s) {
+  int rc = check_desc(c);
+  if (rc) return rc;
+  if (!x || !dy) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  const Geo g = make_geo(c);
+  const void* small = c->transposed ? x : dy;
+  const void* big = c->transposed ? dy : x;
+  if (dw) {
+    bool done = false;
+    if (tc_allowed(c) && tc_wgrad_supported(g)) {
+      t_last_algo = B2C_ALGO_TC;
+      rc = tc_wgrad_launch(g, small, big, dw, ws, wsb, st);
+      if (rc) return rc;
+      done = true;
+    } else if (c->algo == B2C_ALGO_TC) {
+      return B2C_ERR_UNSUPPORTED;
+    }
+    if (!done) {
+      t_last_algo = B2C_ALGO_DIRECT;
+      rc = direct_wgrad(g, c->io_dtype, small, big, dw, st);
+      if (rc) return rc;
+    }
+  }
+  if (dbias) {
+    const int64_t rows = (int64_t)c->y.n * c->y.d * c->y.h * c->y.w;
+    rc = channel_sum(dy, rows, c->y.c, c->io_dtype, dbias, st);
+    if (rc) return rc;
+  }
+  return B2C_OK;
+}

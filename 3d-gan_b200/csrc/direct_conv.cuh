@@ -1,0 +1,18 @@
+// direct_conv.cuh — CUDA-core direct convolution (fp32 accumulate).  The exact
+// fp32 path (north_star: fp32 max-rel <= 1e-4) and the catch-all for shapes the
+// tcgen05 path does not take.
+#pragma once
+#include "common.cuh"
+
+namespace b2c {
+// small <- big gather : out[n,o,co]  = sum in[n,o*s+k*dl-p,ci] * W[t][co][ci]   (co in small.c, ci in big.c)
+int direct_gather(const Geo& g, int dt, const void* in_big, const void* w, void* out_small, const float* bias,
+                  int act, float slope, cudaStream_t st);
+// big <- small scatter: out[n,i,co]  = sum [s|(i+p-k*dl)] in[n,(i+p-k*dl)/s,ci] * W[t][co][ci]  (co in big.c, ci in small.c)
+int direct_scatter(const Geo& g, int dt, const void* in_small, const void* w, void* out_big, const float* bias,
+                   int act, float slope, cudaStream_t st);
+// dW[a][b][t] = sum small[n,o,a] * big[n,o*s+k*dl-p,b]   (torch layout, fp32, overwritten)
+int direct_wgrad(const Geo& g, int dt, const void* small, const void* big, float* dw, cudaStream_t st);
+// out[c] = sum_rows x[r][c]
+int channel_sum(const void* x, int64_t rows, int C, int dt, float* out, cudaStream_t st);
+}  // namespace b2c

@@ -1,0 +1,576 @@
+// norm.cu — HBM-bound normalisation / activation passes over NDHWC tensors:
+// BatchNorm3d statistics + apply (+residual, +activation) and backward,
+// whole-sample LayerNorm (+activation) and backward, pointwise activations.
+// Every kernel moves 16-byte vectors, grids are sized in multiples of the SM
+// count, and all reductions are deterministic two-stage trees (no atomics).
+#include "common.cuh"
+
+namespace b2c {
+
+constexpr int kThreads = 256;
+constexpr int kBlocksPerSM = 4;
+
+// ===========================================================================
+// Per-channel two-value reduction over rows of an [rows][C] tensor.
+//   out0[c] = sum_r f0(r,c),  out1[c] = sum_r f1(r,c)
+// Stage 1: block b owns a contiguous slab of rows; a thread owns VEC adjacent
+// channels (one 16 B load) and walks rows with stride (kThreads / lanes_per_row).
+// Partial sums for the same channel group are combined through shared memory
+// and written to ws[b][2][C].  Stage 2 sums ws over blocks in fixed order.
+// ===========================================================================
+template <typename T>
+struct BnBwdF {            // g = dy*act'(z);  f0 = g, f1 = g*xhat
+  const T* dy; const T* res;
+  const float *mean, *invstd, *scale, *shift;
+  int act; float slope;
+};
+
+template <typename T, int VEC, bool BWD>
+__global__ void __launch_bounds__(kThreads)
+chan_reduce_stage1(const T* __restrict__ x, int64_t rows, int C, BnBwdF<T> f, float* __restrict__ ws,
+                   int64_t rows_per_block) {
+  extern __shared__ float sm[];           // [kThreads][2*VEC]
+  const int groups = (C + VEC - 1) / VEC;                 // channel groups per row
+  const int lanes = groups < kThreads ? groups : kThreads; // threads across channels
+  const int rstep = kThreads / lanes;                     // rows processed in parallel
+  const int lane = threadIdx.x % lanes, rlane = threadIdx.x / lanes;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+  float* wsb = ws + (int64_t)blockIdx.x * 2 * C;
+  for (int g0 = 0; g0 < groups; g0 += lanes) {
+    const int g = g0 + lane;
+    const int c0 = g * VEC;
+    float a[VEC], b[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; i++) a[i] = b[i] = 0.f;
+    if (g < groups && rlane < rstep) {
+      float mu[VEC], is[VEC], sc[VEC], sh[VEC];
+      if (BWD) {
+#pragma unroll
+        for (int i = 0; i < VEC; i++) {
+          int c = c0 + i < C ? c0 + i : C - 1;
+          mu[i] = f.mean[c]; is[i] = f.invstd[c]; sc[i] = f.scale[c]; sh[i] = f.shift[c];
+        }
+      }
+      for (int64_t r = r0 + rlane; r < r1; r += rstep) {
+        float xv[VEC], dv[VEC], rv[VEC];
+        const int64_t off = r * C + c0;
+        if (VEC > 1) {
+          Vec<T> v; v.load(x + off); v.unpack(xv);
+          if (BWD) { v.load(f.dy + off); v.unpack(dv); if (f.res) { v.load(f.res + off); v.unpack(rv); } }
+        } else {
+          xv[0] = ldf(x, off);
+          if (BWD) { dv[0] = ldf(f.dy, off); if (f.res) rv[0] = ldf(f.res, off); }
+        }
+#pragma unroll
+        for (int i = 0; i < VEC; i++) {
+          if (BWD) {
+            float z = xv[i] * sc[i] + sh[i];
+            if (f.res) z += rv[i];
+            float gg = dv[i] * act_dz(z, f.act, f.slope);
+            a[i] += gg; b[i] += gg * (xv[i] - mu[i]) * is[i];
+          } else {
+            a[i] += xv[i]; b[i] += xv[i] * xv[i];
+          }
+        }
+      }
+    }
+    // combine the rstep row-lanes of each channel group
+    float* my = sm + threadIdx.x * 2 * VEC;
+#pragma unroll
+    for (int i = 0; i < VEC; i++) { my[i] = a[i]; my[VEC + i] = b[i]; }
+    __syncthreads();
+    if (rlane == 0 && g < groups) {
+      for (int j = 1; j < rstep; j++) {
+        const float* o = sm + (j * lanes + lane) * 2 * VEC;
+#pragma unroll
+        for (int i = 0; i < VEC; i++) { a[i] += o[i]; b[i] += o[VEC + i]; }
+      }
+#pragma unroll
+      for (int i = 0; i < VEC; i++)
+        if (c0 + i < C) { wsb[c0 + i] = a[i]; wsb[C + c0 + i] = b[i]; }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void chan_reduce_stage2(const float* __restrict__ ws, int nblocks, int C,
+                                   float* __restrict__ out0, float* __restrict__ out1) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double a = 0.0, b = 0.0;
+  for (int i = 0; i < nblocks; i++) { a += ws[(int64_t)i * 2 * C + c]; b += ws[(int64_t)i * 2 * C + C + c]; }
+  out0[c] = (float)a; out1[c] = (float)b;
+}
+
+static int reduce_blocks(int64_t rows) {
+  int64_t nb = (int64_t)num_sms() * kBlocksPerSM;
+  if (nb > rows) nb = rows;
+  return (int)(nb < 1 ? 1 : nb);
+}
+
+template <typename T, bool BWD>
+static int chan_reduce(const T* x, int64_t rows, int64_t C, BnBwdF<T> f, float* o0, float* o1, void* ws,
+                       size_t wsb, cudaStream_t st) {
+  const int nb = reduce_blocks(rows);
+  if (wsb < (size_t)nb * 2 * C * sizeof(float)) return B2C_ERR_WORKSPACE;
+  const int64_t rpb = cdiv(rows, nb);
+  constexpr int V = Vec<T>::N;
+  float* w = static_cast<float*>(ws);
+  bool vec_ok = (C % V == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+  if (BWD) vec_ok = vec_ok && ((reinterpret_cast<uintptr_t>(f.dy) & 15) == 0) &&
+                    (!f.res || (reinterpret_cast<uintptr_t>(f.res) & 15) == 0);
+  if (vec_ok)
+    chan_reduce_stage1<T, V, BWD><<<nb, kThreads, kThreads * 2 * V * sizeof(float), st>>>(x, rows, (int)C, f, w, rpb);
+  else
+    chan_reduce_stage1<T, 1, BWD><<<nb, kThreads, kThreads * 2 * sizeof(float), st>>>(x, rows, (int)C, f, w, rpb);
+  int rc = launched();
+  if (rc) return rc;
+  chan_reduce_stage2<<<(unsigned)cdiv(C, 256), 256, 0, st>>>(w, nb, (int)C, o0, o1);
+  return launched();
+}
+
+// ===========================================================================
+// BatchNorm finalize: tiny [C] kernel.
+// ===========================================================================
+__global__ void bn_finalize_kernel(const float* sum, const float* sq, double inv_count, double unbias, int C,
+                                   float eps, float mom, const float* gamma, const float* beta, float* mean,
+                                   float* invstd, float* scale, float* shift, float* rmean, float* rvar) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double m = (double)sum[c] * inv_count;
+  double var = (double)sq[c] * inv_count - m * m;
+  if (var < 0) var = 0;
+  double is = rsqrt(var + (double)eps);
+  double g = gamma ? (double)gamma[c] : 1.0, b = beta ? (double)beta[c] : 0.0;
+  mean[c] = (float)m; invstd[c] = (float)is;
+  scale[c] = (float)(g * is); shift[c] = (float)(b - m * g * is);
+  if (rmean) rmean[c] = (float)((1.0 - mom) * rmean[c] + mom * m);
+  if (rvar) rvar[c] = (float)((1.0 - mom) * rvar[c] + mom * var * unbias);
+}
+
+// ===========================================================================
+// Elementwise BN apply (+residual, +act) and backward apply.
+// ===========================================================================
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThreads)
+bn_act_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, const T* __restrict__ res, int64_t nvec, int C,
+                  const float* __restrict__ scale, const float* __restrict__ shift, int act, float slope) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const int64_t off = i * VEC;
+    const int c0 = (int)(off % C);
+    float xv[VEC], rv[VEC];
+    if (VEC > 1) {
+      Vec<T> v; v.load(x + off); v.unpack(xv);
+      if (res) { v.load(res + off); v.unpack(rv); }
+    } else { xv[0] = ldf(x, off); if (res) rv[0] = ldf(res, off); }
+#pragma unroll
+    for (int k = 0; k < VEC; k++) {
+      float z = xv[k] * scale[c0 + k] + shift[c0 + k];
+      if (res) z += rv[k];
+      xv[k] = act_f(z, act, slope);
+    }
+    if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(y + off); } else stf(y, off, xv[0]);
+  }
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThreads)
+bn_act_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ res,
+                  T* __restrict__ dx, T* __restrict__ dres, int64_t nvec, int C, float inv_rows,
+                  const float* __restrict__ mean, const float* __restrict__ invstd,
+                  const float* __restrict__ scale, const float* __restrict__ shift,
+                  const float* __restrict__ s1, const float* __restrict__ s2, int act, float slope) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const int64_t off = i * VEC;
+    const int c0 = (int)(off % C);
+    float xv[VEC], dv[VEC], rv[VEC], gv[VEC];
+    if (VEC > 1) {
+      Vec<T> v; v.load(x + off); v.unpack(xv); v.load(dy + off); v.unpack(dv);
+      if (res) { v.load(res + off); v.unpack(rv); }
+    } else { xv[0] = ldf(x, off); dv[0] = ldf(dy, off); if (res) rv[0] = ldf(res, off); }
+#pragma unroll
+    for (int k = 0; k < VEC; k++) {
+      const int c = c0 + k;
+      float z = xv[k] * scale[c] + shift[c];
+      if (res) z += rv[k];
+      float g = dv[k] * act_dz(z, act, slope);
+      float xh = (xv[k] - mean[c]) * invstd[c];
+      gv[k] = g;
+      xv[k] = scale[c] * (g - s1[c] * inv_rows - xh * s2[c] * inv_rows);
+    }
+    if (VEC > 1) {
+      Vec<T> v; v.pack(xv); v.store(dx + off);
+      if (dres) { v.pack(gv); v.store(dres + off); }
+    } else { stf(dx, off, xv[0]); if (dres) stf(dres, off, gv[0]); }
+  }
+}
+
+static unsigned ew_grid(int64_t nvec) {
+  int64_t nb = cdiv(nvec, kThreads), cap = (int64_t)num_sms() * 8;
+  return (unsigned)(nb < cap ? (nb < 1 ? 1 : nb) : cap);
+}
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <typename T>
+static int bn_fwd_t(const void* x, void* y, const void* res, int64_t rows, int64_t C, const float* scale,
+                    const float* shift, int act, float slope, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const int64_t n = rows * C;
+  if (n == 0) return B2C_OK;
+  const T* xp = static_cast<const T*>(x); T* yp = static_cast<T*>(y); const T* rp = static_cast<const T*>(res);
+  if (C % V == 0 && aligned16(x) && aligned16(y) && (!res || aligned16(res)))
+    bn_act_fwd_kernel<T, V><<<ew_grid(n / V), kThreads, 0, st>>>(xp, yp, rp, n / V, (int)C, scale, shift, act, slope);
+  else
+    bn_act_fwd_kernel<T, 1><<<ew_grid(n), kThreads, 0, st>>>(xp, yp, rp, n, (int)C, scale, shift, act, slope);
+  return launched();
+}
+
+template <typename T>
+static int bn_bwd_t(const void* x, const void* dy, const void* res, void* dx, void* dres, int64_t rows, int64_t C,
+                    const float* mean, const float* invstd, const float* scale, const float* shift,
+                    const float* s1, const float* s2, int act, float slope, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const int64_t n = rows * C;
+  if (n == 0) return B2C_OK;
+  const T* xp = static_cast<const T*>(x); const T* dp = static_cast<const T*>(dy);
+  const T* rp = static_cast<const T*>(res); T* dxp = static_cast<T*>(dx); T* drp = static_cast<T*>(dres);
+  const float inv = 1.0f / (float)rows;
+  if (C % V == 0 && aligned16(x) && aligned16(dy) && aligned16(dx) && (!res || aligned16(res)) &&
+      (!dres || aligned16(dres)))
+    bn_act_bwd_kernel<T, V><<<ew_grid(n / V), kThreads, 0, st>>>(xp, dp, rp, dxp, drp, n / V, (int)C, inv, mean,
+                                                                 invstd, scale, shift, s1, s2, act, slope);
+  else
+    bn_act_bwd_kernel<T, 1><<<ew_grid(n), kThreads, 0, st>>>(xp, dp, rp, dxp, drp, n, (int)C, inv, mean, invstd,
+                                                             scale, shift, s1, s2, act, slope);
+  return launched();
+}
+
+}  // namespace b2c
+
+namespace b2c {
+
+// ===========================================================================
+// Whole-sample LayerNorm (+activation).  x [N][L]; gamma/beta [L] fp32.
+// ===========================================================================
+__device__ __forceinline__ void block_sum2(float& a, float& b) {
+  __shared__ float sa[kThreads / 32], sb[kThreads / 32];
+  a = warp_sum(a); b = warp_sum(b);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) { sa[w] = a; sb[w] = b; }
+  __syncthreads();
+  if (w == 0) {
+    a = l < kThreads / 32 ? sa[l] : 0.f; b = l < kThreads / 32 ? sb[l] : 0.f;
+    a = warp_sum(a); b = warp_sum(b);
+  }
+  __syncthreads();
+}
+
+// grid (chunks, N).  FWD: (sum x, sum x^2).  BWD: (sum g, sum g*xhat), g = dy*act'(z)*gamma.
+template <typename T, int VEC, bool BWD>
+__global__ void __launch_bounds__(kThreads)
+ln_partial_kernel(const T* __restrict__ x, const T* __restrict__ dy, int64_t L, const float* __restrict__ gamma,
+                  const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd,
+                  int act, float slope, float* __restrict__ part) {
+  const int n = blockIdx.y;
+  const int64_t nvec = L / VEC;
+  const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
+  const int64_t v0 = (int64_t)blockIdx.x * per, v1 = v0 + per < nvec ? v0 + per : nvec;
+  const T* xs = x + (int64_t)n * L;
+  const T* ds = BWD ? dy + (int64_t)n * L : nullptr;
+  float mu = 0.f, rs = 0.f;
+  if (BWD) { mu = mean[n]; rs = rstd[n]; }
+  float a = 0.f, b = 0.f;
+  for (int64_t i = v0 + threadIdx.x; i < v1; i += kThreads) {
+    const int64_t off = i * VEC;
+    float xv[VEC], dv[VEC];
+    if (VEC > 1) { Vec<T> v; v.load(xs + off); v.unpack(xv); if (BWD) { v.load(ds + off); v.unpack(dv); } }
+    else { xv[0] = ldf(xs, off); if (BWD) dv[0] = ldf(ds, off); }
+#pragma unroll
+    for (int k = 0; k < VEC; k++) {
+      if (BWD) {
+        float ga = gamma ? gamma[off + k] : 1.f, be = beta ? beta[off + k] : 0.f;
+        float xh = (xv[k] - mu) * rs;
+        float g = dv[k] * act_dz(xh * ga + be, act, slope) * ga;
+        a += g; b += g * xh;
+      } else { a += xv[k]; b += xv[k] * xv[k]; }
+    }
+  }
+  block_sum2(a, b);
+  if (threadIdx.x == 0) {
+    part[((int64_t)n * gridDim.x + blockIdx.x) * 2] = a;
+    part[((int64_t)n * gridDim.x + blockIdx.x) * 2 + 1] = b;
+  }
+}
+
+// one thread per sample; chunks is a few hundred at most.
+__global__ void ln_finalize_kernel(const float* part, int chunks, int N, double invL, float eps, int bwd,
+                                   float* o0, float* o1) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  double a = 0, b = 0;
+  for (int i = 0; i < chunks; i++) { a += part[((int64_t)n * chunks + i) * 2]; b += part[((int64_t)n * chunks + i) * 2 + 1]; }
+  if (bwd) { o0[n] = (float)(a * invL); o1[n] = (float)(b * invL); }   // mean(g), mean(g*xhat)
+  else {
+    double m = a * invL, var = b * invL - m * m;
+    if (var < 0) var = 0;
+    o0[n] = (float)m; o1[n] = (float)rsqrt(var + (double)eps);
+  }
+}
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThreads)
+ln_apply_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t L, int64_t nvec_total,
+                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ mean, const float* __restrict__ rstd, int act, float slope) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec_total; i += stride) {
+    const int64_t off = i * VEC;
+    const int n = (int)(off / L);
+    const int64_t e = off - (int64_t)n * L;
+    const float mu = mean[n], rs = rstd[n];
+    float xv[VEC];
+    if (VEC > 1) { Vec<T> v; v.load(x + off); v.unpack(xv); } else xv[0] = ldf(x, off);
+#pragma unroll
+    for (int k = 0; k < VEC; k++) {
+      float z = (xv[k] - mu) * rs;
+      z = z * (gamma ? gamma[e + k] : 1.f) + (beta ? beta[e + k] : 0.f);
+      xv[k] = act_f(z, act, slope);
+    }
+    if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(y + off); } else stf(y, off, xv[0]);
+  }
+}
+
+// Thread owns VEC adjacent elements e and walks the batch: dx per sample and
+// the full-shape affine gradients dgamma[e], dbeta[e] without atomics.
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThreads)
+ln_apply_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __restrict__ dx, int N, int64_t L,
+                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                    const float* __restrict__ mg, const float* __restrict__ mgx, int act, float slope,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int64_t nvec = L / VEC;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const int64_t e = i * VEC;
+    float ga[VEC], be[VEC], dg[VEC], db[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; k++) {
+      ga[k] = gamma ? gamma[e + k] : 1.f; be[k] = beta ? beta[e + k] : 0.f; dg[k] = db[k] = 0.f;
+    }
+    for (int n = 0; n < N; n++) {
+      const int64_t off = (int64_t)n * L + e;
+      const float mu = mean[n], rs = rstd[n], a = mg[n], b = mgx[n];
+      float xv[VEC], dv[VEC];
+      if (VEC > 1) { Vec<T> v; v.load(x + off); v.unpack(xv); v.load(dy + off); v.unpack(dv); }
+      else { xv[0] = ldf(x, off); dv[0] = ldf(dy, off); }
+#pragma unroll
+      for (int k = 0; k < VEC; k++) {
+        float xh = (xv[k] - mu) * rs;
+        float g0 = dv[k] * act_dz(xh * ga[k] + be[k], act, slope);
+        dg[k] += g0 * xh; db[k] += g0;
+        xv[k] = rs * (g0 * ga[k] - a - xh * b);
+      }
+      if (dx) { if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(dx + off); } else stf(dx, off, xv[0]); }
+    }
+#pragma unroll
+    for (int k = 0; k < VEC; k++) { if (dgamma) dgamma[e + k] = dg[k]; if (dbeta) dbeta[e + k] = db[k]; }
+  }
+}
+
+static int ln_chunks(int64_t N, int64_t L) {
+  int64_t want = cdiv((int64_t)num_sms() * kBlocksPerSM, N);
+  int64_t maxc = cdiv(L, (int64_t)kThreads * 8);
+  if (want > maxc) want = maxc;
+  return (int)(want < 1 ? 1 : want);
+}
+
+template <typename T>
+static int ln_fwd_t(const void* x, void* y, int64_t N, int64_t L, const float* gamma, const float* beta, float eps,
+                    int act, float slope, float* mean, float* rstd, void* ws, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const T* xp = static_cast<const T*>(x); T* yp = static_cast<T*>(y);
+  const int chunks = ln_chunks(N, L);
+  float* part = static_cast<float*>(ws);
+  const bool vec = (L % V == 0) && aligned16(x) && aligned16(y);
+  dim3 grid(chunks, (unsigned)N);
+  if (vec) ln_partial_kernel<T, V, false><<<grid, kThreads, 0, st>>>(xp, nullptr, L, nullptr, nullptr, nullptr, nullptr, 0, 0.f, part);
+  else     ln_partial_kernel<T, 1, false><<<grid, kThreads, 0, st>>>(xp, nullptr, L, nullptr, nullptr, nullptr, nullptr, 0, 0.f, part);
+  int rc = launched(); if (rc) return rc;
+  ln_finalize_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(part, chunks, (int)N, 1.0 / (double)L, eps, 0, mean, rstd);
+  rc = launched(); if (rc) return rc;
+  const int64_t tot = N * L;
+  if (vec) ln_apply_fwd_kernel<T, V><<<ew_grid(tot / V), kThreads, 0, st>>>(xp, yp, L, tot / V, gamma, beta, mean, rstd, act, slope);
+  else     ln_apply_fwd_kernel<T, 1><<<ew_grid(tot), kThreads, 0, st>>>(xp, yp, L, tot, gamma, beta, mean, rstd, act, slope);
+  return launched();
+}
+
+template <typename T>
+static int ln_bwd_t(const void* x, const void* dy, void* dx, int64_t N, int64_t L, const float* gamma,
+                    const float* beta, const float* mean, const float* rstd, int act, float slope, float* dgamma,
+                    float* dbeta, void* ws, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const T* xp = static_cast<const T*>(x); const T* dp = static_cast<const T*>(dy); T* dxp = static_cast<T*>(dx);
+  const int chunks = ln_chunks(N, L);
+  float* part = static_cast<float*>(ws);
+  float* mg = part + (size_t)N * chunks * 2;
+  float* mgx = mg + N;
+  const bool vec = (L % V == 0) && aligned16(x) && aligned16(dy) && (!dx || aligned16(dx));
+  dim3 grid(chunks, (unsigned)N);
+  if (vec) ln_partial_kernel<T, V, true><<<grid, kThreads, 0, st>>>(xp, dp, L, gamma, beta, mean, rstd, act, slope, part);
+  else     ln_partial_kernel<T, 1, true><<<grid, kThreads, 0, st>>>(xp, dp, L, gamma, beta, mean, rstd, act, slope, part);
+  int rc = launched(); if (rc) return rc;
+  ln_finalize_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(part, chunks, (int)N, 1.0 / (double)L, 0.f, 1, mg, mgx);
+  rc = launched(); if (rc) return rc;
+  if (vec) ln_apply_bwd_kernel<T, V><<<ew_grid(L / V), kThreads, 0, st>>>(xp, dp, dxp, (int)N, L, gamma, beta, mean, rstd, mg, mgx, act, slope, dgamma, dbeta);
+  else     ln_apply_bwd_kernel<T, 1><<<ew_grid(L), kThreads, 0, st>>>(xp, dp, dxp, (int)N, L, gamma, beta, mean, rstd, mg, mgx, act, slope, dgamma, dbeta);
+  return launched();
+}
+
+// ===========================================================================
+// Pointwise activation fwd / bwd (bwd from the output).
+// ===========================================================================
+template <typename T, int VEC, bool BWD>
+__global__ void __launch_bounds__(kThreads)
+act_kernel(const T* __restrict__ a, const T* __restrict__ dy, T* __restrict__ out, int64_t nvec, int act, float slope) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const int64_t off = i * VEC;
+    float av[VEC], dv[VEC];
+    if (VEC > 1) { Vec<T> v; v.load(a + off); v.unpack(av); if (BWD) { v.load(dy + off); v.unpack(dv); } }
+    else { av[0] = ldf(a, off); if (BWD) dv[0] = ldf(dy, off); }
+#pragma unroll
+    for (int k = 0; k < VEC; k++) av[k] = BWD ? dv[k] * act_dy(av[k], act, slope) : act_f(av[k], act, slope);
+    if (VEC > 1) { Vec<T> v; v.pack(av); v.store(out + off); } else stf(out, off, av[0]);
+  }
+}
+
+template <typename T, bool BWD>
+static int act_t(const void* a, const void* dy, void* out, int64_t n, int act, float slope, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  if (n == 0) return B2C_OK;
+  const T* ap = static_cast<const T*>(a); const T* dp = static_cast<const T*>(dy); T* op = static_cast<T*>(out);
+  const int64_t nv = n / V, tail = n - nv * V;
+  const bool vec = aligned16(a) && aligned16(out) && (!BWD || aligned16(dy));
+  if (vec && nv > 0) {
+    act_kernel<T, V, BWD><<<ew_grid(nv), kThreads, 0, st>>>(ap, dp, op, nv, act, slope);
+    int rc = launched(); if (rc) return rc;
+    if (tail) {
+      act_kernel<T, 1, BWD><<<1, kThreads, 0, st>>>(ap + nv * V, BWD ? dp + nv * V : nullptr, op + nv * V, tail, act, slope);
+      return launched();
+    }
+    return B2C_OK;
+  }
+  act_kernel<T, 1, BWD><<<ew_grid(n), kThreads, 0, st>>>(ap, dp, op, n, act, slope);
+  return launched();
+}
+
+}  // namespace b2c
+
+using namespace b2c;
+
+extern "C" size_t b2c_stats_workspace(int64_t rows, int64_t C) {
+  if (rows <= 0 || C <= 0) return 0;
+  return (size_t)reduce_blocks(rows) * 2 * C * sizeof(float);
+}
+
+extern "C" int b2c_channel_stats(const void* x, int64_t rows, int64_t C, int dt, float* sum, float* sq, void* ws,
+                                 size_t wsb, b2c_stream s) {
+  if (!x || !sum || !sq || !ws || !dt_ok(dt) || rows <= 0 || C <= 0 || C > 0x7fffffff) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (dt == B2C_BF16) {
+    BnBwdF<__nv_bfloat16> f{};
+    return chan_reduce<__nv_bfloat16, false>(static_cast<const __nv_bfloat16*>(x), rows, C, f, sum, sq, ws, wsb, st);
+  }
+  BnBwdF<float> f{};
+  return chan_reduce<float, false>(static_cast<const float*>(x), rows, C, f, sum, sq, ws, wsb, st);
+}
+
+extern "C" int b2c_bn_finalize(const float* sum, const float* sq, int64_t count, int64_t C, float eps, float momentum,
+                               const float* gamma, const float* beta, float* mean, float* invstd, float* scale,
+                               float* shift, float* rmean, float* rvar, b2c_stream s) {
+  if (!sum || !sq || !mean || !invstd || !scale || !shift || count <= 0 || C <= 0) return B2C_ERR_INVALID;
+  const double unbias = count > 1 ? (double)count / (double)(count - 1) : 1.0;
+  bn_finalize_kernel<<<(unsigned)cdiv(C, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      sum, sq, 1.0 / (double)count, unbias, (int)C, eps, momentum, gamma, beta, mean, invstd, scale, shift, rmean, rvar);
+  return launched();
+}
+
+extern "C" int b2c_bn_act_fwd(const void* x, void* y, const void* res, int64_t rows, int64_t C, int dt,
+                              const float* scale, const float* shift, int act, float slope, b2c_stream s) {
+  if (!x || !y || !scale || !shift || !dt_ok(dt) || rows < 0 || C <= 0) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? bn_fwd_t<__nv_bfloat16>(x, y, res, rows, C, scale, shift, act, slope, st)
+                        : bn_fwd_t<float>(x, y, res, rows, C, scale, shift, act, slope, st);
+}
+
+extern "C" int b2c_bn_act_bwd_reduce(const void* x, const void* dy, const void* res, int64_t rows, int64_t C, int dt,
+                                     const float* mean, const float* invstd, const float* scale, const float* shift,
+                                     int act, float slope, float* s1, float* s2, void* ws, size_t wsb, b2c_stream s) {
+  if (!x || !dy || !mean || !invstd || !scale || !shift || !s1 || !s2 || !ws || !dt_ok(dt) || rows <= 0 || C <= 0)
+    return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (dt == B2C_BF16) {
+    BnBwdF<__nv_bfloat16> f{static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(res),
+                            mean, invstd, scale, shift, act, slope};
+    return chan_reduce<__nv_bfloat16, true>(static_cast<const __nv_bfloat16*>(x), rows, C, f, s1, s2, ws, wsb, st);
+  }
+  BnBwdF<float> f{static_cast<const float*>(dy), static_cast<const float*>(res), mean, invstd, scale, shift, act, slope};
+  return chan_reduce<float, true>(static_cast<const float*>(x), rows, C, f, s1, s2, ws, wsb, st);
+}
+
+extern "C" int b2c_bn_act_bwd_apply(const void* x, const void* dy, const void* res, void* dx, void* dres, int64_t rows,
+                                    int64_t C, int dt, const float* mean, const float* invstd, const float* scale,
+                                    const float* shift, const float* s1, const float* s2, int act, float slope,
+                                    b2c_stream s) {
+  if (!x || !dy || !dx || !mean || !invstd || !scale || !shift || !s1 || !s2 || !dt_ok(dt) || rows <= 0 || C <= 0)
+    return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16
+             ? bn_bwd_t<__nv_bfloat16>(x, dy, res, dx, dres, rows, C, mean, invstd, scale, shift, s1, s2, act, slope, st)
+             : bn_bwd_t<float>(x, dy, res, dx, dres, rows, C, mean, invstd, scale, shift, s1, s2, act, slope, st);
+}
+
+extern "C" size_t b2c_ln_workspace(int64_t N, int64_t L) {
+  if (N <= 0 || L <= 0) return 0;
+  return ((size_t)N * ln_chunks(N, L) * 2 + 2 * (size_t)N) * sizeof(float);
+}
+
+extern "C" int b2c_ln_act_fwd(const void* x, void* y, int64_t N, int64_t L, int dt, const float* gamma,
+                              const float* beta, float eps, int act, float slope, float* mean, float* rstd, void* ws,
+                              size_t wsb, b2c_stream s) {
+  if (!x || !y || !mean || !rstd || !ws || !dt_ok(dt) || N <= 0 || L <= 0 || N > 65535) return B2C_ERR_INVALID;
+  if (wsb < b2c_ln_workspace(N, L)) return B2C_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? ln_fwd_t<__nv_bfloat16>(x, y, N, L, gamma, beta, eps, act, slope, mean, rstd, ws, st)
+                        : ln_fwd_t<float>(x, y, N, L, gamma, beta, eps, act, slope, mean, rstd, ws, st);
+}
+
+extern "C" int b2c_ln_act_bwd(const void* x, const void* dy, void* dx, int64_t N, int64_t L, int dt,
+                              const float* gamma, const float* beta, const float* mean, const float* rstd, int act,
+                              float slope, float* dgamma, float* dbeta, void* ws, size_t wsb, b2c_stream s) {
+  if (!x || !dy || !mean || !rstd || !ws || !dt_ok(dt) || N <= 0 || L <= 0 || N > 65535) return B2C_ERR_INVALID;
+  if (wsb < b2c_ln_workspace(N, L)) return B2C_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16
+             ? ln_bwd_t<__nv_bfloat16>(x, dy, dx, N, L, gamma, beta, mean, rstd, act, slope, dgamma, dbeta, ws, st)
+             : ln_bwd_t<float>(x, dy, dx, N, L, gamma, beta, mean, rstd, act, slope, dgamma, dbeta, ws, st);
+}
+
+extern "C" int b2c_act_fwd(const void* x, void* y, int64_t n, int dt, int act, float slope, b2c_stream s) {
+  if (!x || !y || !dt_ok(dt) || n < 0) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? act_t<__nv_bfloat16, false>(x, nullptr, y, n, act, slope, st)
+                        : act_t<float, false>(x, nullptr, y, n, act, slope, st);
+}
+
+extern "C" int b2c_act_bwd(const void* y, const void* dy, void* dx, int64_t n, int dt, int act, float slope,
+                           b2c_stream s) {
+  if (!y || !dy || !dx || !dt_ok(dt) || n < 0) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? act_t<__nv_bfloat16, true>(y, dy, dx, n, act, slope, st)
+                        : act_t<float, true>(y, dy, dx, n, act, slope, st);
+}

@@ -1,0 +1,17 @@
+// tc_conv.cuh — host interface of the tcgen05 kernels (tc_conv.cu).
+#pragma once
+#include "common.cuh"
+#include "tc_plan.h"
+
+namespace b2c {
+// out = plan(in, w_packed); bf16 I/O, fp32 accumulate in TMEM.
+int tc_conv_launch(const ConvPlan& p, const void* in, const void* w_packed, void* out, const float* bias, int bias_mod,
+                   int act, float slope, cudaStream_t st);
+// dW[a][b][t] (torch layout, fp32) = sum small[v,a] * big[v*s+k*dl-p, b]; split-K through `ws`.
+bool tc_wgrad_supported(const Geo& g);
+size_t tc_wgrad_workspace(const Geo& g);
+int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw, void* ws, size_t wsb,
+                    cudaStream_t st);
+// Sticky device error word of the tensor-core kernels (synchronises the device).
+unsigned tc_error_fetch_clear();
+}  // namespace b2c
