@@ -1,0 +1,120 @@
+"""GPU parity at the nn.Module boundary: drop-in layers on cuda:0 vs the stock
+torch layers (the reference's own arithmetic) in fp32 on the
+CPU with the same state_dict and inputs.  fp32 <= 1e-4, bf16 <= 2e-2."""
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+import b200conv3d as B
+from abi import rel_err
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _pair(make):
+    torch.manual_seed(3)
+    ref = make(nn)
+    ours = make(B.nn)
+    ours.load_state_dict(ref.state_dict())
+    return ref, ours.to(DEV)
+
+
+def _check(ref, ours, x, tol, autocast=False, params=True):
+    xr = x.clone().requires_grad_(True)
+    xo = x.clone().to(DEV).requires_grad_(True)
+    yr = ref(xr)
+    if autocast:
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            yo = ours(xo)
+    else:
+        yo = ours(xo)
+    assert yo.shape == yr.shape
+    assert rel_err(yo.float(), yr) < tol, "forward"
+    g = torch.randn_like(yr)
+    yr.backward(g)
+    yo.backward(g.to(DEV).to(yo.dtype))
+    assert rel_err(xo.grad, xr.grad) < tol, "dx"
+    if params:
+        for (n1, p1), (_, p2) in zip(ref.named_parameters(), ours.named_parameters()):
+            assert p2.grad is not None, n1
+            assert rel_err(p2.grad, p1.grad) < tol, n1
+
+
+@pytest.mark.parametrize("autocast,tol", [(False, 1e-4), (True, 2e-2)])
+def test_batchnorm_relu(autocast, tol):
+    ref, ours = _pair(lambda m: nn.Sequential(m.BatchNorm3d(32), m.ReLU(True)))
+    with torch.no_grad():
+        ref[0].weight.normal_(1, 0.2); ref[0].bias.normal_(0, 0.2)
+        ours.load_state_dict(ref.state_dict())
+    B.fuse(ours)
+    x = torch.randn(3, 32, 6, 5, 4) * 2 + 0.5
+    _check(ref, ours, x, tol, autocast)
+    assert rel_err(ours[0].running_mean, ref[0].running_mean) < 1e-3
+    assert rel_err(ours[0].running_var, ref[0].running_var) < 1e-3
+    assert int(ours[0].num_batches_tracked) == 1
+
+
+@pytest.mark.parametrize("autocast,tol", [(False, 1e-4), (True, 2e-2)])
+def test_layernorm_lrelu(autocast, tol):
+    ref, ours = _pair(lambda m: nn.Sequential(m.LayerNorm([16, 4, 6, 8]), m.LeakyReLU(0.2, inplace=True)))
+    with torch.no_grad():
+        ref[0].weight.normal_(1, 0.2); ref[0].bias.normal_(0, 0.2)
+        ours.load_state_dict(ref.state_dict())
+    B.fuse(ours)
+    _check(ref, ours, torch.randn(5, 16, 4, 6, 8) * 1.5 + 0.3, tol, autocast)
+
+
+def test_unfused_activation_modules():
+    for make in (lambda m: m.ReLU(), lambda m: m.LeakyReLU(0.1), lambda m: m.Tanh()):
+        ref, ours = make(nn), make(B.nn)
+        x = torch.randn(2, 8, 4, 4, 4)
+        _check(ref, ours, x, 1e-5, params=False)
+    # in-place on a channels_last_3d tensor produced by our conv
+    conv = B.nn.Conv3d(8, 16, 3, 1, 1).to(DEV)
+    y = conv(x.to(DEV))
+    z = B.nn.LeakyReLU(0.2, inplace=True)(y)
+    assert z.data_ptr() == y.data_ptr()
+
+
+@pytest.mark.parametrize("autocast,tol", [(False, 1e-4), (True, 2e-2)])
+def test_dcgan_generator_slice(autocast, tol):
+    """dcgan.py:45-70 at reduced width: ConvT(z) BN ReLU, ConvT s2 BN ReLU, ConvT->1 Tanh."""
+    def make(m):
+        return nn.Sequential(m.ConvTranspose3d(32, 128, 4, stride=1), m.BatchNorm3d(128), m.ReLU(True),
+                             m.ConvTranspose3d(128, 64, 4, stride=2, padding=1), m.BatchNorm3d(64), m.ReLU(True),
+                             m.ConvTranspose3d(64, 1, 4, stride=2, padding=1), m.Tanh())
+    ref, ours = _pair(make)
+    B.fuse(ours)
+    _check(ref, ours, torch.randn(4, 32, 1, 1, 1), tol if not autocast else 4e-2, autocast)
+
+
+@pytest.mark.parametrize("autocast,tol", [(False, 1e-4), (True, 2e-2)])
+def test_dcgan_discriminator_slice(autocast, tol):
+    """dcgan.py:158-182 at reduced width and 16^3 input."""
+    def make(m):
+        return nn.Sequential(m.Conv3d(1, 64, 4, stride=2, padding=1, bias=False), m.LayerNorm([64, 8, 8, 8]),
+                             m.LeakyReLU(0.2, inplace=True),
+                             m.Conv3d(64, 128, 4, stride=2, padding=1, bias=False), m.LayerNorm([128, 4, 4, 4]),
+                             m.LeakyReLU(0.2, inplace=True),
+                             m.Conv3d(128, 1, (4, 4, 4), stride=1, padding=0, bias=False))
+    ref, ours = _pair(make)
+    B.fuse(ours)
+    _check(ref, ours, torch.rand(4, 1, 16, 16, 16) * 2 - 1, tol if not autocast else 4e-2, autocast)
+
+
+def test_frozen_parameters_skip_wgrad():
+    """trainer.py:249-256: with D frozen only dgrad runs, no parameter grads."""
+    conv = B.nn.Conv3d(64, 64, 3, 1, 1).to(DEV)
+    for p in conv.parameters():
+        p.requires_grad = False
+    x = torch.randn(2, 64, 4, 4, 4, device=DEV, requires_grad=True)
+    conv(x).sum().backward()
+    assert x.grad is not None and all(p.grad is None for p in conv.parameters())
+
+
+def test_cpu_tensor_fails_loudly():
+    conv = B.nn.Conv3d(4, 4, 3)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        conv(torch.randn(1, 4, 5, 5, 5))
