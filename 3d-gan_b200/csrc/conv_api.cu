@@ -3,6 +3,7 @@
 // (fp32, or shapes the tensor-core path does not take).
 #include "direct_conv.cuh"
 #include "tc_conv.cuh"
+#include "thin.cuh"
 
 using namespace b2c;
 
@@ -23,8 +24,13 @@ bool is_point_convT(const b2c_conv_desc* c) {
 }
 
 int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w, void* out, const float* bias,
-             int act, float slope, cudaStream_t st) {
+             int act, float slope, void* ws, size_t wsb, cudaStream_t st) {
   const Geo g = make_geo(c);
+  if (thin_applicable(c, g)) {
+    t_last_algo = B2C_ALGO_TC;
+    return scatter ? thin_scatter(g, in, w, out, bias, act, slope, ws, wsb, st)
+                   : thin_gather(g, in, w, out, bias, act, slope, ws, wsb, st);
+  }
   if (tc_allowed(c)) {
     ConvPlan plan;
     int rc;
@@ -57,13 +63,18 @@ int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w
 
 extern "C" size_t b2c_conv3d_workspace(const b2c_conv_desc* c, int pass) {
   if (check_desc(c)) return 0;
-  if (pass == B2C_PASS_WGRAD && tc_allowed(c)) return tc_wgrad_workspace(make_geo(c));
+  const Geo g = make_geo(c);
+  if (thin_applicable(c, g)) {
+    if (pass == B2C_PASS_WGRAD) return thin_workspace(g, 2);
+    const bool scatter = (pass == B2C_PASS_FWD) == (c->transposed != 0);
+    return thin_workspace(g, scatter ? 1 : 0);
+  }
+  if (pass == B2C_PASS_WGRAD && tc_allowed(c)) return tc_wgrad_workspace(g);
   return 0;
 }
 
 extern "C" int b2c_conv3d_fwd(const b2c_conv_desc* c, const void* x, const void* wp, void* y, const b2c_fusion* f,
                               void* ws, size_t wsb, b2c_stream s) {
-  (void)ws; (void)wsb;
   int rc = check_desc(c);
   if (rc) return rc;
   if (!x || !wp || !y) return B2C_ERR_INVALID;
@@ -71,21 +82,23 @@ extern "C" int b2c_conv3d_fwd(const b2c_conv_desc* c, const void* x, const void*
   const int act = f ? f->act : B2C_ACT_NONE;
   const float slope = f ? f->slope : 0.f;
   if (act < B2C_ACT_NONE || act > B2C_ACT_TANH) return B2C_ERR_INVALID;
-  return fwd_like(c, c->transposed != 0, x, wp, y, bias, act, slope, static_cast<cudaStream_t>(s));
+  return fwd_like(c, c->transposed != 0, x, wp, y, bias, act, slope, ws, wsb, static_cast<cudaStream_t>(s));
 }
 
 extern "C" int b2c_conv3d_dgrad(const b2c_conv_desc* c, const void* dy, const void* wp, void* dx, void* ws,
                                 size_t wsb, b2c_stream s) {
-  (void)ws; (void)wsb;
   int rc = check_desc(c);
   if (rc) return rc;
   if (!dy || !wp || !dx) return B2C_ERR_INVALID;
   // dgrad of a conv is the scatter form; dgrad of a convT is the gather form.
-  b2c_conv_desc d = *c;
-  // fwd_like() reads geometry only through make_geo(), which is pass-independent.
-  const Geo g = make_geo(&d);
+  const Geo g = make_geo(c);
   const bool scatter = !c->transposed;
   cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (thin_applicable(c, g)) {
+    t_last_algo = B2C_ALGO_TC;
+    return scatter ? thin_scatter(g, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, ws, wsb, st)
+                   : thin_gather(g, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, ws, wsb, st);
+  }
   if (tc_allowed(c)) {
     ConvPlan plan;
     rc = scatter ? plan_scatter(g, &plan) : plan_gather(g, &plan);
@@ -113,7 +126,12 @@ extern "C" int b2c_conv3d_wgrad(const b2c_conv_desc* c, const void* x, const voi
   const void* big = c->transposed ? dy : x;
   if (dw) {
     bool done = false;
-    if (tc_allowed(c) && tc_wgrad_supported(g)) {
+    if (thin_applicable(c, g)) {
+      t_last_algo = B2C_ALGO_TC;
+      rc = thin_wgrad(g, small, big, dw, ws, wsb, st);
+      if (rc) return rc;
+      done = true;
+    } else if (tc_allowed(c) && tc_wgrad_supported(g)) {
       t_last_algo = B2C_ALGO_TC;
       rc = tc_wgrad_launch(g, small, big, dw, ws, wsb, st);
       if (rc) return rc;

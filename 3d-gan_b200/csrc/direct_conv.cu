@@ -92,6 +92,43 @@ scatter_kernel(Geo g, const T* __restrict__ in, const T* __restrict__ w, T* __re
   stf(out, idx, act_f(acc, act, slope));
 }
 
+// BLOCK variant of the gather: one 256-thread block per output element, threads
+// stride the flattened (tap, ci) reduction (ci fastest -> coalesced).  For heads
+// with few outputs and a very long K (dcgan.py:181: Conv3d(2048->1, k4) on 4^3).
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_block_kernel(Geo g, const T* __restrict__ in, const T* __restrict__ w, T* __restrict__ out,
+                    const float* __restrict__ bias, int act, float slope) {
+  __shared__ float red[8];
+  const int64_t idx = blockIdx.x;
+  const int co = (int)(idx % g.sc);
+  int n, od, oh, ow;
+  decode_vox(idx / g.sc, g.sd, g.sh, g.sw, n, od, oh, ow);
+  const int T_ = g.taps();
+  const int64_t K = (int64_t)T_ * g.bc;
+  float acc = 0.f;
+  for (int64_t j = threadIdx.x; j < K; j += 256) {
+    const int t = (int)(j / g.bc), ci = (int)(j - (int64_t)t * g.bc);
+    const int kw = t % g.k[2], kh = (t / g.k[2]) % g.k[1], kd = t / (g.k[2] * g.k[1]);
+    const int id = od * g.s[0] + kd * g.dl[0] - g.p[0];
+    const int ih = oh * g.s[1] + kh * g.dl[1] - g.p[1];
+    const int iw = ow * g.s[2] + kw * g.dl[2] - g.p[2];
+    if (id < 0 || id >= g.bd || ih < 0 || ih >= g.bh || iw < 0 || iw >= g.bw) continue;
+    acc += ldf(in, ((((int64_t)n * g.bd + id) * g.bh + ih) * g.bw + iw) * g.bc + ci) *
+           ldf(w, ((int64_t)t * g.sc + co) * g.bc + ci);
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += red[i];
+    if (bias) s += bias[co];
+    stf(out, idx, act_f(s, act, slope));
+  }
+}
+
 template <typename T>
 static int launch_fwdlike(bool scatter, const Geo& g, const void* in, const void* w, void* out, const float* bias,
                           int act, float slope, cudaStream_t st) {
@@ -104,6 +141,10 @@ static int launch_fwdlike(bool scatter, const Geo& g, const void* in, const void
   const int64_t blocks = cdiv(threads, 256);
   if (blocks > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
   const T* ip = static_cast<const T*>(in); const T* wp = static_cast<const T*>(w); T* op = static_cast<T*>(out);
+  if (!scatter && total <= 4096 && (int64_t)g.taps() * ic >= 8192) {
+    gather_block_kernel<T><<<(unsigned)total, 256, 0, st>>>(g, ip, wp, op, bias, act, slope);
+    return launched();
+  }
   if (scatter) {
     if (warp) scatter_kernel<T, true><<<(unsigned)blocks, 256, 0, st>>>(g, ip, wp, op, bias, act, slope, total);
     else      scatter_kernel<T, false><<<(unsigned)blocks, 256, 0, st>>>(g, ip, wp, op, bias, act, slope, total);

@@ -1,6 +1,7 @@
 // pack.cu — filter re-packing, layout transposition and dtype casts.
 // All HBM-bound: coalesced reads AND writes through a padded shared tile.
 #include "common.cuh"
+#include "thin.cuh"
 
 namespace b2c {
 
@@ -138,6 +139,8 @@ extern "C" int b2c_cast(const void* src, void* dst, int64_t n, int sdt, int ddt,
 extern "C" size_t b2c_filter_packed_bytes(const b2c_conv_desc* c, int pass) {
   (void)pass;
   if (check_desc(c)) return 0;
+  const Geo g = make_geo(c);
+  if (thin_applicable(c, g)) return thin_packed_bytes(g);
   return (size_t)c->k[0] * c->k[1] * c->k[2] * c->x.c * c->y.c * esize(c->io_dtype);
 }
 
@@ -151,6 +154,8 @@ extern "C" int b2c_filter_pack(const b2c_conv_desc* c, int pass, const float* w,
   // conv fwd / convT dgrad produce torch-dim-0 channels; the other two dim 1
   const bool out_is_A = (pass == B2C_PASS_FWD) != (c->transposed != 0);
   cudaStream_t st = static_cast<cudaStream_t>(s);
+  const Geo g = make_geo(c);
+  if (thin_applicable(c, g)) return thin_pack(g, /*gather=*/out_is_A, w, wp, st);
   if (c->io_dtype == B2C_BF16) return pack_launch<__nv_bfloat16>(w, wp, A, B, T, out_is_A, st);
   return pack_launch<float>(w, wp, A, B, T, out_is_A, st);
 }

@@ -1,0 +1,231 @@
+// thin.cu — see thin.cuh.
+#include "thin.cuh"
+
+#include "tc_conv.cuh"
+
+namespace b2c {
+
+typedef __nv_bfloat16 bf16;
+
+// ---------------------------------------------------------------------------
+// im2col of a 1-channel tensor: col[v][t] = big[n, o*s + k*dl - p] (0 outside),
+// t = (kd*k1 + kh)*k2 + kw, zero for t in [T, Kp).  One thread per (v, kd): it
+// produces the k1*k2 taps of one kd plane, contiguous in the col row, so a warp
+// writes whole 128-byte lines.  KHW > 0: compile-time plane size with 16-byte
+// stores (k1*k2 % 8 == 0); KHW == 0: any size, scalar stores.
+template <int KHW>
+__global__ void __launch_bounds__(256)
+im2col1_kernel(Geo g, const bf16* __restrict__ big, bf16* __restrict__ col, int Kp, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int kd = (int)(idx % g.k[0]);
+  int64_t v = idx / g.k[0];
+  const int64_t row = v;
+  const int ow = (int)(v % g.sw); v /= g.sw;
+  const int oh = (int)(v % g.sh); v /= g.sh;
+  const int od = (int)(v % g.sd);
+  const int n = (int)(v / g.sd);
+  const int khw = g.k[1] * g.k[2];
+  bf16* dst = col + row * Kp + (int64_t)kd * khw;
+  const int id = od * g.s[0] + kd * g.dl[0] - g.p[0];
+  const bool dok = id >= 0 && id < g.bd;
+  const bf16* plane = big + ((int64_t)n * g.bd + (dok ? id : 0)) * g.bh * g.bw;
+  const int ih0 = oh * g.s[1] - g.p[1], iw0 = ow * g.s[2] - g.p[2];
+  const bf16 zero = __float2bfloat16_rn(0.f);
+  if (KHW > 0) {
+    __align__(16) bf16 buf[KHW > 0 ? KHW : 8];
+    int j = 0;
+    for (int kh = 0; kh < g.k[1]; kh++) {
+      const int ih = ih0 + kh * g.dl[1];
+      const bool hok = dok && ih >= 0 && ih < g.bh;
+      const bf16* rowp = plane + (int64_t)(hok ? ih : 0) * g.bw;
+#pragma unroll 4
+      for (int kw = 0; kw < g.k[2]; kw++, j++) {
+        const int iw = iw0 + kw * g.dl[2];
+        buf[j < KHW ? j : 0] = (hok && iw >= 0 && iw < g.bw) ? rowp[iw] : zero;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < KHW / 8; q++)
+      reinterpret_cast<uint4*>(dst)[q] = reinterpret_cast<const uint4*>(buf)[q];
+  } else {
+    int j = 0;
+    for (int kh = 0; kh < g.k[1]; kh++) {
+      const int ih = ih0 + kh * g.dl[1];
+      const bool hok = dok && ih >= 0 && ih < g.bh;
+      const bf16* rowp = plane + (int64_t)(hok ? ih : 0) * g.bw;
+      for (int kw = 0; kw < g.k[2]; kw++, j++) {
+        const int iw = iw0 + kw * g.dl[2];
+        dst[j] = (hok && iw >= 0 && iw < g.bw) ? rowp[iw] : zero;
+      }
+    }
+  }
+  if (kd == 0) {
+    bf16* r = col + row * Kp;
+    for (int t = g.k[0] * khw; t < Kp; t++) r[t] = zero;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// col2im onto a 1-channel tensor (a gather over the taps that divide):
+//   big[i] = act(bias + sum_t [s | (i + p - k*dl)] col[(i + p - k*dl)/s][t])
+__global__ void __launch_bounds__(256)
+col2im1_kernel(Geo g, const bf16* __restrict__ col, bf16* __restrict__ big, int Kp, const float* __restrict__ bias,
+               int act, float slope, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  int64_t v = idx;
+  const int iw = (int)(v % g.bw); v /= g.bw;
+  const int ih = (int)(v % g.bh); v /= g.bh;
+  const int id = (int)(v % g.bd);
+  const int n = (int)(v / g.bd);
+  float acc = bias ? bias[0] : 0.f;
+  for (int kd = 0; kd < g.k[0]; kd++) {
+    const int nd = id + g.p[0] - kd * g.dl[0];
+    if (nd < 0 || nd % g.s[0]) continue;
+    const int od = nd / g.s[0];
+    if (od >= g.sd) continue;
+    for (int kh = 0; kh < g.k[1]; kh++) {
+      const int nh = ih + g.p[1] - kh * g.dl[1];
+      if (nh < 0 || nh % g.s[1]) continue;
+      const int oh = nh / g.s[1];
+      if (oh >= g.sh) continue;
+      const bf16* base = col + ((((int64_t)n * g.sd + od) * g.sh + oh) * g.sw) * Kp + (kd * g.k[1] + kh) * g.k[2];
+      for (int kw = 0; kw < g.k[2]; kw++) {
+        const int nw = iw + g.p[2] - kw * g.dl[2];
+        if (nw < 0 || nw % g.s[2]) continue;
+        const int ow = nw / g.s[2];
+        if (ow >= g.sw) continue;
+        acc += __bfloat162float(base[(int64_t)ow * Kp + kw]);
+      }
+    }
+  }
+  big[idx] = __float2bfloat16_rn(act_f(acc, act, slope));
+}
+
+// packed filters --------------------------------------------------------------
+// gather : wp[a][t]  (Kp columns, zero padded)   = w[a][t]
+// scatter: wp[t][a]  (Kp rows,    zero padded)   = w[a][t]
+__global__ void __launch_bounds__(256)
+thin_pack_kernel(const float* __restrict__ w, bf16* __restrict__ wp, int A, int T, int Kp, int gather) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)A * Kp) return;
+  int a, t;
+  if (gather) { a = (int)(idx / Kp); t = (int)(idx % Kp); }
+  else        { t = (int)(idx / A);  a = (int)(idx % A); }
+  wp[idx] = __float2bfloat16_rn(t < T ? w[(int64_t)a * T + t] : 0.f);
+}
+
+// dw[a][t] = tmp[a][t] for t < T  (tmp has Kp columns)
+__global__ void __launch_bounds__(256)
+thin_unpad_kernel(const float* __restrict__ tmp, float* __restrict__ dw, int A, int T, int Kp) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)A * T) return;
+  dw[idx] = tmp[(idx / T) * Kp + idx % T];
+}
+
+// ---------------------------------------------------------------------------
+bool thin_applicable(const b2c_conv_desc* c, const Geo& g) {
+  if (c->io_dtype != B2C_BF16 || c->algo == B2C_ALGO_DIRECT) return false;
+  if (g.bc != 1 || g.sc % 8 != 0 || g.sc < 16) return false;
+  const int64_t rows = (int64_t)g.n * g.sd * g.sh * g.sw;
+  return g.taps() <= 1024 && rows < 0x7fffffffLL && g.k[1] * g.k[2] <= 64;
+}
+int thin_kp(const Geo& g) { int kp = (g.taps() + 7) / 8 * 8; return kp < 16 ? 16 : kp; }
+size_t thin_packed_bytes(const Geo& g) { return (size_t)thin_kp(g) * g.sc * sizeof(bf16); }
+
+int thin_pack(const Geo& g, bool gather, const float* w, void* wp, cudaStream_t st) {
+  const int Kp = thin_kp(g);
+  const int64_t n = (int64_t)g.sc * Kp;
+  thin_pack_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(w, static_cast<bf16*>(wp), g.sc, g.taps(), Kp,
+                                                          gather ? 1 : 0);
+  return launched();
+}
+
+static int64_t rows_of(const Geo& g) { return (int64_t)g.n * g.sd * g.sh * g.sw; }
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+static size_t col_bytes(const Geo& g) { return align256((size_t)rows_of(g) * thin_kp(g) * sizeof(bf16)); }
+
+// the GEMM [rows][kin] x [nout][kin]^T as a 1x1x1 convolution over a 1 x 1 x 1 x rows lattice
+static Geo gemm_geo(int64_t rows, int nout, int kin) {
+  Geo p;
+  p.n = 1;
+  p.sc = nout; p.sd = 1; p.sh = 1; p.sw = (int)rows;
+  p.bc = kin;  p.bd = 1; p.bh = 1; p.bw = (int)rows;
+  for (int i = 0; i < 3; i++) { p.k[i] = 1; p.s[i] = 1; p.p[i] = 0; p.dl[i] = 1; }
+  return p;
+}
+
+size_t thin_workspace(const Geo& g, int kind) {
+  size_t b = col_bytes(g);
+  if (kind == 2) {
+    b += align256((size_t)g.sc * thin_kp(g) * sizeof(float));
+    b += tc_wgrad_workspace(gemm_geo(rows_of(g), g.sc, thin_kp(g)));
+  }
+  return b;
+}
+
+static int im2col_launch(const Geo& g, const void* big, void* col, cudaStream_t st) {
+  const int Kp = thin_kp(g);
+  const int64_t total = rows_of(g) * g.k[0];
+  if (total == 0) return B2C_OK;
+  const int64_t blocks = cdiv(total, 256);
+  if (blocks > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  const bf16* b = static_cast<const bf16*>(big);
+  bf16* c = static_cast<bf16*>(col);
+  const int khw = g.k[1] * g.k[2];
+  if (khw == 16) im2col1_kernel<16><<<(unsigned)blocks, 256, 0, st>>>(g, b, c, Kp, total);
+  else if (khw == 8) im2col1_kernel<8><<<(unsigned)blocks, 256, 0, st>>>(g, b, c, Kp, total);
+  else im2col1_kernel<0><<<(unsigned)blocks, 256, 0, st>>>(g, b, c, Kp, total);
+  return launched();
+}
+
+int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, const float* bias, int act,
+                float slope, void* ws, size_t wsb, cudaStream_t st) {
+  if (!ws || wsb < thin_workspace(g, 0)) return B2C_ERR_WORKSPACE;
+  int rc = im2col_launch(g, big, ws, st);
+  if (rc) return rc;
+  ConvPlan plan;
+  rc = plan_gather(gemm_geo(rows_of(g), g.sc, thin_kp(g)), &plan);
+  if (rc) return rc;
+  return tc_conv_launch(plan, ws, wp, out_small, bias, 0, act, slope, st);
+}
+
+int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big, const float* bias, int act,
+                 float slope, void* ws, size_t wsb, cudaStream_t st) {
+  if (!ws || wsb < thin_workspace(g, 1)) return B2C_ERR_WORKSPACE;
+  const int Kp = thin_kp(g);
+  ConvPlan plan;
+  int rc = plan_gather(gemm_geo(rows_of(g), Kp, g.sc), &plan);
+  if (rc) return rc;
+  rc = tc_conv_launch(plan, small, wp, ws, nullptr, 0, B2C_ACT_NONE, 0.f, st);
+  if (rc) return rc;
+  const int64_t total = (int64_t)g.n * g.bd * g.bh * g.bw;
+  if (total == 0) return B2C_OK;
+  col2im1_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(g, static_cast<const bf16*>(ws),
+                                                             static_cast<bf16*>(out_big), Kp, bias, act, slope, total);
+  return launched();
+}
+
+int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void* ws, size_t wsb, cudaStream_t st) {
+  if (!ws || wsb < thin_workspace(g, 2)) return B2C_ERR_WORKSPACE;
+  const int Kp = thin_kp(g), T = g.taps();
+  int rc = im2col_launch(g, big, ws, st);
+  if (rc) return rc;
+  uint8_t* p = static_cast<uint8_t*>(ws) + col_bytes(g);
+  float* tmp = reinterpret_cast<float*>(p);
+  p += align256((size_t)g.sc * Kp * sizeof(float));
+  const Geo gg = gemm_geo(rows_of(g), g.sc, Kp);
+  const size_t tcws = tc_wgrad_workspace(gg);
+  float* target = Kp == T ? dw : tmp;
+  rc = tc_wgrad_launch(gg, small, ws, target, p, tcws, st);
+  if (rc) return rc;
+  if (Kp != T) {
+    const int64_t n = (int64_t)g.sc * T;
+    thin_unpad_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(tmp, dw, g.sc, T, Kp);
+    return launched();
+  }
+  return B2C_OK;
+}
+
+}  // namespace b2c

@@ -42,6 +42,15 @@ DIRECT_CASES = [
     (True, 8, 12, 4, 1, 0, 1, (1, 1, 1), 3),
     (True, 40, 8, 3, 2, 0, 1, (5, 5, 5), 2),
 ]
+# big-side tensor has ONE channel: im2col / col2im + tcgen05 GEMM (csrc/thin.cu)
+THIN_CASES = [
+    (False, 1, 16, 4, 2, 1, 1, (16, 16, 16), 2),    # dcgan.py:161 stem
+    (False, 1, 64, 4, 2, 1, 1, (8, 10, 12), 3),     # ragged spatial extents
+    (False, 1, 32, 7, 2, 3, 1, (12, 12, 12), 2),    # FID_ResNet.py:119 stem (Kp = 344)
+    (False, 1, 64, 3, 1, 1, 1, (6, 7, 8), 2),       # biggan.py:78 input conv (Kp = 32)
+    (True, 16, 1, 4, 2, 1, 1, (8, 8, 8), 2),        # dcgan.py:67 G head
+    (True, 128, 1, 4, 2, 1, 1, (6, 6, 6), 2),       # dcgan.py:67 at full width
+]
 
 
 @pytest.fixture(scope="module")
@@ -97,6 +106,13 @@ def test_direct_path_bf16(libs, case):
 @pytest.mark.parametrize("case", TC_CASES[:3] + TC_CASES[12:14] + DIRECT_CASES)
 def test_direct_path_fp32(libs, case):
     _run(libs, case, torch.float32, AUTO)
+
+
+@pytest.mark.parametrize("case", THIN_CASES)
+def test_thin_path_bf16(libs, case):
+    _run(libs, case, torch.bfloat16, AUTO)
+    assert libs[0].last_algo() == TC
+    _run(libs, case, torch.bfloat16, AUTO, act=3)      # tanh epilogue (dcgan.py:68)
 
 
 @pytest.mark.parametrize("act", [1, 2, 3])
