@@ -20,6 +20,30 @@ from ._lib import (ACT_IDS, ACT_NONE, ALGO_AUTO, BF16, F32, PASS_DGRAD,
                    PASS_FWD, PASS_WGRAD, ConvDesc, Fusion, check)
 
 _force_algo = [ALGO_AUTO]     # tests / profiling: force DIRECT or TC
+PROFILE = None                # bench.py: list collecting (pass, desc tuple, start event, end event)
+
+
+class _timed:
+    """Bracket one C-ABI conv launch with CUDA events on its stream when bench.py has
+    switched per-launch profiling on (PROFILE is a list)."""
+
+    def __init__(self, pas, desc):
+        self.on = PROFILE is not None
+        if self.on:
+            self.key = (pas, bool(desc.transposed), desc.x.n, desc.x.c, desc.x.d, desc.y.c, desc.y.d,
+                        desc.k[0], desc.stride[0], desc.pad[0], desc.dil[0])
+
+    def __enter__(self):
+        if self.on:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *a):
+        if self.on:
+            self.e1.record()
+            PROFILE.append((self.key, self.e0, self.e1, _lib.lib().b2c_last_algo()))
+
 
 
 def set_algo(algo):
@@ -124,6 +148,15 @@ def from_ndhwc(buf):
     return buf.permute(0, 4, 1, 2, 3)
 
 
+def alloc_out(n, d, h, w, c, dtype, device):
+    """Fresh logical-NCDHW tensor whose storage is dense NDHWC.  Not a view, so the
+    reference's in-place activations (nn.ReLU(True), dcgan.py:49) may modify the
+    output of a custom Function.  Returns (logical tensor, NDHWC view of it)."""
+    t = torch.empty_strided((n, c, d, h, w), (d * h * w * c, 1, h * w * c, w * c, c),
+                            dtype=dtype, device=device)
+    return t, t.permute(0, 2, 3, 4, 1)
+
+
 def _triple(v):
     if isinstance(v, (list, tuple)):
         if len(v) == 1:
@@ -219,24 +252,26 @@ class _ConvFn(Function):
         desc = _desc(g, tuple(xb.shape), cout, cd, _force_algo[0])
         L = _lib.lib()
         wp = _packed_filter(w, desc, PASS_FWD, cd)
-        y = torch.empty((desc.y.n, desc.y.d, desc.y.h, desc.y.w, desc.y.c), dtype=cd, device=x.device)
+        yl, y = alloc_out(desc.y.n, desc.y.d, desc.y.h, desc.y.w, desc.y.c, cd, x.device)
         bf = None
         if bias is not None:
             bf = bias.detach()
             bf = bf if bf.dtype == torch.float32 else bf.float()
         fu = Fusion(_ptr(bf), int(act), float(slope))
         ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_FWD), x)
-        with _dev(x):
+        with _dev(x), _timed("fwd", desc):
             check(L.b2c_conv3d_fwd(C.byref(desc), _ptr(xb), _ptr(wp), _ptr(y), C.byref(fu),
                                    _ptr(ws), ws.numel(), _stream(x)), "conv3d_fwd")
         ctx.g, ctx.act, ctx.slope, ctx.cd = g, int(act), float(slope), cd
         ctx.x_dtype, ctx.has_bias = x.dtype, bias is not None
-        ctx.save_for_backward(xb, w, y if act != ACT_NONE else None)
-        return from_ndhwc(y)
+        ctx.save_for_backward(xb, w, yl if act != ACT_NONE else None)
+        return yl
 
     @staticmethod
     def backward(ctx, gy):
         xb, w, y = ctx.saved_tensors
+        if y is not None:
+            y = y.permute(0, 2, 3, 4, 1)
         g, cd = ctx.g, ctx.cd
         L = _lib.lib()
         cout = w.shape[1] if g.transposed else w.shape[0]
@@ -253,7 +288,7 @@ class _ConvFn(Function):
             wp = _packed_filter(w, desc, PASS_DGRAD, cd)
             dxb = torch.empty_like(xb)
             ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_DGRAD), xb)
-            with _dev(xb):
+            with _dev(xb), _timed("dgrad", desc):
                 check(L.b2c_conv3d_dgrad(C.byref(desc), _ptr(gyb), _ptr(wp), _ptr(dxb), _ptr(ws),
                                          ws.numel(), _stream(xb)), "conv3d_dgrad")
             dx = from_ndhwc(dxb)
@@ -265,7 +300,7 @@ class _ConvFn(Function):
             dw = torch.empty(w.shape, dtype=torch.float32, device=w.device) if need_w else None
             db = torch.empty(cout, dtype=torch.float32, device=w.device) if need_b else None
             ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_WGRAD), xb)
-            with _dev(xb):
+            with _dev(xb), _timed("wgrad", desc):
                 check(L.b2c_conv3d_wgrad(C.byref(desc), _ptr(xb), _ptr(gyb), _ptr(dw), _ptr(db),
                                          _ptr(ws), ws.numel(), _stream(xb)), "conv3d_wgrad")
             if dw is not None and w.dtype != torch.float32:
@@ -343,7 +378,7 @@ class _BNActFn(Function):
                 invstd.copy_(torch.rsqrt(rvar.float() + eps))
                 scale.copy_(invstd if gf is None else gf * invstd)
                 shift.copy_((0 if bf is None else bf) - mean * scale)
-            y = torch.empty_like(xb)
+            yl, y = alloc_out(n, d, h, w, c, cd, dev)
             check(L.b2c_bn_act_fwd(_ptr(xb), _ptr(y), _ptr(rb), rows, c, _dt(cd), _ptr(scale),
                                    _ptr(shift), int(act), float(slope), st), "bn_act_fwd")
         ctx.save_for_backward(xb, rb, stats)
@@ -351,7 +386,7 @@ class _BNActFn(Function):
         ctx.x_dtype = x.dtype
         ctx.res_dtype = residual.dtype if residual is not None else None
         ctx.affine = (gamma is not None, beta is not None)
-        return from_ndhwc(y)
+        return yl
 
     @staticmethod
     def backward(ctx, gy):
@@ -429,7 +464,7 @@ class _LNActFn(Function):
         gp = _perm_affine(gamma, c, d * h * w, True) if gamma is not None else None
         bp = _perm_affine(beta, c, d * h * w, True) if beta is not None else None
         mr = torch.empty((2, n), dtype=torch.float32, device=x.device)
-        y = torch.empty_like(xb)
+        yl, y = alloc_out(n, d, h, w, c, cd, x.device)
         ws = _ws(L.b2c_ln_workspace(n, Lh), x)
         with _dev(x):
             check(L.b2c_ln_act_fwd(_ptr(xb), _ptr(y), n, Lh, _dt(cd), _ptr(gp), _ptr(bp),
@@ -438,7 +473,7 @@ class _LNActFn(Function):
         ctx.save_for_backward(xb, gp, bp, mr)
         ctx.act, ctx.slope, ctx.cd, ctx.x_dtype = int(act), float(slope), cd, x.dtype
         ctx.pshape = tuple(gamma.shape) if gamma is not None else None
-        return from_ndhwc(y)
+        return yl
 
     @staticmethod
     def backward(ctx, gy):

@@ -1,0 +1,99 @@
+"""One GAN training step exactly as the reference trainer schedules it
+(trainer.py:208-252 D_step, trainer.py:254-283 G_step, trainer.py:296-303 loop):
+parameter freeze / unfreeze decides which of fwd / dgrad / wgrad run, Adam
+betas=(0, 0.9) (trainer.py:77-78), WGAN or hinge loss, mixed precision through
+autocast.  The reference asks for fp16 autocast + GradScaler (trainer.py:14,80-81);
+the B200 path computes in bf16, where loss scaling is the identity, so the scaler
+is constructed disabled.
+
+Works with any pair of nn.Modules (the drop-in layers on CUDA, or stock torch layers
+on the CPU for the reference arm of bench.py).  `reducer_d` / `reducer_g` are
+optional :class:`b200conv3d.parallel.GradReducer`s for data-parallel training.
+"""
+import contextlib
+
+import torch
+import torch.nn as tnn
+import torch.optim as optim
+
+
+class GanStep:
+    def __init__(self, netG, netD, z_size=512, lrG=5e-5, lrD=1e-4, hinge=False, iterD=2,
+                 autocast_dtype=torch.bfloat16, reducer_g=None, reducer_d=None, seed=None):
+        self.netG, self.netD = netG, netD
+        self.z_size, self.hinge, self.iterD = z_size, hinge, iterD
+        self.device = next(netG.parameters()).device
+        fused = self.device.type == "cuda"
+        self.optimizerD = optim.Adam(netD.parameters(), lr=lrD, betas=(0.0, 0.9), fused=fused)
+        self.optimizerG = optim.Adam(netG.parameters(), lr=lrG, betas=(0.0, 0.9), fused=fused)
+        self.autocast_dtype = autocast_dtype
+        self.reducer_g, self.reducer_d = reducer_g, reducer_d
+        self.gen = None
+        if seed is not None:
+            self.gen = torch.Generator(device=self.device)
+            self.gen.manual_seed(seed)
+        for p in list(netD.parameters()) + list(netG.parameters()):   # trainer.py:290-293
+            p.requires_grad = False
+
+    def _amp(self):
+        if self.autocast_dtype is None or self.device.type != "cuda":
+            return contextlib.nullcontext()
+        return torch.autocast("cuda", dtype=self.autocast_dtype)
+
+    def noise(self, n):
+        return torch.randn(n, self.z_size, 1, 1, 1, dtype=torch.float, device=self.device,
+                           generator=self.gen)
+
+    def D_step(self, real):
+        """trainer.py:208-252.  Returns (errD_real, errD_fake) as 0-d device tensors."""
+        for p in self.netD.parameters():
+            p.requires_grad = True
+        self.netD.zero_grad()
+        if self.reducer_d is not None:
+            self.reducer_d.begin()
+        with self._amp():
+            fake = self.netG(self.noise(real.shape[0]))
+            if self.hinge:
+                errD_real = tnn.functional.relu(1.0 - self.netD(real)).mean()
+                errD_fake = tnn.functional.relu(1.0 + self.netD(fake)).mean()
+                errD = errD_fake + errD_real
+            else:
+                errD_real = self.netD(real).mean()
+                errD_fake = self.netD(fake).mean()
+                errD = errD_fake - errD_real
+            errD.backward()
+        if self.reducer_d is not None:
+            self.reducer_d.finish()
+        self.optimizerD.step()
+        for p in self.netD.parameters():
+            p.requires_grad = False
+        return errD_real.detach(), errD_fake.detach()
+
+    def G_step(self, batch):
+        """trainer.py:254-283.  Returns (errG, fake)."""
+        for p in self.netG.parameters():
+            p.requires_grad = True
+        self.netG.zero_grad()
+        if self.reducer_g is not None:
+            self.reducer_g.begin()
+        with self._amp():
+            fake = self.netG(self.noise(batch))
+            errG = -self.netD(fake).mean()
+            errG.backward()
+        if self.reducer_g is not None:
+            self.reducer_g.finish()
+        self.optimizerG.step()
+        for p in self.netG.parameters():
+            p.requires_grad = False
+        return errG.detach(), fake.detach()
+
+    def step(self, reals):
+        """One iteration of trainer.py:296-303: iterD discriminator steps, one generator step.
+        `reals` is an iterable yielding iterD real batches [B,1,128,128,128] on the device."""
+        out = []
+        batch = None
+        for real in reals:
+            batch = real.shape[0]
+            out.append(self.D_step(real))
+        errG, fake = self.G_step(batch)
+        return out, errG, fake
