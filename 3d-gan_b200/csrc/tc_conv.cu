@@ -13,6 +13,7 @@
 #include "tc_conv.cuh"
 
 #include <mutex>
+#include <stdlib.h>
 
 #include "ptx.cuh"
 
@@ -25,63 +26,90 @@ constexpr uint32_t kABytes = kBlockM * kBlockK * 2;   // 16 KB: 128 rows x 128 B
 
 struct alignas(64) TcConvParams {
   CUtensorMap in_maps[kMaxMaps];
+  CUtensorMap out_maps[kMaxSubs];
   CUtensorMap w_map;
   SubDesc subs[kMaxSubs];
   TapDesc taps[kMaxTaps];
   int32_t nsubs;
   int32_t box[4];
+  int32_t mt, split_dim, sub_ext;
   int32_t nout, block_n, tiles_n, kchunks;
+  int32_t num_tiles;
   int32_t stages;
   uint32_t idesc, tmem_cols;
-  __nv_bfloat16* out;
   const float* bias;
   int32_t bias_mod;      // bias index = column % bias_mod (point-convT: columns are (tap, co))
   int32_t act;
   float slope;
+  int32_t dbg;           // B2C_DBG env (diagnostics only): 1 no TMA store, 2 no tcgen05.ld, 4 no st.shared
 };
+
+// hardware tanh (abs error ~5e-4 of full scale): far inside bf16 output resolution near +-1
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+struct TileCoord { int si, nt, q[4], iters; };
+
+__device__ __forceinline__ TileCoord decode_tile(const TcConvParams& P, int tile) {
+  TileCoord c;
+  c.nt = tile % P.tiles_n;
+  const int mtile = tile / P.tiles_n;
+  int si = 0;
+  for (int s = 1; s < P.nsubs; s++) if (mtile >= P.subs[s].tile0) si = s;
+  c.si = si;
+  const SubDesc& sub = P.subs[si];
+  int local = mtile - sub.tile0;
+  const int tw = local % sub.tiles[3]; local /= sub.tiles[3];
+  const int th = local % sub.tiles[2]; local /= sub.tiles[2];
+  const int td = local % sub.tiles[1]; local /= sub.tiles[1];
+  c.q[0] = local * P.box[0]; c.q[1] = td * P.box[1]; c.q[2] = th * P.box[2]; c.q[3] = tw * P.box[3];
+  c.iters = sub.ntaps * P.kchunks;
+  return c;
+}
+
+constexpr uint32_t kStagingBytes = 2 * kABytes;      // two 128-row x 64-column bf16 slabs (ring)
+constexpr int kEpiThreads = 128;
+
+// Persistent, warp-specialised: CTA b processes tiles b, b + grid, ...
+//   warp 0      TMA producer: runs ahead across tiles through the smem ring
+//   warp 1      tcgen05.mma issuer; two TMEM accumulator sets so that the epilogue of
+//               tile i overlaps the main loop of tile i+1
+//   warps 2..5  epilogue: TMEM -> registers -> bias/activation -> bf16 -> swizzled smem
+//               slab -> TMA store (coalesced, clipped at the tensor edge)
 __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_constant__ TcConvParams P) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t sbase = (raw + 1023u) & ~1023u;               // SW128 needs 1024-B alignment
   uint8_t* sgen = smem_raw + (sbase - raw);
   const int stages = P.stages;
+  const uint32_t a_bytes = (uint32_t)P.mt * kABytes;
   const uint32_t b_bytes = (uint32_t)P.block_n * 128u;
-  const uint32_t stage_bytes = kABytes + b_bytes;
-  const uint32_t bar0 = sbase + stages * stage_bytes;           // full[stages], empty[stages], acc
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sgen + stages * stage_bytes + (2 * stages + 1) * 8);
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t staging = sbase + stages * stage_bytes;
+  const uint32_t bar0 = staging + kStagingBytes;                // full[stages], empty[stages], tfull[2], tempty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sgen + stages * stage_bytes + kStagingBytes + (2 * stages + 4) * 8);
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (stages + s); };
-  const uint32_t acc_bar = bar0 + 8u * (2 * stages);
+  auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * stages + a); };
+  auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * stages + 2 + a); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // ---- tile decode ---------------------------------------------------------
-  const int nt = blockIdx.x % P.tiles_n;
-  const int mt = blockIdx.x / P.tiles_n;
-  int si = 0;
-  for (int s = 1; s < P.nsubs; s++) if (mt >= P.subs[s].tile0) si = s;
-  const SubDesc& sub = P.subs[si];
-  int local = mt - sub.tile0;
-  const int tw = local % sub.tiles[3]; local /= sub.tiles[3];
-  const int th = local % sub.tiles[2]; local /= sub.tiles[2];
-  const int td = local % sub.tiles[1]; local /= sub.tiles[1];
-  const int tn = local;
-  const int q0n = tn * P.box[0], q0d = td * P.box[1], q0h = th * P.box[2], q0w = tw * P.box[3];
-  const int iters = sub.ntaps * P.kchunks;
-
-  // ---- setup ---------------------------------------------------------------
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < stages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    mbar_init(acc_bar, 1);
+    for (int a = 0; a < 2; a++) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), kEpiThreads / 32); }
     fence_barrier_init();
     prefetch_tmap(&P.w_map);
     prefetch_tmap(&P.in_maps[0]);
+    prefetch_tmap(&P.out_maps[0]);
   }
   if (warp == 1) {
     tmem_alloc(smem_u32(tmem_slot), P.tmem_cols);
@@ -91,22 +119,29 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+  const uint32_t acc_cols = (uint32_t)P.mt * (uint32_t)P.block_n;
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      int it = 0;
-      for (int t = 0; t < sub.ntaps; t++) {
-        const TapDesc tp = P.taps[sub.tap0 + t];
-        const CUtensorMap* im = &P.in_maps[tp.map];
-        for (int kc = 0; kc < P.kchunks; kc++, it++) {
-          const int s = it % stages;
-          const uint32_t ph = (uint32_t)(it / stages) & 1u;
-          if (!mbar_wait(empty_bar(s), ph ^ 1u)) break;
-          mbar_arrive_expect_tx(full_bar(s), stage_bytes);
-          const uint32_t a_dst = sbase + s * stage_bytes;
-          tma_load_5d(a_dst, im, full_bar(s), kc * kBlockK, q0w + tp.off_w, q0h + tp.off_h, q0d + tp.off_d, q0n);
-          tma_load_3d(a_dst + kABytes, &P.w_map, full_bar(s), kc * kBlockK, nt * P.block_n, tp.wtap);
+      uint32_t it = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < P.num_tiles && ok; tile += gridDim.x) {
+        const TileCoord c = decode_tile(P, tile);
+        const SubDesc& sub = P.subs[c.si];
+        for (int t = 0; t < sub.ntaps && ok; t++) {
+          const TapDesc tp = P.taps[sub.tap0 + t];
+          const CUtensorMap* im = &P.in_maps[tp.map];
+          for (int kc = 0; kc < P.kchunks; kc++, it++) {
+            const uint32_t s = it % stages;
+            const uint32_t ph = (it / stages) & 1u;
+            if (!mbar_wait(empty_bar(s), ph ^ 1u)) { ok = false; break; }
+            mbar_arrive_expect_tx(full_bar(s), stage_bytes);
+            const uint32_t a_dst = sbase + s * stage_bytes;
+            tma_load_5d(a_dst, im, full_bar(s), kc * kBlockK, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
+                        c.q[1] + tp.off_d, c.q[0]);
+            tma_load_3d(a_dst + a_bytes, &P.w_map, full_bar(s), kc * kBlockK, c.nt * P.block_n, tp.wtap);
+          }
         }
       }
     }
@@ -114,64 +149,113 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
     // ===== MMA issuer (single thread) =====
     if (lane == 0) {
       constexpr uint64_t hi = smem_desc_hi(16, 1024, 2);         // K-major, SWIZZLE_128B
+      uint32_t it = 0, tcount = 0;
       bool ok = true;
-      for (int it = 0; it < iters && ok; it++) {
-        const int s = it % stages;
-        const uint32_t ph = (uint32_t)(it / stages) & 1u;
-        ok = mbar_wait(full_bar(s), ph);
+      for (int tile = blockIdx.x; tile < P.num_tiles && ok; tile += gridDim.x, tcount++) {
+        const TileCoord c = decode_tile(P, tile);
+        const uint32_t acc = tcount & 1u;
+        const uint32_t aph = (tcount >> 1) & 1u;
+        ok = mbar_wait(tempty_bar(acc), aph ^ 1u);               // epilogue has drained this accumulator set
         tc_fence_after();
-        const uint32_t a_addr = sbase + s * stage_bytes, b_addr = a_addr + kABytes;
+        const uint32_t d_tmem = tmem_base + acc * acc_cols;
+        for (int i = 0; i < c.iters && ok; i++, it++) {
+          const uint32_t s = it % stages;
+          const uint32_t ph = (it / stages) & 1u;
+          ok = mbar_wait(full_bar(s), ph);
+          tc_fence_after();
+          const uint32_t a_addr = sbase + s * stage_bytes, b_addr = a_addr + a_bytes;
+          for (int m = 0; m < P.mt; m++) {
 #pragma unroll
-        for (int k = 0; k < kBlockK / 16; k++)
-          umma_f16(tmem_base, smem_desc(a_addr + k * 32, hi), smem_desc(b_addr + k * 32, hi), P.idesc,
-                   (it | k) != 0 ? 1u : 0u);
-        umma_commit(empty_bar(s));       // frees the smem slot when these MMAs retire
+            for (int k = 0; k < kBlockK / 16; k++)
+              umma_f16(d_tmem + m * P.block_n, smem_desc(a_addr + m * kABytes + k * 32, hi),
+                       smem_desc(b_addr + k * 32, hi), P.idesc, (i | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(empty_bar(s));       // frees the smem slot when these MMAs retire
+        }
+        if (c.iters > 0) umma_commit(tfull_bar(acc));   // accumulator complete
+        else mbar_arrive(tfull_bar(acc));
       }
-      if (iters > 0) umma_commit(acc_bar);   // accumulator complete
-      else mbar_arrive(acc_bar);
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> bias/activation -> bf16 -> global =====
+    // ===== epilogue =====
     const int grp = warp & 3;                    // TMEM sub-partition of this warp
-    const int row = grp * 32 + lane;
-    int r = row;
-    const int rw = r % P.box[3]; r /= P.box[3];
-    const int rh = r % P.box[2]; r /= P.box[2];
-    const int rd = r % P.box[1]; r /= P.box[1];
-    const int qn = q0n + r, qd = q0d + rd, qh = q0h + rh, qw = q0w + rw;
-    const bool valid = qn < sub.ext[0] && qd < sub.ext[1] && qh < sub.ext[2] && qw < sub.ext[3];
-    __nv_bfloat16* orow = P.out + sub.obase + qn * sub.ostr[0] + qd * sub.ostr[1] + qh * sub.ostr[2] +
-                          qw * sub.ostr[3];
-    mbar_wait(acc_bar, 0);
-    tc_fence_after();
-    const uint32_t trow = tmem_base + ((uint32_t)(grp * 32) << 16);
-    for (int c0 = 0; c0 < P.block_n; c0 += 16) {
-      uint32_t v[16];
-      if (iters > 0) { tmem_ld16(trow + c0, v); tmem_ld_wait(); }
-      else {
+    const int row = grp * 32 + lane;             // row of the 128-row sub-tile
+    const int et = threadIdx.x - 64;             // 0..127
+    const uint32_t lane_off = (uint32_t)(grp * 32) << 16;
+    uint32_t tcount = 0, slab_count = 0;
+    // A failed (timed-out) wait only raises g_tc_error: the loop is never left early, so the
+    // named barriers of the 128 epilogue threads stay matched and the kernel drains.
+    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, tcount++) {
+      const TileCoord c = decode_tile(P, tile);
+      const uint32_t acc = tcount & 1u;
+      const uint32_t aph = (tcount >> 1) & 1u;
+      mbar_wait(tfull_bar(acc), aph);
+      tc_fence_after();
+      const CUtensorMap* om = &P.out_maps[c.si];
+      const int nslab = (P.block_n + 63) >> 6;
+      for (int m = 0; m < P.mt; m++) {
+        int q[4] = {c.q[0], c.q[1], c.q[2], c.q[3]};
+        q[P.split_dim] += m * P.sub_ext;
+        for (int j = 0; j < nslab; j++, slab_count++) {
+          const uint32_t sbuf = staging + (slab_count & 1u) * kABytes;
+          // the TMA store that last read this slab buffer (2 slabs ago) must be done with it
+          if (et == 0) tma_store_wait_read<1>();
+          named_bar_sync(1, kEpiThreads);
+          const uint32_t tcol = tmem_base + lane_off + acc * acc_cols + m * P.block_n + j * 64;
+          uint32_t v[64];
+          const int ncol = P.block_n - j * 64 < 64 ? P.block_n - j * 64 : 64;   // multiple of 16
+          if (c.iters > 0) {
 #pragma unroll
-        for (int j = 0; j < 16; j++) v[j] = 0u;
-      }
-      const int col = nt * P.block_n + c0;
-      if (valid) {
+            for (int g = 0; g < 4; g++)
+              if (g * 16 < ncol) tmem_ld16(tcol + g * 16, v + g * 16);
+            tmem_ld_wait();
+          } else {
 #pragma unroll
-        for (int j = 0; j < 16; j += 8) {
-          if (col + j < P.nout) {                 // nout % 8 == 0: whole 8-group in range
-            float f[8];
+            for (int i = 0; i < 64; i++) v[i] = 0u;
+          }
+          const int col0 = c.nt * P.block_n + j * 64;
+          if (P.bias) {
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-              float x = __uint_as_float(v[j + i]);
-              if (P.bias) x += __ldg(P.bias + (col + j + i) % P.bias_mod);
-              f[i] = act_f(x, P.act, P.slope);
+            for (int i = 0; i < 64; i++)
+              if (i < ncol) v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(P.bias + (col0 + i) % P.bias_mod));
+          }
+          // activation: one uniform branch per slab, never a per-element switch
+          if (P.act == B2C_ACT_RELU) {
+#pragma unroll
+            for (int i = 0; i < 64; i++) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
+          } else if (P.act == B2C_ACT_LRELU) {
+#pragma unroll
+            for (int i = 0; i < 64; i++) {
+              const float x = __uint_as_float(v[i]);
+              v[i] = __float_as_uint(x > 0.f ? x : x * P.slope);
             }
-            uint4 o;
-            o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-            o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-            *reinterpret_cast<uint4*>(orow + col + j) = o;
+          } else if (P.act == B2C_ACT_TANH) {
+#pragma unroll
+            for (int i = 0; i < 64; i++) v[i] = __float_as_uint(tanh_approx(__uint_as_float(v[i])));
+          }
+#pragma unroll
+          for (int ch = 0; ch < 8; ch++) {
+            if (ch * 8 < ncol)
+              st_shared_v4(sbuf + row * 128 + ((ch ^ (row & 7)) << 4),
+                           pack_bf16x2(__uint_as_float(v[ch * 8 + 0]), __uint_as_float(v[ch * 8 + 1])),
+                           pack_bf16x2(__uint_as_float(v[ch * 8 + 2]), __uint_as_float(v[ch * 8 + 3])),
+                           pack_bf16x2(__uint_as_float(v[ch * 8 + 4]), __uint_as_float(v[ch * 8 + 5])),
+                           pack_bf16x2(__uint_as_float(v[ch * 8 + 6]), __uint_as_float(v[ch * 8 + 7])));
+          }
+          fence_proxy_async();                   // make the generic-proxy smem writes visible to TMA
+          named_bar_sync(1, kEpiThreads);
+          if (et == 0) {
+            tma_store_5d(om, sbuf, col0, q[3], q[2], q[1], q[0]);
+            tma_store_commit();
           }
         }
       }
+      // all TMEM reads of this accumulator set are complete (tmem_ld_wait above)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
     }
+    if (et == 0) tma_store_wait<0>();
   }
 
   // ---- teardown --------------------------------------------------------------
@@ -386,6 +470,20 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
     int rc = encode_map(&P.in_maps[i], in, p.maps[i], 5, abox);
     if (rc) return rc;
   }
+  // output lattices (one per sub-problem): box = one 128-row sub-tile x 64 channels
+  int sbox[4] = {p.box[0], p.box[1], p.box[2], p.box[3]};
+  sbox[p.split_dim] = p.sub_ext;
+  const int obox[5] = {kBlockK, sbox[3], sbox[2], sbox[1], sbox[0]};
+  for (int s = 0; s < p.nsubs; s++) {
+    const SubDesc& sd = p.subs[s];
+    MapDesc om;
+    om.base = sd.obase;
+    om.dims[0] = p.nout; om.dims[1] = sd.ext[3]; om.dims[2] = sd.ext[2]; om.dims[3] = sd.ext[1]; om.dims[4] = sd.ext[0];
+    om.strides[0] = 1; om.strides[1] = sd.ostr[3]; om.strides[2] = sd.ostr[2]; om.strides[3] = sd.ostr[1];
+    om.strides[4] = sd.ostr[0];
+    int rc = encode_map(&P.out_maps[s], out, om, 5, obox);
+    if (rc) return rc;
+  }
   MapDesc wm;
   wm.base = 0;
   const int T = [&] { int mx = 0; for (int i = 0; i < p.ntaps_total; i++) if (p.taps[i].wtap > mx) mx = p.taps[i].wtap; return mx + 1; }();
@@ -398,23 +496,30 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   memcpy(P.taps, p.taps, sizeof(P.taps));
   P.nsubs = p.nsubs;
   for (int i = 0; i < 4; i++) P.box[i] = p.box[i];
+  P.mt = p.mt; P.split_dim = p.split_dim; P.sub_ext = p.sub_ext;
   P.nout = p.nout; P.block_n = p.block_n; P.tiles_n = p.tiles_n; P.kchunks = p.kchunks;
-  const uint32_t stage_bytes = kABytes + (uint32_t)p.block_n * 128u;
-  int stages = (kSmemBudget - 1024 - 256) / (int)stage_bytes;
+  const uint32_t stage_bytes = (uint32_t)p.mt * kABytes + (uint32_t)p.block_n * 128u;
+  const int fixed = 1024 /*alignment slack*/ + (int)kStagingBytes + 256 /*barriers + tmem slot*/;
+  int stages = (kSmemBudget - fixed) / (int)stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return B2C_ERR_UNSUPPORTED;
   P.stages = stages;
   P.idesc = idesc_bf16(kBlockM, p.block_n, 0, 0);
-  P.tmem_cols = tmem_cols_for(p.block_n);
-  P.out = static_cast<__nv_bfloat16*>(out);
+  P.tmem_cols = tmem_cols_for(2 * p.mt * p.block_n);
+  if (P.tmem_cols > 512) return B2C_ERR_UNSUPPORTED;
   P.bias = bias; P.bias_mod = bias_mod > 0 ? bias_mod : p.nout; P.act = act; P.slope = slope;
-  const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+  { const char* e = getenv("B2C_DBG"); P.dbg = e ? atoi(e) : 0; }
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
   // the attribute is per device; set it on every call (cheap) rather than caching per device
   if (cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
     return B2C_ERR_CUDA;
-  const int64_t grid = (int64_t)p.m_tiles * p.tiles_n;
-  if (grid <= 0) return B2C_OK;
-  tc_conv_kernel<<<(unsigned)grid, kThreadsTc, smem, st>>>(P);
+  const int64_t tiles = (int64_t)p.m_tiles * p.tiles_n;
+  if (tiles <= 0) return B2C_OK;
+  if (tiles > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  P.num_tiles = (int32_t)tiles;
+  const int sms = num_sms();
+  const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+  tc_conv_kernel<<<grid, kThreadsTc, smem, st>>>(P);
   return launched();
 }
 

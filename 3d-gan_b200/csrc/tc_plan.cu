@@ -10,8 +10,8 @@ static int posmod(int a, int b) { int m = a % b; return m < 0 ? m + b : m; }
 static int pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 static int imin(int a, int b) { return a < b ? a : b; }
 
-static void choose_box(const int ext[4], int box[4]) {
-  int rem = kBlockM;
+static void choose_box(const int ext[4], int box[4], int rows) {
+  int rem = rows;
   box[3] = imin(rem, pow2ceil(ext[3])); rem /= box[3];
   box[2] = imin(rem, pow2ceil(ext[2])); rem /= box[2];
   box[1] = imin(rem, pow2ceil(ext[1])); rem /= box[1];
@@ -29,7 +29,21 @@ static int finish(ConvPlan* p, int kin, int nout) {
   int ext[4] = {0, 0, 0, 0};
   for (int s = 0; s < p->nsubs; s++)
     for (int i = 0; i < 4; i++) if (p->subs[s].ext[i] > ext[i]) ext[i] = p->subs[s].ext[i];
-  choose_box(ext, p->box);
+  // Narrow N tiles are L2-bandwidth bound at 128 rows: give the CTA mt sub-tiles that share
+  // every B (filter) stage, keeping mt * block_n fp32 accumulator columns <= 256 so that
+  // two accumulator sets (epilogue overlap) fit the 512 TMEM columns.
+  int mt = bn > 128 ? 1 : 2;
+  int64_t vox = 1;
+  for (int i = 0; i < 4; i++) vox *= pow2ceil(ext[i] > 0 ? ext[i] : 1);
+  while (mt > 1 && vox < (int64_t)kBlockM * mt) mt >>= 1;
+  for (;; mt >>= 1) {
+    choose_box(ext, p->box, kBlockM * mt);
+    int sd = 0;
+    while (sd < 3 && p->box[sd] == 1) sd++;
+    if (p->box[sd] >= mt && p->box[sd] % mt == 0) { p->split_dim = sd; p->sub_ext = p->box[sd] / mt; break; }
+    if (mt == 1) return B2C_ERR_UNSUPPORTED;
+  }
+  p->mt = mt;
   for (int i = 0; i < 4; i++) if (p->box[i] > 256) return B2C_ERR_UNSUPPORTED;
   int64_t t0 = 0;
   for (int s = 0; s < p->nsubs; s++) {

@@ -50,7 +50,7 @@ def test_plan_matches_torch(dbg, case):
         info = (C.c_int32 * 8)()
         rc = dbg.b2c_debug_plan_run(C.byref(desc), pas, inp.data_ptr(), wp.data_ptr(), out.data_ptr(), info)
         assert rc == 0
-        assert info[3] * info[4] * info[5] * info[6] == 128          # tile box covers UMMA M
+        assert info[3] * info[4] * info[5] * info[6] in (128, 256, 512)   # 1, 2 or 4 UMMA M sub-tiles
         assert torch.isfinite(out).all()                              # every output voxel written
         assert (out - ref).abs().max() < 2e-4 * ref.abs().max()
 
