@@ -215,9 +215,15 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
           }
           const int col0 = c.nt * P.block_n + j * 64;
           if (P.bias) {
+            const int b0 = col0 % P.bias_mod;      // one modulo per slab; bias_mod >= 8
 #pragma unroll
-            for (int i = 0; i < 64; i++)
-              if (i < ncol) v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(P.bias + (col0 + i) % P.bias_mod));
+            for (int i = 0; i < 64; i++) {
+              if (i < ncol) {
+                int bi = b0 + i;
+                if (P.bias_mod >= 64) { if (bi >= P.bias_mod) bi -= P.bias_mod; } else bi %= P.bias_mod;
+                v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(P.bias + bi));
+              }
+            }
           }
           // activation: one uniform branch per slab, never a per-element switch
           if (P.act == B2C_ACT_RELU) {

@@ -1,0 +1,81 @@
+"""GPU parity of the whole DCGAN path against (1) the golden vectors of the UNMODIFIED
+reference (tests/golden/dcgan_ref.npz, width 2: exact fp32 kernels, tol 1e-4) and (2) the
+pinned CPU restatement oracle/ref_dcgan.py at a width that takes the tcgen05 path in bf16."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import b200conv3d as B
+from abi import rel_err
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import ref_dcgan  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(ROOT, "tests", "golden", "dcgan_ref.npz")
+
+
+def _load(net, gold, prefix):
+    sd = net.state_dict()
+    for k in list(sd):
+        if prefix + k in gold.files:
+            sd[k] = torch.from_numpy(gold[prefix + k])
+    net.load_state_dict(sd)
+
+
+def test_reference_golden_fp32():
+    gold = np.load(GOLD)
+    width, z, b = int(gold["width"]), int(gold["z"]), int(gold["batch"])
+    g, d = B.dcgan.build(z, width, width, 128, "cpu", fuse=False)
+    _load(g, gold, "g0.")
+    _load(d, gold, "d0.")
+    g, d = g.cuda(), d.cuda()
+    B.fuse(g), B.fuse(d)
+    torch.manual_seed(5)
+    zin = torch.randn(b, z, 1, 1, 1)
+    real = torch.rand(b, 1, 128, 128, 128) * 2 - 1
+    with torch.no_grad():
+        fake = g(zin.cuda())
+        dreal = d(real.cuda())
+    assert rel_err(fake[:, 0, ::8, ::8, ::8], torch.from_numpy(gold["fake0_sample"])) < 1e-4
+    assert rel_err(dreal.reshape(-1), torch.from_numpy(gold["dreal0"])) < 1e-4
+    # trainer.py:208-283, one D_step + G_step with the reference's noise draws
+    step = B.train.GanStep(g, d, z, autocast_dtype=None)
+    step.noise = lambda n: torch.randn(n, z, 1, 1, 1).cuda()
+    torch.manual_seed(77)
+    er, ef = step.D_step(real.cuda())
+    torch.manual_seed(78)
+    eg, _ = step.G_step(b)
+    np.testing.assert_allclose([er.item(), ef.item()], gold["D_losses"][0], rtol=2e-4, atol=2e-5)
+    np.testing.assert_allclose([eg.item()], gold["G_losses"], rtol=2e-4, atol=2e-5)
+    for k, v in g.state_dict().items():
+        if v.dim() == 5:
+            assert rel_err(v, torch.from_numpy(gold["g1." + k])) < 2e-3, k     # one Adam step (sign-like update)
+
+
+@pytest.mark.parametrize("width", [16])
+def test_tensor_core_model_vs_oracle_bf16(width):
+    """Width 16 (channels 16..256): every body layer takes the tcgen05 path, the 1-channel
+    stem / head the thin path.  bf16 vs the fp32 CPU oracle on the same weights."""
+    z, b = 32, 2
+    torch.manual_seed(11)
+    rg, rd = ref_dcgan.Generator(z, width), ref_dcgan.Discriminator(width)
+    g, d = B.dcgan.build(z, width, width, 128, "cpu", fuse=False)
+    g.load_state_dict(rg.state_dict()), d.load_state_dict(rd.state_dict())
+    g, d = g.cuda(), d.cuda()
+    B.fuse(g), B.fuse(d)
+    zin = torch.randn(b, z, 1, 1, 1)
+    real = torch.rand(b, 1, 128, 128, 128) * 2 - 1
+    with torch.no_grad():
+        f_ref, d_ref = rg(zin), rd(real)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            f, dd = g(zin.cuda()), d(real.cuda())
+    assert B._lib.lib().b2c_last_algo() in (1, 2)
+    ef = ((f.float().cpu() - f_ref).norm() / f_ref.norm()).item()
+    ed = ((dd.float().cpu() - d_ref).abs().max() / d_ref.abs().max()).item()
+    assert ef < 4e-2, ef          # 6 stacked bf16 layers with batch-2 BatchNorm: relative L2
+    assert ed < 4e-2, ed

@@ -1,0 +1,88 @@
+"""Pins oracle/ref_dcgan.py (the CPU restatement used as bench.py's reference arm and
+as the module-level oracle) against golden vectors produced by the UNMODIFIED reference
+(/root/reference dcgan.py + trainer.py, see oracle/gen_golden.py)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import ref_dcgan  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden", "dcgan_ref.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(GOLD)
+
+
+def _build(gold):
+    width, z = int(gold["width"]), int(gold["z"])
+    g, d = ref_dcgan.Generator(z, width), ref_dcgan.Discriminator(width)
+    sd = g.state_dict()
+    for k in sd:
+        sd[k] = torch.from_numpy(gold["g0." + k])
+    g.load_state_dict(sd)
+    sd = d.state_dict()
+    for k in list(sd):
+        if "d0." + k in gold.files:
+            sd[k] = torch.from_numpy(gold["d0." + k])
+    d.load_state_dict(sd)
+    return g, d, z
+
+
+def _inputs(gold):
+    torch.manual_seed(5)
+    b, z = int(gold["batch"]), int(gold["z"])
+    zin = torch.randn(b, z, 1, 1, 1)
+    real = torch.rand(b, 1, 128, 128, 128) * 2 - 1
+    np.testing.assert_array_equal(zin.numpy(), gold["zin"])
+    np.testing.assert_array_equal(real[:, 0, ::16, ::16, ::16].numpy(), gold["real_sample"])
+    return zin, real
+
+
+def test_state_dict_keys_match_reference(gold):
+    g, d, _ = _build(gold)
+    assert sorted("g0." + k for k in g.state_dict()) == sorted(k for k in gold.files if k.startswith("g0."))
+    ref_conv = sorted(k for k in gold.files if k.startswith("d0."))
+    ours_conv = sorted("d0." + k for k, v in d.state_dict().items() if v.dim() == 5 and v.shape[2] == 4)
+    assert ref_conv == ours_conv
+
+
+def test_forward_matches_reference(gold):
+    g, d, _ = _build(gold)
+    zin, real = _inputs(gold)
+    with torch.no_grad():
+        fake = g(zin)
+        dreal = d(real)
+    np.testing.assert_allclose(fake[:, 0, ::8, ::8, ::8].numpy(), gold["fake0_sample"], rtol=1e-5, atol=1e-7)
+    assert abs(fake.double().sum().item() - float(gold["fake0_sum"])) < 1e-6 * fake.numel() ** 0.5 + 1e-3
+    np.testing.assert_allclose(dreal.reshape(-1).numpy(), gold["dreal0"], rtol=1e-5, atol=1e-7)
+
+
+def test_train_phases_match_reference(gold):
+    """One Trainer.D_step + G_step (trainer.py:208-283): losses and updated filters."""
+    g, d, z = _build(gold)
+    _, real = _inputs(gold)
+    tr = ref_dcgan.RefTrainer(g, d, z)
+    torch.manual_seed(77)
+    er, ef = tr.d_step(real)
+    torch.manual_seed(78)
+    eg, _ = tr.g_step(int(gold["batch"]))
+    np.testing.assert_allclose([er, ef], gold["D_losses"][0], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose([eg], gold["G_losses"], rtol=1e-5, atol=1e-7)
+    for k, v in g.state_dict().items():
+        if v.dim() == 5:
+            np.testing.assert_allclose(v.numpy(), gold["g1." + k], rtol=1e-4, atol=1e-6)
+    for k, v in d.state_dict().items():
+        if v.dim() == 5 and v.shape[2] == 4:
+            np.testing.assert_allclose(v.numpy(), gold["d1." + k], rtol=1e-4, atol=1e-6)
+    sd = d.state_dict()
+    np.testing.assert_allclose(sd["main.1.weight"][:, ::16, ::16, ::16].numpy(), gold["d1.ln1_weight_sample"],
+                               rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(sd["main.1.bias"][:, ::16, ::16, ::16].numpy(), gold["d1.ln1_bias_sample"],
+                               rtol=1e-4, atol=1e-6)

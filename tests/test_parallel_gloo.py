@@ -1,0 +1,80 @@
+"""World-size-2 gloo test (CPU) of the data-parallel host logic
+(b200conv3d.parallel.GradReducer + b200conv3d.train.GanStep):
+rank-averaged gradients must equal the gradients of the concatenated global batch,
+frozen parameters must not take part, and both ranks must step identically."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+import torch.nn as nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _nets():
+    torch.manual_seed(0)
+    g = nn.Sequential(nn.ConvTranspose3d(4, 3, 4, 1), nn.ReLU(), nn.ConvTranspose3d(3, 1, 4, 2, 1), nn.Tanh())
+    d = nn.Sequential(nn.Conv3d(1, 3, 4, 2, 1, bias=False), nn.LeakyReLU(0.2), nn.Conv3d(3, 1, 4, 1, 0, bias=False))
+    return g, d
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, os.path.join(ROOT, "3d-gan_b200"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from b200conv3d.parallel import GradReducer
+    from b200conv3d.train import GanStep
+    g, d = _nets()
+    rg, rd = GradReducer(g, bucket_mb=0), GradReducer(d, bucket_mb=0)     # one bucket per parameter
+    step = GanStep(g, d, z_size=4, autocast_dtype=None, reducer_g=rg, reducer_d=rd)
+    torch.manual_seed(100)
+    reals = torch.rand(4, 1, 8, 8, 8) * 2 - 1
+    zs = torch.randn(4, 4, 1, 1, 1)
+    lo, hi = rank * 2, rank * 2 + 2
+    step.noise = lambda n: zs[lo:hi]
+    step.D_step(reals[lo:hi])
+    gd = [p.grad.clone() for p in d.parameters()]
+    assert all(p.grad is None for p in g.parameters())          # G frozen during D_step
+    step.G_step(2)
+    gg = [p.grad.clone() for p in g.parameters()]
+    npy = lambda ts: [t.detach().numpy().copy() for t in ts]          # by value: the worker exits before the read
+    q.put((rank, npy(gd), npy(gg), npy(list(d.parameters()) + list(g.parameters()))))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_grad_reducer_world2_matches_global_batch():
+    sys.path.insert(0, os.path.join(ROOT, "3d-gan_b200"))
+    from b200conv3d.train import GanStep
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(2)], key=lambda t: t[0])
+    res = [(r[0],) + tuple([torch.from_numpy(a) for a in part] for part in r[1:]) for r in res]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    # single-process run on the global batch of 4 (losses are batch means -> same gradients)
+    g, d = _nets()
+    step = GanStep(g, d, z_size=4, autocast_dtype=None)
+    torch.manual_seed(100)
+    reals = torch.rand(4, 1, 8, 8, 8) * 2 - 1
+    zs = torch.randn(4, 4, 1, 1, 1)
+    step.noise = lambda n: zs
+    step.D_step(reals)
+    gd = [p.grad.clone() for p in d.parameters()]
+    step.G_step(4)
+    gg = [p.grad.clone() for p in g.parameters()]
+    for r in res:
+        for a, b in zip(r[1], gd):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-6)
+        for a, b in zip(r[2], gg):
+            torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-6)   # D differs by one Adam step only through fp noise
+    for a, b in zip(res[0][3], res[1][3]):
+        torch.testing.assert_close(a, b, rtol=0, atol=0)             # replicas stay bit-identical
