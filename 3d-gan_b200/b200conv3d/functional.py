@@ -203,13 +203,33 @@ def _desc(g, xshape, cout, dtype, algo):
     return d
 
 
+_weights_epoch = [0]
+_hook_installed = [False]
+
+
+def invalidate_packs(*_a, **_k):
+    """Drop every cached packed filter (called after each optimizer step: fused /
+    foreach optimizers update parameters in place WITHOUT bumping ``Tensor._version``,
+    so the version counter alone cannot be trusted)."""
+    _weights_epoch[0] += 1
+
+
+def watch_optimizers():
+    """Register a global optimizer post-step hook that invalidates the packed-filter
+    cache.  Idempotent; called by install(), prepare() and GanStep."""
+    if not _hook_installed[0]:
+        from torch.optim.optimizer import register_optimizer_step_post_hook
+        register_optimizer_step_post_hook(invalidate_packs)
+        _hook_installed[0] = True
+
+
 def _packed_filter(w, desc, pas, dtype):
     """bf16/fp32 streaming copy of a torch-layout filter, cached on the tensor
     object and invalidated by its version counter (optimizer steps bump it;
     spectral-norm weights are fresh tensors every forward, utils.py:13)."""
-    key = (pas, dtype, w.data_ptr(), w._version, desc.transposed)
+    state = (w.data_ptr(), w._version, _weights_epoch[0])
     cache = getattr(w, "_b2c_pack", None)
-    if cache is not None and cache[0] == key[2:4] and (pas, dtype) in cache[1]:
+    if cache is not None and cache[0] == state and (pas, dtype) in cache[1]:
         return cache[1][(pas, dtype)]
     wf = w.detach()
     if wf.dtype != torch.float32:
@@ -222,8 +242,8 @@ def _packed_filter(w, desc, pas, dtype):
     with _dev(w):
         check(L.b2c_filter_pack(C.byref(desc), pas, _ptr(wf), _ptr(out), _stream(w)), "filter_pack")
     try:
-        if cache is None or cache[0] != key[2:4]:
-            cache = (key[2:4], {})
+        if cache is None or cache[0] != state:
+            cache = (state, {})
             w._b2c_pack = cache
         cache[1][(pas, dtype)] = out
     except AttributeError:

@@ -46,6 +46,7 @@ def install():
         setattr(tnn, name, ours)
     TF.conv3d = _f_conv3d
     TF.conv_transpose3d = _f_conv_transpose3d
+    BF.watch_optimizers()
     _installed[0] = True
 
 
@@ -121,6 +122,7 @@ def fuse(model):
 
 def prepare(model, do_fuse=True):
     """convert + fuse; returns the model."""
+    BF.watch_optimizers()
     convert(model)
     if do_fuse:
         fuse(model)

@@ -20,6 +20,8 @@ import torch.optim as optim
 class GanStep:
     def __init__(self, netG, netD, z_size=512, lrG=5e-5, lrD=1e-4, hinge=False, iterD=2,
                  autocast_dtype=torch.bfloat16, reducer_g=None, reducer_d=None, seed=None):
+        from . import functional as BF
+        BF.watch_optimizers()          # fused Adam does not bump Tensor._version (packed-filter cache)
         self.netG, self.netD = netG, netD
         self.z_size, self.hinge, self.iterD = z_size, hinge, iterD
         self.device = next(netG.parameters()).device

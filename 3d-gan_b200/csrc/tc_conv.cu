@@ -35,6 +35,7 @@ struct alignas(64) TcConvParams {
   int32_t mt, split_dim, sub_ext;
   int32_t nout, block_n, tiles_n, kchunks;
   int32_t num_tiles;
+  int32_t interleave;    // all sub-problems have identical tile grids: order tiles spatial-major, phase-minor
   int32_t stages;
   uint32_t idesc, tmem_cols;
   const float* bias;
@@ -62,11 +63,18 @@ __device__ __forceinline__ TileCoord decode_tile(const TcConvParams& P, int tile
   TileCoord c;
   c.nt = tile % P.tiles_n;
   const int mtile = tile / P.tiles_n;
-  int si = 0;
-  for (int s = 1; s < P.nsubs; s++) if (mtile >= P.subs[s].tile0) si = s;
+  int si = 0, local;
+  if (P.interleave) {
+    // the stride^3 sub-pixel phases of one spatial tile read the same input voxels:
+    // run them back to back so the input is fetched from HBM once, not once per phase
+    si = mtile % P.nsubs;
+    local = mtile / P.nsubs;
+  } else {
+    for (int s = 1; s < P.nsubs; s++) if (mtile >= P.subs[s].tile0) si = s;
+    local = mtile - P.subs[si].tile0;
+  }
   c.si = si;
   const SubDesc& sub = P.subs[si];
-  int local = mtile - sub.tile0;
   const int tw = local % sub.tiles[3]; local /= sub.tiles[3];
   const int th = local % sub.tiles[2]; local /= sub.tiles[2];
   const int td = local % sub.tiles[1]; local /= sub.tiles[1];
@@ -406,19 +414,28 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
 }
 
 // dw[(a*B + b)*T + t] = sum_split ws[split][tapidx(t)][a][b]   (0 when the tap only sees padding)
+// A block owns 32 consecutive (a,b) pairs: partials are read coalesced along (a,b) per tap,
+// staged in shared memory, and written back coalesced along the torch layout (t fastest).
 struct TapIndex { int16_t idx[kMaxTaps]; };
+constexpr int kRedAB = 32;
 __global__ void __launch_bounds__(256)
-wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int A, int B, int T, int ntaps, int splits,
+wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int64_t plane, int T, int ntaps, int splits,
                     TapIndex ti) {
-  const int64_t ab = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (ab >= (int64_t)A * B) return;
-  const int64_t plane = (int64_t)A * B;
-  for (int t = 0; t < T; t++) {
+  extern __shared__ float red_sm[];            // [kRedAB][T + 1]
+  const int64_t ab0 = (int64_t)blockIdx.x * kRedAB;
+  const int nab = plane - ab0 < kRedAB ? (int)(plane - ab0) : kRedAB;
+  for (int i = threadIdx.x; i < kRedAB * T; i += blockDim.x) {
+    const int t = i / kRedAB, a = i % kRedAB;
     float acc = 0.f;
     const int idx = ti.idx[t];
-    if (idx >= 0)
-      for (int s = 0; s < splits; s++) acc += ws[((int64_t)s * ntaps + idx) * plane + ab];
-    dw[ab * T + t] = acc;
+    if (idx >= 0 && a < nab)
+      for (int s = 0; s < splits; s++) acc += ws[((int64_t)s * ntaps + idx) * plane + ab0 + a];
+    red_sm[a * (T + 1) + t] = acc;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nab * T; i += blockDim.x) {
+    const int a = i / T, t = i - a * T;
+    dw[ab0 * T + i] = red_sm[a * (T + 1) + t];
   }
 }
 
@@ -523,6 +540,9 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   if (tiles <= 0) return B2C_OK;
   if (tiles > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
   P.num_tiles = (int32_t)tiles;
+  P.interleave = p.nsubs > 1;
+  for (int s2 = 1; s2 < p.nsubs; s2++)
+    for (int i = 0; i < 4; i++) if (p.subs[s2].tiles[i] != p.subs[0].tiles[i]) P.interleave = 0;
   const int sms = num_sms();
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
   tc_conv_kernel<<<grid, kThreadsTc, smem, st>>>(P);
@@ -620,7 +640,8 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
   for (int t = 0; t < kMaxTaps; t++) ti.idx[t] = -1;
   for (int i = 0; i < c.plan.ntaps_total; i++) ti.idx[c.plan.taps[i].wtap] = (int16_t)i;
   const int64_t ab = (int64_t)g.sc * g.bc;
-  wgrad_reduce_kernel<<<(unsigned)cdiv(ab, 256), 256, 0, st>>>(P.ws, dw, g.sc, g.bc, T, P.ntaps, c.splits, ti);
+  wgrad_reduce_kernel<<<(unsigned)cdiv(ab, kRedAB), 256, kRedAB * (T + 1) * sizeof(float), st>>>(P.ws, dw, ab, T, P.ntaps,
+                                                                                             c.splits, ti);
   return launched();
 }
 
