@@ -59,12 +59,19 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 struct TileCoord { int si, nt, q[4], iters; };
 
-__device__ __forceinline__ TileCoord decode_tile(const TcConvParams& P, int tile) {
+// NCTA == 2: `tile` indexes PAIR tiles; the two CTAs of a pair take M tiles 2j and 2j+1 of
+// the same sub-problem and the same N tile (an odd last one is fully out of range: TMA
+// zero-fills its loads and clips its stores).
+template <int NCTA>
+__device__ __forceinline__ TileCoord decode_tile(const TcConvParams& P, int tile, int rank) {
   TileCoord c;
   c.nt = tile % P.tiles_n;
   const int mtile = tile / P.tiles_n;
   int si = 0, local;
-  if (P.interleave) {
+  if (NCTA == 2) {
+    si = P.nsubs > 1 ? mtile % P.nsubs : 0;
+    local = 2 * (P.nsubs > 1 ? mtile / P.nsubs : mtile) + rank;
+  } else if (P.interleave) {
     // the stride^3 sub-pixel phases of one spatial tile read the same input voxels:
     // run them back to back so the input is fetched from HBM once, not once per phase
     si = mtile % P.nsubs;
@@ -92,14 +99,19 @@ constexpr int kEpiThreads = 128;
 //               tile i overlaps the main loop of tile i+1
 //   warps 2..5  epilogue: TMEM -> registers -> bias/activation -> bf16 -> swizzled smem
 //               slab -> TMA store (coalesced, clipped at the tensor edge)
+template <int NCTA>
 __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_constant__ TcConvParams P) {
   extern __shared__ uint8_t smem_raw[];
+  const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;     // rank 0 = leader: issues every MMA of the pair
+  const int first_tile = NCTA == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_step = NCTA == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t sbase = (raw + 1023u) & ~1023u;               // SW128 needs 1024-B alignment
   uint8_t* sgen = smem_raw + (sbase - raw);
   const int stages = P.stages;
   const uint32_t a_bytes = (uint32_t)P.mt * kABytes;
-  const uint32_t b_bytes = (uint32_t)P.block_n * 128u;
+  const uint32_t b_rows = (uint32_t)P.block_n / NCTA;          // pair: each CTA stages half of the filter tile
+  const uint32_t b_bytes = b_rows * 128u;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t staging = sbase + stages * stage_bytes;
   const uint32_t bar0 = staging + kStagingBytes;                // full[stages], empty[stages], tfull[2], tempty[2]
@@ -113,18 +125,19 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < stages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; a++) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), kEpiThreads / 32); }
+    for (int a = 0; a < 2; a++) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), NCTA * kEpiThreads / 32); }
     fence_barrier_init();
     prefetch_tmap(&P.w_map);
     prefetch_tmap(&P.in_maps[0]);
     prefetch_tmap(&P.out_maps[0]);
   }
   if (warp == 1) {
-    tmem_alloc(smem_u32(tmem_slot), P.tmem_cols);
-    tmem_relinquish();
+    if (NCTA == 2) { tmem_alloc_pair(smem_u32(tmem_slot), P.tmem_cols); tmem_relinquish_pair(); }
+    else { tmem_alloc(smem_u32(tmem_slot), P.tmem_cols); tmem_relinquish(); }
   }
   tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) cluster_sync_all();      // peer barriers are initialised before anyone signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   const uint32_t acc_cols = (uint32_t)P.mt * (uint32_t)P.block_n;
@@ -134,8 +147,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
     if (lane == 0) {
       uint32_t it = 0;
       bool ok = true;
-      for (int tile = blockIdx.x; tile < P.num_tiles && ok; tile += gridDim.x) {
-        const TileCoord c = decode_tile(P, tile);
+      for (int tile = first_tile; tile < P.num_tiles && ok; tile += tile_step) {
+        const TileCoord c = decode_tile<NCTA>(P, tile, rank);
         const SubDesc& sub = P.subs[c.si];
         for (int t = 0; t < sub.ntaps && ok; t++) {
           const TapDesc tp = P.taps[sub.tap0 + t];
@@ -144,44 +157,62 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
             const uint32_t s = it % stages;
             const uint32_t ph = (it / stages) & 1u;
             if (!mbar_wait(empty_bar(s), ph ^ 1u)) { ok = false; break; }
-            mbar_arrive_expect_tx(full_bar(s), stage_bytes);
             const uint32_t a_dst = sbase + s * stage_bytes;
-            tma_load_5d(a_dst, im, full_bar(s), kc * kBlockK, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
-                        c.q[1] + tp.off_d, c.q[0]);
-            tma_load_3d(a_dst + a_bytes, &P.w_map, full_bar(s), kc * kBlockK, c.nt * P.block_n, tp.wtap);
+            if (NCTA == 2) {
+              // both CTAs of the pair complete the LEADER's full barrier; only the leader arms it
+              const uint32_t fb = mapa_u32(full_bar(s), 0);
+              if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * stage_bytes);
+              tma_load_5d_pair(a_dst, im, fb, kc * kBlockK, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
+                               c.q[1] + tp.off_d, c.q[0]);
+              tma_load_3d_pair(a_dst + a_bytes, &P.w_map, fb, kc * kBlockK, c.nt * P.block_n + rank * (int)b_rows,
+                               tp.wtap);
+            } else {
+              mbar_arrive_expect_tx(full_bar(s), stage_bytes);
+              tma_load_5d(a_dst, im, full_bar(s), kc * kBlockK, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
+                          c.q[1] + tp.off_d, c.q[0]);
+              tma_load_3d(a_dst + a_bytes, &P.w_map, full_bar(s), kc * kBlockK, c.nt * P.block_n, tp.wtap);
+            }
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (single thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer (single thread; in a pair only the leader CTA issues) =====
+    if (lane == 0 && rank == 0) {
       constexpr uint64_t hi = smem_desc_hi(16, 1024, 2);         // K-major, SWIZZLE_128B
       uint32_t it = 0, tcount = 0;
       bool ok = true;
-      for (int tile = blockIdx.x; tile < P.num_tiles && ok; tile += gridDim.x, tcount++) {
-        const TileCoord c = decode_tile(P, tile);
+      for (int tile = first_tile; tile < P.num_tiles && ok; tile += tile_step, tcount++) {
+        const TileCoord c = decode_tile<NCTA>(P, tile, 0);
         const uint32_t acc = tcount & 1u;
         const uint32_t aph = (tcount >> 1) & 1u;
-        ok = mbar_wait(tempty_bar(acc), aph ^ 1u);               // epilogue has drained this accumulator set
+        // the epilogues (of both CTAs) have drained this accumulator set
+        ok = NCTA == 2 ? mbar_wait_cluster(tempty_bar(acc), aph ^ 1u) : mbar_wait(tempty_bar(acc), aph ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * acc_cols;
         for (int i = 0; i < c.iters && ok; i++, it++) {
           const uint32_t s = it % stages;
           const uint32_t ph = (it / stages) & 1u;
-          ok = mbar_wait(full_bar(s), ph);
+          ok = NCTA == 2 ? mbar_wait_cluster(full_bar(s), ph) : mbar_wait(full_bar(s), ph);
           tc_fence_after();
           const uint32_t a_addr = sbase + s * stage_bytes, b_addr = a_addr + a_bytes;
           for (int m = 0; m < P.mt; m++) {
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; k++)
-              umma_f16(d_tmem + m * P.block_n, smem_desc(a_addr + m * kABytes + k * 32, hi),
-                       smem_desc(b_addr + k * 32, hi), P.idesc, (i | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kBlockK / 16; k++) {
+              const uint64_t ad = smem_desc(a_addr + m * kABytes + k * 32, hi), bd = smem_desc(b_addr + k * 32, hi);
+              if (NCTA == 2) umma_f16_pair(d_tmem + m * P.block_n, ad, bd, P.idesc, (i | k) != 0 ? 1u : 0u);
+              else umma_f16(d_tmem + m * P.block_n, ad, bd, P.idesc, (i | k) != 0 ? 1u : 0u);
+            }
           }
-          umma_commit(empty_bar(s));       // frees the smem slot when these MMAs retire
+          // frees the smem slot (in both CTAs of a pair) when these MMAs retire
+          if (NCTA == 2) umma_commit_pair(empty_bar(s)); else umma_commit(empty_bar(s));
         }
-        if (c.iters > 0) umma_commit(tfull_bar(acc));   // accumulator complete
-        else mbar_arrive(tfull_bar(acc));
+        if (c.iters > 0) {                   // accumulator complete
+          if (NCTA == 2) umma_commit_pair(tfull_bar(acc)); else umma_commit(tfull_bar(acc));
+        } else {
+          mbar_arrive(tfull_bar(acc));
+          if (NCTA == 2) mbar_arrive_cluster(mapa_u32(tfull_bar(acc), 1));
+        }
       }
     }
   } else {
@@ -193,11 +224,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
     uint32_t tcount = 0, slab_count = 0;
     // A failed (timed-out) wait only raises g_tc_error: the loop is never left early, so the
     // named barriers of the 128 epilogue threads stay matched and the kernel drains.
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, tcount++) {
-      const TileCoord c = decode_tile(P, tile);
+    for (int tile = first_tile; tile < P.num_tiles; tile += tile_step, tcount++) {
+      const TileCoord c = decode_tile<NCTA>(P, tile, rank);
       const uint32_t acc = tcount & 1u;
       const uint32_t aph = (tcount >> 1) & 1u;
-      mbar_wait(tfull_bar(acc), aph);
+      if (NCTA == 2) mbar_wait_cluster(tfull_bar(acc), aph); else mbar_wait(tfull_bar(acc), aph);
       tc_fence_after();
       const CUtensorMap* om = &P.out_maps[c.si];
       const int nslab = (P.block_n + 63) >> 6;
@@ -267,15 +298,22 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
       // all TMEM reads of this accumulator set are complete (tmem_ld_wait above)
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (lane == 0) {
+        if (NCTA == 2) mbar_arrive_cluster(mapa_u32(tempty_bar(acc), 0));   // the leader's barrier counts both CTAs
+        else mbar_arrive(tempty_bar(acc));
+      }
     }
     if (et == 0) tma_store_wait<0>();
   }
 
   // ---- teardown --------------------------------------------------------------
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, P.tmem_cols);
+  if (NCTA == 2) cluster_sync_all();      // the peer may still read this CTA's smem / signal its barriers
+  else __syncthreads();
+  if (warp == 1) {
+    if (NCTA == 2) tmem_dealloc_pair(tmem_base, P.tmem_cols);
+    else tmem_dealloc(tmem_base, P.tmem_cols);
+  }
 }
 
 
@@ -298,7 +336,8 @@ struct alignas(64) TcWgradParams {
   int32_t ntaps;
   int32_t box[4], tiles[4];          // voxel tile box (product 64) and counts over {n,d,h,w}
   int32_t ktiles, ktiles_per_split, splits;
-  int32_t a_ch, b_ch, a_tiles, b_tiles, block_n;
+  int32_t a_ch, b_ch, a_tiles, b_tiles, block_n;   // M side (128-row tiles) / N side (block_n columns)
+  int32_t m_big;                     // 1: M side = big tensor (tap-shifted), N side = small tensor
   int32_t stages;
   uint32_t idesc, tmem_cols;
   float* ws;
@@ -357,11 +396,16 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
         if (!mbar_wait(empty_bar(s), ph ^ 1u)) break;
         mbar_arrive_expect_tx(full_bar(s), stage_bytes);
         const uint32_t a_dst = sbase + s * stage_bytes;
+        // the big tensor is read at the tap-shifted voxel box, the small one at the box itself
+        const CUtensorMap* mm = P.m_big ? bm : &P.s_map;
+        const CUtensorMap* nm = P.m_big ? &P.s_map : bm;
+        const int mw = P.m_big ? tp.off_w : 0, mh = P.m_big ? tp.off_h : 0, md = P.m_big ? tp.off_d : 0;
+        const int nw = tp.off_w - mw, nh = tp.off_h - mh, nd = tp.off_d - md;
         for (int j = 0; j < 2; j++)
-          tma_load_5d(a_dst + j * kSlabBytes, &P.s_map, full_bar(s), at * 128 + j * 64, q0w, q0h, q0d, q0n);
+          tma_load_5d(a_dst + j * kSlabBytes, mm, full_bar(s), at * 128 + j * 64, q0w + mw, q0h + mh, q0d + md, q0n);
         for (int j = 0; j < b_slabs; j++)
-          tma_load_5d(a_dst + a_bytes + j * kSlabBytes, bm, full_bar(s), bt * P.block_n + j * 64, q0w + tp.off_w,
-                      q0h + tp.off_h, q0d + tp.off_d, q0n);
+          tma_load_5d(a_dst + a_bytes + j * kSlabBytes, nm, full_bar(s), bt * P.block_n + j * 64, q0w + nw, q0h + nh,
+                      q0d + nd, q0n);
       }
     }
   } else if (warp == 1) {
@@ -413,29 +457,32 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
   if (warp == 1) tmem_dealloc(tmem_base, P.tmem_cols);
 }
 
-// dw[(a*B + b)*T + t] = sum_split ws[split][tapidx(t)][a][b]   (0 when the tap only sees padding)
-// A block owns 32 consecutive (a,b) pairs: partials are read coalesced along (a,b) per tap,
-// staged in shared memory, and written back coalesced along the torch layout (t fastest).
+// dw[(a*B + b)*T + t] = sum_split ws[split][tapidx(t)][m][n]   (0 when the tap only sees padding)
+// where (m, n) = (a, b), or (b, a) when the GEMM ran with the big tensor on the M side.
+// A block owns 32 consecutive (m,n) pairs: partials are read coalesced along (m,n) per tap,
+// staged in shared memory, and written back as runs of T contiguous floats (t fastest).
 struct TapIndex { int16_t idx[kMaxTaps]; };
 constexpr int kRedAB = 32;
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int64_t plane, int T, int ntaps, int splits,
-                    TapIndex ti) {
+                    int m_big, int n_ch, int big_ch, TapIndex ti) {
   extern __shared__ float red_sm[];            // [kRedAB][T + 1]
-  const int64_t ab0 = (int64_t)blockIdx.x * kRedAB;
-  const int nab = plane - ab0 < kRedAB ? (int)(plane - ab0) : kRedAB;
+  const int64_t mn0 = (int64_t)blockIdx.x * kRedAB;
+  const int nmn = plane - mn0 < kRedAB ? (int)(plane - mn0) : kRedAB;
   for (int i = threadIdx.x; i < kRedAB * T; i += blockDim.x) {
     const int t = i / kRedAB, a = i % kRedAB;
     float acc = 0.f;
     const int idx = ti.idx[t];
-    if (idx >= 0 && a < nab)
-      for (int s = 0; s < splits; s++) acc += ws[((int64_t)s * ntaps + idx) * plane + ab0 + a];
+    if (idx >= 0 && a < nmn)
+      for (int s = 0; s < splits; s++) acc += ws[((int64_t)s * ntaps + idx) * plane + mn0 + a];
     red_sm[a * (T + 1) + t] = acc;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < nab * T; i += blockDim.x) {
-    const int a = i / T, t = i - a * T;
-    dw[ab0 * T + i] = red_sm[a * (T + 1) + t];
+  for (int i = threadIdx.x; i < nmn * T; i += blockDim.x) {
+    const int q = i / T, t = i - q * T;
+    int64_t ab = mn0 + q;                      // (a*B + b) when M = small
+    if (m_big) { const int64_t m = ab / n_ch, n = ab - m * n_ch; ab = n * big_ch + m; }   // m = b, n = a
+    dw[ab * T + t] = red_sm[q * (T + 1) + t];
   }
 }
 
@@ -507,12 +554,21 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
     int rc = encode_map(&P.out_maps[s], out, om, 5, obox);
     if (rc) return rc;
   }
+  // CTA pairs (cta_group::2): two M tiles of one sub-problem share the filter tile, each CTA
+  // staging half of it -> 1.5x fewer L2->SM bytes per FLOP and deeper pipelines.
+  int uniform = 1;
+  for (int s2 = 1; s2 < p.nsubs; s2++)
+    for (int i = 0; i < 4; i++) if (p.subs[s2].tiles[i] != p.subs[0].tiles[i]) uniform = 0;
+  const int64_t sub_tiles = (int64_t)p.subs[0].tiles[0] * p.subs[0].tiles[1] * p.subs[0].tiles[2] * p.subs[0].tiles[3];
+  static const bool no_pair = getenv("B2C_PAIR") == nullptr;   // measured: no gain yet (r1e) -> opt-in
+  const bool pair = !no_pair && uniform && sub_tiles >= 2 && p.block_n % 32 == 0;
+  const int ncta = pair ? 2 : 1;
   MapDesc wm;
   wm.base = 0;
   const int T = [&] { int mx = 0; for (int i = 0; i < p.ntaps_total; i++) if (p.taps[i].wtap > mx) mx = p.taps[i].wtap; return mx + 1; }();
   wm.dims[0] = p.kin; wm.dims[1] = p.nout; wm.dims[2] = T;
   wm.strides[0] = 1; wm.strides[1] = p.kin; wm.strides[2] = (int64_t)p.kin * p.nout;
-  const int wbox[3] = {kBlockK, p.block_n, 1};
+  const int wbox[3] = {kBlockK, p.block_n / ncta, 1};
   int rc = encode_map(&P.w_map, w, wm, 3, wbox);
   if (rc) return rc;
   memcpy(P.subs, p.subs, sizeof(P.subs));
@@ -521,36 +577,49 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   for (int i = 0; i < 4; i++) P.box[i] = p.box[i];
   P.mt = p.mt; P.split_dim = p.split_dim; P.sub_ext = p.sub_ext;
   P.nout = p.nout; P.block_n = p.block_n; P.tiles_n = p.tiles_n; P.kchunks = p.kchunks;
-  const uint32_t stage_bytes = (uint32_t)p.mt * kABytes + (uint32_t)p.block_n * 128u;
+  const uint32_t stage_bytes = (uint32_t)p.mt * kABytes + (uint32_t)(p.block_n / ncta) * 128u;
   const int fixed = 1024 /*alignment slack*/ + (int)kStagingBytes + 256 /*barriers + tmem slot*/;
   int stages = (kSmemBudget - fixed) / (int)stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return B2C_ERR_UNSUPPORTED;
   P.stages = stages;
-  P.idesc = idesc_bf16(kBlockM, p.block_n, 0, 0);
+  P.idesc = idesc_bf16(kBlockM * ncta, p.block_n, 0, 0);
   P.tmem_cols = tmem_cols_for(2 * p.mt * p.block_n);
   if (P.tmem_cols > 512) return B2C_ERR_UNSUPPORTED;
   P.bias = bias; P.bias_mod = bias_mod > 0 ? bias_mod : p.nout; P.act = act; P.slope = slope;
-  { const char* e = getenv("B2C_DBG"); P.dbg = e ? atoi(e) : 0; }
   const size_t smem = (size_t)stages * stage_bytes + fixed;
-  // the attribute is per device; set it on every call (cheap) rather than caching per device
-  if (cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
-    return B2C_ERR_CUDA;
-  const int64_t tiles = (int64_t)p.m_tiles * p.tiles_n;
+  const int64_t tiles = pair ? (int64_t)p.nsubs * ((sub_tiles + 1) / 2) * p.tiles_n : (int64_t)p.m_tiles * p.tiles_n;
   if (tiles <= 0) return B2C_OK;
   if (tiles > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
   P.num_tiles = (int32_t)tiles;
-  P.interleave = p.nsubs > 1;
-  for (int s2 = 1; s2 < p.nsubs; s2++)
-    for (int i = 0; i < 4; i++) if (p.subs[s2].tiles[i] != p.subs[0].tiles[i]) P.interleave = 0;
+  P.interleave = p.nsubs > 1 && uniform;
   const int sms = num_sms();
+  // the attribute is per device; set it on every call (cheap) rather than caching per device
+  if (pair) {
+    if (cudaFuncSetAttribute(tc_conv_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
+      return B2C_ERR_CUDA;
+    const int64_t clusters = tiles < sms / 2 ? tiles : sms / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * clusters));
+    cfg.blockDim = dim3(kThreadsTc);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    if (cudaLaunchKernelEx(&cfg, tc_conv_kernel<2>, P) != cudaSuccess) { cudaGetLastError(); return B2C_ERR_CUDA; }
+    return launched();
+  }
+  if (cudaFuncSetAttribute(tc_conv_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
+    return B2C_ERR_CUDA;
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-  tc_conv_kernel<<<grid, kThreadsTc, smem, st>>>(P);
+  tc_conv_kernel<1><<<grid, kThreadsTc, smem, st>>>(P);
   return launched();
 }
 
 // ---- wgrad ---------------------------------------------------------------------
-struct WgradCfg { ConvPlan plan; int box[4], tiles[4]; int ktiles, splits, kps, a_tiles, b_tiles, block_n; };
+struct WgradCfg { ConvPlan plan; int box[4], tiles[4]; int ktiles, splits, kps, a_tiles, b_tiles, block_n, m_big, m_ch, n_ch; };
 
 static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   if (g.sc % 8 != 0 || g.bc % 8 != 0 || g.sc < 16 || g.bc < 16) return B2C_ERR_UNSUPPORTED;
@@ -568,14 +637,30 @@ static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   for (int i = 0; i < 4; i++) { c->tiles[i] = (ext[i] + c->box[i] - 1) / c->box[i]; kt *= c->tiles[i]; }
   if (kt > 0x7fffffff) return B2C_ERR_UNSUPPORTED;
   c->ktiles = (int)kt;
-  int bn = ((g.bc + 63) / 64) * 64;
-  if (bn > 256) bn = 256;
+  // Which tensor's channels sit on N (<= 256 columns per tile)?  The wider N tile wins: a
+  // 128 x 256 tile moves 2/3 of the L2 bytes per FLOP of a 128 x 128 one.
+  auto ru64 = [](int v) { int r = (v + 63) / 64 * 64; return r > 256 ? 256 : r; };
+  c->m_big = ru64(g.sc) > ru64(g.bc) ? 1 : 0;
+  c->m_ch = c->m_big ? g.bc : g.sc;
+  c->n_ch = c->m_big ? g.sc : g.bc;
+  const int bn = ru64(c->n_ch);
   c->block_n = bn;
-  c->a_tiles = (g.sc + 127) / 128;
-  c->b_tiles = (g.bc + bn - 1) / bn;
+  c->a_tiles = (c->m_ch + 127) / 128;
+  c->b_tiles = (c->n_ch + bn - 1) / bn;
   const int64_t units = (int64_t)c->plan.ntaps_total * c->a_tiles * c->b_tiles;
   if (units <= 0) return B2C_ERR_UNSUPPORTED;
-  int64_t splits = cdiv((int64_t)num_sms() * 3, units);
+  // split-K count: fill 2.5 .. 5 waves of the SMs and pick the count whose last wave is fullest
+  const int sms = num_sms();
+  int64_t splits = 1;
+  {
+    double best = -1.0;
+    const int64_t lo = cdiv((int64_t)sms * 5 / 2, units), hi = cdiv((int64_t)sms * 5, units);
+    for (int64_t sp = lo < 1 ? 1 : lo; sp <= (hi < 1 ? 1 : hi); sp++) {
+      const double waves = (double)(units * sp) / sms;
+      const double eff = waves / (double)cdiv(units * sp, sms);
+      if (eff > best + 0.02) { best = eff; splits = sp; }
+    }
+  }
   if (splits > c->ktiles) splits = c->ktiles;
   // bound the fp32 partial buffer to 1 GiB
   const int64_t plane = (int64_t)c->plan.ntaps_total * g.sc * g.bc * 4;
@@ -620,7 +705,8 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
   P.ntaps = c.plan.ntaps_total;
   for (int i = 0; i < 4; i++) { P.box[i] = c.box[i]; P.tiles[i] = c.tiles[i]; }
   P.ktiles = c.ktiles; P.ktiles_per_split = c.kps; P.splits = c.splits;
-  P.a_ch = g.sc; P.b_ch = g.bc; P.a_tiles = c.a_tiles; P.b_tiles = c.b_tiles; P.block_n = c.block_n;
+  P.a_ch = c.m_ch; P.b_ch = c.n_ch; P.a_tiles = c.a_tiles; P.b_tiles = c.b_tiles; P.block_n = c.block_n;
+  P.m_big = c.m_big;
   const uint32_t stage_bytes = 2 * kSlabBytes + (c.block_n / 64) * kSlabBytes;
   int stages = (kSmemBudget - 1024 - 256) / (int)stage_bytes;
   if (stages > 8) stages = 8;
@@ -641,7 +727,7 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
   for (int i = 0; i < c.plan.ntaps_total; i++) ti.idx[c.plan.taps[i].wtap] = (int16_t)i;
   const int64_t ab = (int64_t)g.sc * g.bc;
   wgrad_reduce_kernel<<<(unsigned)cdiv(ab, kRedAB), 256, kRedAB * (T + 1) * sizeof(float), st>>>(P.ws, dw, ab, T, P.ntaps,
-                                                                                             c.splits, ti);
+                                                                                             c.splits, c.m_big, c.n_ch, g.bc, ti);
   return launched();
 }
 
