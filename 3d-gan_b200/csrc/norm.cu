@@ -10,6 +10,36 @@ namespace b2c {
 constexpr int kThreads = 256;
 constexpr int kBlocksPerSM = 4;
 
+// VEC consecutive fp32 values (offset a multiple of VEC) as 16-byte loads / stores.
+template <int VEC>
+__device__ __forceinline__ void ldvecf(const float* __restrict__ p, int64_t off, float* out, float dflt) {
+  if (!p) {
+#pragma unroll
+    for (int k = 0; k < VEC; k++) out[k] = dflt;
+  } else if (VEC % 4 == 0) {
+#pragma unroll
+    for (int q = 0; q < VEC / 4; q++) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(p + off) + q);
+      out[4 * q] = v.x; out[4 * q + 1] = v.y; out[4 * q + 2] = v.z; out[4 * q + 3] = v.w;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < VEC; k++) out[k] = p[off + k];
+  }
+}
+template <int VEC>
+__device__ __forceinline__ void stvecf(float* __restrict__ p, int64_t off, const float* v) {
+  if (!p) return;
+  if (VEC % 4 == 0) {
+#pragma unroll
+    for (int q = 0; q < VEC / 4; q++)
+      reinterpret_cast<float4*>(p + off)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < VEC; k++) p[off + k] = v[k];
+  }
+}
+
 // ===========================================================================
 // Per-channel two-value reduction over rows of an [rows][C] tensor.
 //   out0[c] = sum_r f0(r,c),  out1[c] = sum_r f1(r,c)
@@ -288,10 +318,12 @@ ln_partial_kernel(const T* __restrict__ x, const T* __restrict__ dy, int64_t L, 
     float xv[VEC], dv[VEC];
     if (VEC > 1) { Vec<T> v; v.load(xs + off); v.unpack(xv); if (BWD) { v.load(ds + off); v.unpack(dv); } }
     else { xv[0] = ldf(xs, off); if (BWD) dv[0] = ldf(ds, off); }
+    float gav[VEC], bev[VEC];
+    if (BWD) { ldvecf<VEC>(gamma, off, gav, 1.f); ldvecf<VEC>(beta, off, bev, 0.f); }
 #pragma unroll
     for (int k = 0; k < VEC; k++) {
       if (BWD) {
-        float ga = gamma ? gamma[off + k] : 1.f, be = beta ? beta[off + k] : 0.f;
+        float ga = gav[k], be = bev[k];
         float xh = (xv[k] - mu) * rs;
         float g = dv[k] * act_dz(xh * ga + be, act, slope) * ga;
         a += g; b += g * xh;
@@ -333,10 +365,12 @@ ln_apply_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t L, int64
     const float mu = mean[n], rs = rstd[n];
     float xv[VEC];
     if (VEC > 1) { Vec<T> v; v.load(x + off); v.unpack(xv); } else xv[0] = ldf(x, off);
+    float gav[VEC], bev[VEC];
+    ldvecf<VEC>(gamma, e, gav, 1.f); ldvecf<VEC>(beta, e, bev, 0.f);
 #pragma unroll
     for (int k = 0; k < VEC; k++) {
       float z = (xv[k] - mu) * rs;
-      z = z * (gamma ? gamma[e + k] : 1.f) + (beta ? beta[e + k] : 0.f);
+      z = z * gav[k] + bev[k];
       xv[k] = act_f(z, act, slope);
     }
     if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(y + off); } else stf(y, off, xv[0]);
@@ -357,10 +391,9 @@ ln_apply_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __rest
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
     const int64_t e = i * VEC;
     float ga[VEC], be[VEC], dg[VEC], db[VEC];
+    ldvecf<VEC>(gamma, e, ga, 1.f); ldvecf<VEC>(beta, e, be, 0.f);
 #pragma unroll
-    for (int k = 0; k < VEC; k++) {
-      ga[k] = gamma ? gamma[e + k] : 1.f; be[k] = beta ? beta[e + k] : 0.f; dg[k] = db[k] = 0.f;
-    }
+    for (int k = 0; k < VEC; k++) dg[k] = db[k] = 0.f;
     for (int n = 0; n < N; n++) {
       const int64_t off = (int64_t)n * L + e;
       const float mu = mean[n], rs = rstd[n], a = mg[n], b = mgx[n];
@@ -376,8 +409,7 @@ ln_apply_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __rest
       }
       if (dx) { if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(dx + off); } else stf(dx, off, xv[0]); }
     }
-#pragma unroll
-    for (int k = 0; k < VEC; k++) { if (dgamma) dgamma[e + k] = dg[k]; if (dbeta) dbeta[e + k] = db[k]; }
+    stvecf<VEC>(dgamma, e, dg); stvecf<VEC>(dbeta, e, db);
   }
 }
 

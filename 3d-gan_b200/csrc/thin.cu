@@ -103,16 +103,85 @@ col2im1_kernel(Geo g, const bf16* __restrict__ col, bf16* __restrict__ big, int 
   big[idx] = __float2bfloat16_rn(act_f(acc, act, slope));
 }
 
+// ---------------------------------------------------------------------------
+// Fast path for k = 4, stride 2, pad 1, dilation 1 (dcgan.py:67 and the data gradient of
+// dcgan.py:161).  Output voxel i = 2j + r (per axis) receives exactly two taps per axis:
+//   a = 0: small voxel j,            tap k = 1 + r
+//   a = 1: small voxel j - 1 + 2r,   tap k = 3 (r = 0) or 0 (r = 1)
+// The GEMM writes its 64 columns in the order t' = a*8 + r (a, r = 3-bit (d,h,w) codes), so
+// that one thread per small voxel j gathers the 2x2x2 output block it owns from the 27
+// neighbouring col rows (L1-resident reuse) and writes coalesced pairs along w.
+__host__ __device__ inline int k4s2_tap(int r, int a) { return r == 0 ? 1 + 2 * a : 2 - 2 * a; }
+__host__ __device__ inline int k4s2_perm(int tp) {          // t' -> torch tap index (kd*4+kh)*4+kw
+  const int a = tp >> 3, r = tp & 7;
+  const int kd = k4s2_tap((r >> 2) & 1, (a >> 2) & 1), kh = k4s2_tap((r >> 1) & 1, (a >> 1) & 1),
+            kw = k4s2_tap(r & 1, a & 1);
+  return (kd * 4 + kh) * 4 + kw;
+}
+
+__global__ void __launch_bounds__(256)
+col2im1_k4s2_kernel(const bf16* __restrict__ col, bf16* __restrict__ big, int n, int sd, int sh, int sw,
+                    const float* __restrict__ bias, int act, float slope) {
+  // block = 4 (h) x 64 (w) small voxels of one (n, d) plane slice
+  const int jw = blockIdx.x * 64 + (threadIdx.x & 63);
+  const int jh = blockIdx.y * 4 + (threadIdx.x >> 6);
+  const int jd = blockIdx.z % sd, in = blockIdx.z / sd;
+  if (jw >= sw || jh >= sh) return;
+  float acc[8];
+  const float b0 = bias ? bias[0] : 0.f;
+#pragma unroll
+  for (int r = 0; r < 8; r++) acc[r] = b0;
+#pragma unroll
+  for (int dd = -1; dd <= 1; dd++) {
+    const int od = jd + dd;
+    if (od < 0 || od >= sd) continue;
+#pragma unroll
+    for (int dh = -1; dh <= 1; dh++) {
+      const int oh = jh + dh;
+      if (oh < 0 || oh >= sh) continue;
+#pragma unroll
+      for (int dw = -1; dw <= 1; dw++) {
+        const int ow = jw + dw;
+        if (ow < 0 || ow >= sw) continue;
+        const bf16* row = col + ((((int64_t)in * sd + od) * sh + oh) * sw + ow) * 64;
+        const int a = ((dd != 0) << 2) | ((dh != 0) << 1) | (dw != 0);
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+          // offset -1 feeds parity 0 only, +1 parity 1 only, 0 feeds both
+          const bool ok = (dd == 0 || ((r >> 2) & 1) == (dd > 0)) && (dh == 0 || ((r >> 1) & 1) == (dh > 0)) &&
+                          (dw == 0 || (r & 1) == (dw > 0));
+          if (ok) acc[r] += __bfloat162float(row[a * 8 + r]);
+        }
+      }
+    }
+  }
+  const int bh = 2 * sh, bw = 2 * sw;
+#pragma unroll
+  for (int rd = 0; rd < 2; rd++)
+#pragma unroll
+    for (int rh = 0; rh < 2; rh++) {
+      const float v0 = act_f(acc[rd * 4 + rh * 2], act, slope), v1 = act_f(acc[rd * 4 + rh * 2 + 1], act, slope);
+      __nv_bfloat162 o = __floats2bfloat162_rn(v0, v1);
+      bf16* dst = big + (((int64_t)in * 2 * sd + 2 * jd + rd) * bh + 2 * jh + rh) * bw + 2 * jw;
+      *reinterpret_cast<__nv_bfloat162*>(dst) = o;
+    }
+}
+
+static bool is_k4s2(const Geo& g) {
+  for (int i = 0; i < 3; i++) if (g.k[i] != 4 || g.s[i] != 2 || g.p[i] != 1 || g.dl[i] != 1) return false;
+  return g.bd == 2 * g.sd && g.bh == 2 * g.sh && g.bw == 2 * g.sw && (int64_t)g.n * g.sd <= 65535;
+}
+
 // packed filters --------------------------------------------------------------
 // gather : wp[a][t]  (Kp columns, zero padded)   = w[a][t]
 // scatter: wp[t][a]  (Kp rows,    zero padded)   = w[a][t]
 __global__ void __launch_bounds__(256)
-thin_pack_kernel(const float* __restrict__ w, bf16* __restrict__ wp, int A, int T, int Kp, int gather) {
+thin_pack_kernel(const float* __restrict__ w, bf16* __restrict__ wp, int A, int T, int Kp, int gather, int k4s2) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)A * Kp) return;
   int a, t;
   if (gather) { a = (int)(idx / Kp); t = (int)(idx % Kp); }
-  else        { t = (int)(idx / A);  a = (int)(idx % A); }
+  else        { t = (int)(idx / A);  a = (int)(idx % A); if (k4s2) t = k4s2_perm(t); }
   wp[idx] = __float2bfloat16_rn(t < T ? w[(int64_t)a * T + t] : 0.f);
 }
 
@@ -138,7 +207,7 @@ int thin_pack(const Geo& g, bool gather, const float* w, void* wp, cudaStream_t 
   const int Kp = thin_kp(g);
   const int64_t n = (int64_t)g.sc * Kp;
   thin_pack_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(w, static_cast<bf16*>(wp), g.sc, g.taps(), Kp,
-                                                          gather ? 1 : 0);
+                                                          gather ? 1 : 0, is_k4s2(g) ? 1 : 0);
   return launched();
 }
 
@@ -202,6 +271,12 @@ int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big,
   if (rc) return rc;
   const int64_t total = (int64_t)g.n * g.bd * g.bh * g.bw;
   if (total == 0) return B2C_OK;
+  if (is_k4s2(g)) {
+    dim3 grid((unsigned)cdiv(g.sw, 64), (unsigned)cdiv(g.sh, 4), (unsigned)(g.n * g.sd));
+    col2im1_k4s2_kernel<<<grid, 256, 0, st>>>(static_cast<const bf16*>(ws), static_cast<bf16*>(out_big), g.n, g.sd,
+                                              g.sh, g.sw, bias, act, slope);
+    return launched();
+  }
   col2im1_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(g, static_cast<const bf16*>(ws),
                                                              static_cast<bf16*>(out_big), Kp, bias, act, slope, total);
   return launched();
