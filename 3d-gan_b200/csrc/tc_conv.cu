@@ -42,6 +42,8 @@ struct alignas(64) TcConvParams {
   int32_t bias_mod;      // bias index = column % bias_mod (point-convT: columns are (tap, co))
   int32_t act;
   float slope;
+  int32_t swap;          // 1: channels on UMMA M (filter tile = A), voxels on N: D^T = W * X^T (narrow Cout)
+  int32_t w_rows;        // filter rows staged per stage
   int32_t dbg;           // B2C_DBG env (diagnostics only): 1 no TMA store, 2 no tcgen05.ld, 4 no st.shared
 };
 
@@ -55,6 +57,26 @@ __device__ __forceinline__ float tanh_approx(float x) {
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// activation over 64 accumulator values: one uniform branch, never a per-element switch
+__device__ __forceinline__ void apply_act64(uint32_t* v, int act, float slope) {
+  if (act == B2C_ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < 64; i++) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
+  } else if (act == B2C_ACT_LRELU) {
+#pragma unroll
+    for (int i = 0; i < 64; i++) {
+      const float x = __uint_as_float(v[i]);
+      v[i] = __float_as_uint(x > 0.f ? x : x * slope);
+    }
+  } else if (act == B2C_ACT_TANH) {
+#pragma unroll
+    for (int i = 0; i < 64; i++) v[i] = __float_as_uint(tanh_approx(__uint_as_float(v[i])));
+  }
+}
+__device__ __forceinline__ void st_shared_b16(uint32_t addr, uint16_t v) {
+  asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
 }
 
 struct TileCoord { int si, nt, q[4], iters; };
@@ -110,7 +132,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
   uint8_t* sgen = smem_raw + (sbase - raw);
   const int stages = P.stages;
   const uint32_t a_bytes = (uint32_t)P.mt * kABytes;
-  const uint32_t b_rows = (uint32_t)P.block_n / NCTA;          // pair: each CTA stages half of the filter tile
+  const uint32_t b_rows = (uint32_t)P.w_rows / NCTA;           // pair: each CTA stages half of the filter tile
   const uint32_t b_bytes = b_rows * 128u;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t staging = sbase + stages * stage_bytes;
@@ -196,6 +218,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
           ok = NCTA == 2 ? mbar_wait_cluster(full_bar(s), ph) : mbar_wait(full_bar(s), ph);
           tc_fence_after();
           const uint32_t a_addr = sbase + s * stage_bytes, b_addr = a_addr + a_bytes;
+          if (P.swap) {
+            // narrow Cout: the filter tile is the M = 128 operand, all 128*mt voxel rows are N
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; k++)
+              umma_f16(d_tmem, smem_desc(b_addr + k * 32, hi), smem_desc(a_addr + k * 32, hi), P.idesc,
+                       (i | k) != 0 ? 1u : 0u);
+          } else
           for (int m = 0; m < P.mt; m++) {
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; k++) {
@@ -232,6 +261,55 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
       tc_fence_after();
       const CUtensorMap* om = &P.out_maps[c.si];
       const int nslab = (P.block_n + 63) >> 6;
+      if (P.swap) {
+        // TMEM lane = output channel, column = voxel: transpose through the two staging slabs
+        // (slab s = channels [64s, 64s+64) of 128 voxel rows, 128-B swizzled like every TMA tile)
+        const int cch = grp * 32 + lane;
+        const int chan = c.nt * 128 + cch;
+        const int nch = P.nout - c.nt * 128 < 128 ? P.nout - c.nt * 128 : 128;
+        const int ns = (nch + 63) >> 6;
+        const bool warp_live = grp * 32 < ns * 64;
+        float bv = 0.f;
+        if (P.bias && chan < P.nout) bv = __ldg(P.bias + chan % P.bias_mod);
+        const uint32_t sdst = staging + (uint32_t)(cch >> 6) * kABytes + (uint32_t)(cch & 7) * 2u;
+        const uint32_t chunk = (uint32_t)(cch & 63) >> 3;
+        for (int m = 0; m < P.mt; m++) {
+          int q[4] = {c.q[0], c.q[1], c.q[2], c.q[3]};
+          q[P.split_dim] += m * P.sub_ext;
+          if (et == 0) tma_store_wait_read<0>();
+          named_bar_sync(1, kEpiThreads);
+          if (warp_live) {
+            for (int h = 0; h < 2; h++) {
+              uint32_t v[64];
+              const uint32_t tcol = tmem_base + lane_off + acc * acc_cols + m * 128 + h * 64;
+              if (c.iters > 0) {
+#pragma unroll
+                for (int g = 0; g < 4; g++) tmem_ld16(tcol + g * 16, v + g * 16);
+                tmem_ld_wait();
+              } else {
+#pragma unroll
+                for (int i = 0; i < 64; i++) v[i] = 0u;
+              }
+#pragma unroll
+              for (int i = 0; i < 64; i++) v[i] = __float_as_uint(__uint_as_float(v[i]) + bv);
+              apply_act64(v, P.act, P.slope);
+#pragma unroll
+              for (int j = 0; j < 64; j++) {
+                const __nv_bfloat16 hv = __float2bfloat16_rn(__uint_as_float(v[j]));
+                st_shared_b16(sdst + (uint32_t)(h * 64 + j) * 128u + ((chunk ^ (uint32_t)(j & 7)) << 4),
+                              *reinterpret_cast<const uint16_t*>(&hv));
+              }
+            }
+          }
+          fence_proxy_async();
+          named_bar_sync(1, kEpiThreads);
+          if (et == 0) {
+            for (int sl = 0; sl < ns; sl++)
+              tma_store_5d(om, staging + sl * kABytes, c.nt * 128 + sl * 64, q[3], q[2], q[1], q[0]);
+            tma_store_commit();
+          }
+        }
+      } else
       for (int m = 0; m < P.mt; m++) {
         int q[4] = {c.q[0], c.q[1], c.q[2], c.q[3]};
         q[P.split_dim] += m * P.sub_ext;
@@ -264,20 +342,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
               }
             }
           }
-          // activation: one uniform branch per slab, never a per-element switch
-          if (P.act == B2C_ACT_RELU) {
-#pragma unroll
-            for (int i = 0; i < 64; i++) v[i] = __float_as_uint(fmaxf(__uint_as_float(v[i]), 0.f));
-          } else if (P.act == B2C_ACT_LRELU) {
-#pragma unroll
-            for (int i = 0; i < 64; i++) {
-              const float x = __uint_as_float(v[i]);
-              v[i] = __float_as_uint(x > 0.f ? x : x * P.slope);
-            }
-          } else if (P.act == B2C_ACT_TANH) {
-#pragma unroll
-            for (int i = 0; i < 64; i++) v[i] = __float_as_uint(tanh_approx(__uint_as_float(v[i])));
-          }
+          apply_act64(v, P.act, P.slope);
 #pragma unroll
           for (int ch = 0; ch < 8; ch++) {
             if (ch * 8 < ncol)
@@ -561,14 +626,15 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
     for (int i = 0; i < 4; i++) if (p.subs[s2].tiles[i] != p.subs[0].tiles[i]) uniform = 0;
   const int64_t sub_tiles = (int64_t)p.subs[0].tiles[0] * p.subs[0].tiles[1] * p.subs[0].tiles[2] * p.subs[0].tiles[3];
   static const bool no_pair = getenv("B2C_PAIR") == nullptr;   // measured: no gain yet (r1e) -> opt-in
-  const bool pair = !no_pair && uniform && sub_tiles >= 2 && p.block_n % 32 == 0;
+  const bool pair = !no_pair && !p.swap && uniform && sub_tiles >= 2 && p.block_n % 32 == 0;
   const int ncta = pair ? 2 : 1;
   MapDesc wm;
   wm.base = 0;
   const int T = [&] { int mx = 0; for (int i = 0; i < p.ntaps_total; i++) if (p.taps[i].wtap > mx) mx = p.taps[i].wtap; return mx + 1; }();
   wm.dims[0] = p.kin; wm.dims[1] = p.nout; wm.dims[2] = T;
   wm.strides[0] = 1; wm.strides[1] = p.kin; wm.strides[2] = (int64_t)p.kin * p.nout;
-  const int wbox[3] = {kBlockK, p.block_n / ncta, 1};
+  const int w_rows = p.swap ? 128 : p.block_n;
+  const int wbox[3] = {kBlockK, w_rows / ncta, 1};
   int rc = encode_map(&P.w_map, w, wm, 3, wbox);
   if (rc) return rc;
   memcpy(P.subs, p.subs, sizeof(P.subs));
@@ -577,13 +643,14 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   for (int i = 0; i < 4; i++) P.box[i] = p.box[i];
   P.mt = p.mt; P.split_dim = p.split_dim; P.sub_ext = p.sub_ext;
   P.nout = p.nout; P.block_n = p.block_n; P.tiles_n = p.tiles_n; P.kchunks = p.kchunks;
-  const uint32_t stage_bytes = (uint32_t)p.mt * kABytes + (uint32_t)(p.block_n / ncta) * 128u;
+  const uint32_t stage_bytes = (uint32_t)p.mt * kABytes + (uint32_t)(w_rows / ncta) * 128u;
+  P.swap = p.swap; P.w_rows = w_rows;
   const int fixed = 1024 /*alignment slack*/ + (int)kStagingBytes + 256 /*barriers + tmem slot*/;
   int stages = (kSmemBudget - fixed) / (int)stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return B2C_ERR_UNSUPPORTED;
   P.stages = stages;
-  P.idesc = idesc_bf16(kBlockM * ncta, p.block_n, 0, 0);
+  P.idesc = p.swap ? idesc_bf16(128, 128 * p.mt, 0, 0) : idesc_bf16(kBlockM * ncta, p.block_n, 0, 0);
   P.tmem_cols = tmem_cols_for(2 * p.mt * p.block_n);
   if (P.tmem_cols > 512) return B2C_ERR_UNSUPPORTED;
   P.bias = bias; P.bias_mod = bias_mod > 0 ? bias_mod : p.nout; P.act = act; P.slope = slope;

@@ -24,6 +24,15 @@ static int finish(ConvPlan* p, int kin, int nout) {
   p->kchunks = (kin + kBlockK - 1) / kBlockK;
   int bn = ((nout + 15) / 16) * 16;
   if (bn > 256) bn = 256;
+  // A UMMA with M = 128 costs about the same for N = 32 .. 128 as for N = 256, so narrow
+  // output-channel counts put the CHANNELS on M (one zero-padded 128-row filter tile) and up
+  // to 256 voxels on N; the epilogue transposes back to NDHWC.
+  // (Short reductions - the K = 64 / 128 GEMMs of the one-channel layers - are epilogue bound and
+  // keep the direct epilogue.)
+  int min_taps = p->nsubs > 0 ? p->subs[0].ntaps : 0;
+  for (int s = 1; s < p->nsubs; s++) if (p->subs[s].ntaps < min_taps) min_taps = p->subs[s].ntaps;
+  p->swap = (bn <= 128 && (int64_t)min_taps * p->kchunks >= 8) ? 1 : 0;
+  if (p->swap) bn = 128;
   p->block_n = bn;
   p->tiles_n = (nout + bn - 1) / bn;
   int ext[4] = {0, 0, 0, 0};
@@ -32,7 +41,7 @@ static int finish(ConvPlan* p, int kin, int nout) {
   // Narrow N tiles are L2-bandwidth bound at 128 rows: give the CTA mt sub-tiles that share
   // every B (filter) stage, keeping mt * block_n fp32 accumulator columns <= 256 so that
   // two accumulator sets (epilogue overlap) fit the 512 TMEM columns.
-  int mt = bn > 128 ? 1 : 2;
+  int mt = bn <= 128 ? 2 : 1;
   int64_t vox = 1;
   for (int i = 0; i < 4; i++) vox *= pow2ceil(ext[i] > 0 ? ext[i] : 1);
   while (mt > 1 && vox < (int64_t)kBlockM * mt) mt >>= 1;

@@ -43,6 +43,7 @@ struct ConvPlan {
   int32_t nmaps, nsubs, ntaps_total;
   int32_t box[4];                // CTA tile box {bn, bd, bh, bw}, product == kBlockM * mt
   int32_t mt;                    // 128-row UMMA sub-tiles per CTA tile (1, 2 or 4); mt * block_n <= 256
+  int32_t swap;                  // 1: nout <= 128 -> channels ride UMMA M (block_n = 128), voxels UMMA N = 128*mt
   int32_t split_dim, sub_ext;    // sub-tile m covers box[split_dim] range [m*sub_ext, (m+1)*sub_ext)
   int32_t kin, nout;             // contracted / produced channels
   int32_t block_n, tiles_n;      // N tile and count
