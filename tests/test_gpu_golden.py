@@ -79,3 +79,34 @@ def test_tensor_core_model_vs_oracle_bf16(width):
     ed = ((dd.float().cpu() - d_ref).abs().max() / d_ref.abs().max()).item()
     assert ef < 4e-2, ef          # 6 stacked bf16 layers with batch-2 BatchNorm: relative L2
     assert ed < 4e-2, ed
+
+
+def test_fid_resnet_vs_reference_golden():
+    """FID_ResNet.resnet50 features (eval_utils.py:41-44) on the product layers, fp32 (exact
+    kernels, 1e-3 through 53 train-mode BatchNorms) and bf16 (tcgen05 path)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "fid_resnet_ref.npz"))
+    import ref_fid_resnet
+    torch.manual_seed(int(g["w_seed"]))
+    ref = ref_fid_resnet.resnet50()
+    m = B.fid_resnet.resnet50()
+    m.load_state_dict(ref.state_dict())
+    m = m.cuda()
+    torch.manual_seed(int(g["x_seed"]))
+    x = torch.randn(2, 1, 32, 32, 32).cuda()
+    with torch.no_grad():
+        y = m(x)
+    assert tuple(y.shape) == tuple(g["y_shape"])
+    assert rel_err(y[:, ::64], torch.from_numpy(g["y_sample"])) < 1e-3
+    f32 = B.fid_resnet.features(m, x)
+    assert rel_err(f32, torch.from_numpy(g["feat"])) < 1e-3
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        fbf = B.fid_resnet.features(m, x)
+    ref_feat = torch.from_numpy(g["feat"])
+    l2 = ((fbf.cpu() - ref_feat).norm() / ref_feat.norm()).item()
+    # 53 stacked bf16 layers with 2-sample train-mode BatchNorm: bounded by what stock torch
+    # bf16 autocast (cuDNN) loses on the same GPU with the same weights
+    wit = ref.cuda()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        fw = wit(x).float().mean(dim=(2, 3, 4))
+    l2w = ((fw.cpu() - ref_feat).norm() / ref_feat.norm()).item()
+    assert l2 < max(4e-2, 1.5 * l2w), (l2, l2w)

@@ -86,3 +86,21 @@ def test_train_phases_match_reference(gold):
                                rtol=1e-4, atol=1e-6)
     np.testing.assert_allclose(sd["main.1.bias"][:, ::16, ::16, ::16].numpy(), gold["d1.ln1_bias_sample"],
                                rtol=1e-4, atol=1e-6)
+
+
+def test_fid_resnet_port_matches_reference():
+    """oracle/ref_fid_resnet.py vs golden of the unmodified FID_ResNet.resnet50 (seed replay)."""
+    import ref_fid_resnet
+    g = np.load(os.path.join(ROOT, "tests", "golden", "fid_resnet_ref.npz"))
+    torch.manual_seed(int(g["w_seed"]))
+    m = ref_fid_resnet.resnet50()
+    sd = m.state_dict()
+    assert abs(sd["conv1.weight"].double().sum().item() - float(g["conv1_w_sum"])) < 1e-9
+    assert abs(sd["layer4.2.conv3.weight"].double().sum().item() - float(g["l4_w_sum"])) < 1e-9
+    torch.manual_seed(int(g["x_seed"]))
+    x = torch.randn(2, 1, 32, 32, 32)
+    with torch.no_grad():
+        y = m(x)
+    assert tuple(y.shape) == tuple(g["y_shape"])
+    np.testing.assert_allclose(y[:, ::64].numpy(), g["y_sample"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(y.mean(dim=(2, 3, 4)).numpy(), g["feat"], rtol=1e-4, atol=1e-5)
