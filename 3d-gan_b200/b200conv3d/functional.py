@@ -207,11 +207,20 @@ _weights_epoch = [0]
 _hook_installed = [False]
 
 
-def invalidate_packs(*_a, **_k):
-    """Drop every cached packed filter (called after each optimizer step: fused /
-    foreach optimizers update parameters in place WITHOUT bumping ``Tensor._version``,
-    so the version counter alone cannot be trusted)."""
-    _weights_epoch[0] += 1
+def invalidate_packs(optimizer=None, *_a, **_k):
+    """Drop the cached packed filters of the parameters an optimizer just stepped (called from
+    a global optimizer post-step hook: fused / foreach optimizers update parameters in place
+    WITHOUT bumping ``Tensor._version``, so the version counter alone cannot be trusted).
+    Parameters of other optimizers keep their packs (G's filters stay packed across the
+    discriminator steps, trainer.py:296-303).  Without an optimizer argument: drop everything."""
+    groups = getattr(optimizer, "param_groups", None)
+    if groups is None:
+        _weights_epoch[0] += 1
+        return
+    for g in groups:
+        for p in g["params"]:
+            if getattr(p, "_b2c_pack", None) is not None:
+                p._b2c_pack = None
 
 
 def watch_optimizers():

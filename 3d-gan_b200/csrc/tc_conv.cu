@@ -716,13 +716,15 @@ static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   c->b_tiles = (c->n_ch + bn - 1) / bn;
   const int64_t units = (int64_t)c->plan.ntaps_total * c->a_tiles * c->b_tiles;
   if (units <= 0) return B2C_ERR_UNSUPPORTED;
-  // split-K count: fill 2.5 .. 5 waves of the SMs and pick the count whose last wave is fullest
+  // split-K count: 2.5 .. 10 waves of the SMs, at least 64 K-iterations per CTA; pick the count
+  // whose last wave is fullest (ties -> fewer splits = less partial-sum traffic)
   const int sms = num_sms();
   int64_t splits = 1;
   {
     double best = -1.0;
-    const int64_t lo = cdiv((int64_t)sms * 5 / 2, units), hi = cdiv((int64_t)sms * 5, units);
+    const int64_t lo = cdiv((int64_t)sms * 5 / 2, units), hi = cdiv((int64_t)sms * 10, units);
     for (int64_t sp = lo < 1 ? 1 : lo; sp <= (hi < 1 ? 1 : hi); sp++) {
+      if (sp > 1 && c->ktiles / sp < 64) break;
       const double waves = (double)(units * sp) / sms;
       const double eff = waves / (double)cdiv(units * sp, sms);
       if (eff > best + 0.02) { best = eff; splits = sp; }

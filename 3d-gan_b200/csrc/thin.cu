@@ -119,42 +119,61 @@ __host__ __device__ inline int k4s2_perm(int tp) {          // t' -> torch tap i
   return (kd * 4 + kh) * 4 + kw;
 }
 
+__device__ __forceinline__ float bf_lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+// One thread per small voxel j, a warp = 32 consecutive jw.  Per (dd, dh) neighbour line each
+// lane reads ONE 32-byte sector of its own col row (groups a0 = (ad,ah,0) and a0+1 = (ad,ah,1));
+// the w-neighbours' contributions (group a0+1 of rows jw-1 / jw+1) come through warp shuffles,
+// only lanes 0 / 31 fetch them from memory.
 __global__ void __launch_bounds__(256)
 col2im1_k4s2_kernel(const bf16* __restrict__ col, bf16* __restrict__ big, int n, int sd, int sh, int sw,
                     const float* __restrict__ bias, int act, float slope) {
-  // block = 4 (h) x 64 (w) small voxels of one (n, d) plane slice
+  const int lane = threadIdx.x & 31;
   const int jw = blockIdx.x * 64 + (threadIdx.x & 63);
   const int jh = blockIdx.y * 4 + (threadIdx.x >> 6);
   const int jd = blockIdx.z % sd, in = blockIdx.z / sd;
-  if (jw >= sw || jh >= sh) return;
+  const bool live = jw < sw && jh < sh;          // jh is warp-uniform
   float acc[8];
   const float b0 = bias ? bias[0] : 0.f;
 #pragma unroll
   for (int r = 0; r < 8; r++) acc[r] = b0;
+  const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
   for (int dd = -1; dd <= 1; dd++) {
     const int od = jd + dd;
-    if (od < 0 || od >= sd) continue;
+    if (od < 0 || od >= sd) continue;              // block-uniform
 #pragma unroll
     for (int dh = -1; dh <= 1; dh++) {
       const int oh = jh + dh;
-      if (oh < 0 || oh >= sh) continue;
+      if (oh < 0 || oh >= sh || jh >= sh) continue;  // warp-uniform
+      const int a0 = ((dd != 0) << 2) | ((dh != 0) << 1);
+      const bf16* line = col + (((int64_t)in * sd + od) * sh + oh) * (int64_t)sw * 64 + a0 * 8;
+      uint4 A0 = zero4, A1 = zero4;
+      if (live) {
+        const uint4* p = reinterpret_cast<const uint4*>(line + (int64_t)jw * 64);
+        A0 = __ldg(p); A1 = __ldg(p + 1);
+      }
+      uint4 L, R;                                   // group a0+1 of rows jw-1 and jw+1
+      L.x = __shfl_up_sync(0xffffffffu, A1.x, 1); L.y = __shfl_up_sync(0xffffffffu, A1.y, 1);
+      L.z = __shfl_up_sync(0xffffffffu, A1.z, 1); L.w = __shfl_up_sync(0xffffffffu, A1.w, 1);
+      R.x = __shfl_down_sync(0xffffffffu, A1.x, 1); R.y = __shfl_down_sync(0xffffffffu, A1.y, 1);
+      R.z = __shfl_down_sync(0xffffffffu, A1.z, 1); R.w = __shfl_down_sync(0xffffffffu, A1.w, 1);
+      if (lane == 0) L = (live && jw > 0) ? __ldg(reinterpret_cast<const uint4*>(line + (int64_t)(jw - 1) * 64) + 1) : zero4;
+      if (lane == 31) R = (live && jw + 1 < sw) ? __ldg(reinterpret_cast<const uint4*>(line + (int64_t)(jw + 1) * 64) + 1) : zero4;
+      if (jw + 1 >= sw) R = zero4;
+      const uint32_t a0v[4] = {A0.x, A0.y, A0.z, A0.w}, lv[4] = {L.x, L.y, L.z, L.w}, rv[4] = {R.x, R.y, R.z, R.w};
 #pragma unroll
-      for (int dw = -1; dw <= 1; dw++) {
-        const int ow = jw + dw;
-        if (ow < 0 || ow >= sw) continue;
-        const bf16* row = col + ((((int64_t)in * sd + od) * sh + oh) * sw + ow) * 64;
-        const int a = ((dd != 0) << 2) | ((dh != 0) << 1) | (dw != 0);
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-          // offset -1 feeds parity 0 only, +1 parity 1 only, 0 feeds both
-          const bool ok = (dd == 0 || ((r >> 2) & 1) == (dd > 0)) && (dh == 0 || ((r >> 1) & 1) == (dh > 0)) &&
-                          (dw == 0 || (r & 1) == (dw > 0));
-          if (ok) acc[r] += __bfloat162float(row[a * 8 + r]);
+      for (int m = 0; m < 4; m++) {                 // m = rd*2 + rh; register m holds (rw = 0 | rw = 1)
+        const bool ok = (dd == 0 || ((m >> 1) & 1) == (dd > 0)) && (dh == 0 || (m & 1) == (dh > 0));
+        if (ok) {
+          acc[2 * m] += bf_lo(a0v[m]) + bf_lo(lv[m]);           // rw = 0: own row (k=1) + row jw-1 (k=3)
+          acc[2 * m + 1] += bf_hi(a0v[m]) + bf_hi(rv[m]);       // rw = 1: own row (k=2) + row jw+1 (k=0)
         }
       }
     }
   }
+  if (!live) return;
   const int bh = 2 * sh, bw = 2 * sw;
 #pragma unroll
   for (int rd = 0; rd < 2; rd++)
