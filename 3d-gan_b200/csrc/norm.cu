@@ -298,42 +298,101 @@ __device__ __forceinline__ void block_sum2(float& a, float& b) {
   __syncthreads();
 }
 
-// grid (chunks, N).  FWD: (sum x, sum x^2).  BWD: (sum g, sum g*xhat), g = dy*act'(z)*gamma.
-template <typename T, int VEC, bool BWD>
+template <typename T, int VEC>
+__device__ __forceinline__ void ldvec(const T* __restrict__ p, int64_t off, float* out) {
+  if (VEC > 1) { Vec<T> v; v.load(p + off); v.unpack(out); } else out[0] = ldf(p, off);
+}
+// a VEC-element load kept packed (16 bytes for bf16 x 8) until it is consumed
+template <typename T, int VEC> struct Pk {
+  Vec<T> v;
+  __device__ __forceinline__ void load(const T* __restrict__ p, int64_t off) { v.load(p + off); }
+  __device__ __forceinline__ void unpack(float* o) const { v.unpack(o); }
+};
+template <typename T> struct Pk<T, 1> {
+  float v;
+  __device__ __forceinline__ void load(const T* __restrict__ p, int64_t off) { v = ldf(p, off); }
+  __device__ __forceinline__ void unpack(float* o) const { o[0] = v; }
+};
+template <typename T, int VEC>
+__device__ __forceinline__ void stvec(T* __restrict__ p, int64_t off, float* v) {
+  if (VEC > 1) { Vec<T> o; o.pack(v); o.store(p + off); } else stf(p, off, v[0]);
+}
+
+// grid (chunks, N): per-chunk (sum x, sum x^2) of one sample.
+template <typename T, int VEC>
 __global__ void __launch_bounds__(kThreads)
-ln_partial_kernel(const T* __restrict__ x, const T* __restrict__ dy, int64_t L, const float* __restrict__ gamma,
-                  const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd,
-                  int act, float slope, float* __restrict__ part) {
+ln_partial_kernel(const T* __restrict__ x, int64_t L, float* __restrict__ part) {
   const int n = blockIdx.y;
   const int64_t nvec = L / VEC;
   const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
   const int64_t v0 = (int64_t)blockIdx.x * per, v1 = v0 + per < nvec ? v0 + per : nvec;
   const T* xs = x + (int64_t)n * L;
-  const T* ds = BWD ? dy + (int64_t)n * L : nullptr;
-  float mu = 0.f, rs = 0.f;
-  if (BWD) { mu = mean[n]; rs = rstd[n]; }
   float a = 0.f, b = 0.f;
   for (int64_t i = v0 + threadIdx.x; i < v1; i += kThreads) {
-    const int64_t off = i * VEC;
-    float xv[VEC], dv[VEC];
-    if (VEC > 1) { Vec<T> v; v.load(xs + off); v.unpack(xv); if (BWD) { v.load(ds + off); v.unpack(dv); } }
-    else { xv[0] = ldf(xs, off); if (BWD) dv[0] = ldf(ds, off); }
-    float gav[VEC], bev[VEC];
-    if (BWD) { ldvecf<VEC>(gamma, off, gav, 1.f); ldvecf<VEC>(beta, off, bev, 0.f); }
+    float xv[VEC];
+    ldvec<T, VEC>(xs, i * VEC, xv);
 #pragma unroll
-    for (int k = 0; k < VEC; k++) {
-      if (BWD) {
-        float ga = gav[k], be = bev[k];
-        float xh = (xv[k] - mu) * rs;
-        float g = dv[k] * act_dz(xh * ga + be, act, slope) * ga;
-        a += g; b += g * xh;
-      } else { a += xv[k]; b += xv[k] * xv[k]; }
-    }
+    for (int k = 0; k < VEC; k++) { a += xv[k]; b += xv[k] * xv[k]; }
   }
   block_sum2(a, b);
   if (threadIdx.x == 0) {
     part[((int64_t)n * gridDim.x + blockIdx.x) * 2] = a;
     part[((int64_t)n * gridDim.x + blockIdx.x) * 2 + 1] = b;
+  }
+}
+
+// Backward statistics (sum g, sum g*xhat), g = dy*act'(z)*gamma.  grid (chunks, ceil(N / kLnGroup)).
+// gamma / beta are fp32 over the whole sample shape (twice the bytes of a bf16 activation), so a
+// thread owns VEC adjacent positions, loads their gamma / beta ONCE and walks kLnGroup samples with
+// per-sample accumulators: affine traffic drops from 8 to 8 / kLnGroup bytes per element.
+constexpr int kLnGroup = 8;
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThreads, 2)
+ln_partial_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, int N, int64_t L,
+                      const float* __restrict__ gamma, const float* __restrict__ beta,
+                      const float* __restrict__ mean, const float* __restrict__ rstd, int act, float slope,
+                      float* __restrict__ part) {
+  const int n0 = blockIdx.y * kLnGroup;
+  const int nn = N - n0 < kLnGroup ? N - n0 : kLnGroup;
+  float a[kLnGroup], b[kLnGroup], mu[kLnGroup], rs[kLnGroup];
+#pragma unroll
+  for (int u = 0; u < kLnGroup; u++) {
+    a[u] = b[u] = 0.f;
+    mu[u] = u < nn ? mean[n0 + u] : 0.f; rs[u] = u < nn ? rstd[n0 + u] : 0.f;
+  }
+  const int64_t nvec = L / VEC;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += stride) {
+    const int64_t e = i * VEC;
+    float ga[VEC], be[VEC];
+    ldvecf<VEC>(gamma, e, ga, 1.f); ldvecf<VEC>(beta, e, be, 0.f);
+#pragma unroll
+    for (int h = 0; h < kLnGroup; h += 4) {
+      Pk<T, VEC> xr[4], dr[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (h + u < nn) { xr[u].load(x, (int64_t)(n0 + h + u) * L + e); dr[u].load(dy, (int64_t)(n0 + h + u) * L + e); }
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (h + u < nn) {
+          float xv[VEC], dv[VEC];
+          xr[u].unpack(xv); dr[u].unpack(dv);
+#pragma unroll
+          for (int k = 0; k < VEC; k++) {
+            const float xh = (xv[k] - mu[h + u]) * rs[h + u];
+            const float g = dv[k] * act_dz(xh * ga[k] + be[k], act, slope) * ga[k];
+            a[h + u] += g; b[h + u] += g * xh;
+          }
+        }
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < kLnGroup; u++) {
+    block_sum2(a[u], b[u]);
+    if (threadIdx.x == 0 && u < nn) {
+      part[((int64_t)(n0 + u) * gridDim.x + blockIdx.x) * 2] = a[u];
+      part[((int64_t)(n0 + u) * gridDim.x + blockIdx.x) * 2 + 1] = b[u];
+    }
   }
 }
 
@@ -352,35 +411,44 @@ __global__ void ln_finalize_kernel(const float* part, int chunks, int N, double 
   }
 }
 
+// grid (position blocks, sample ranges).  A thread owns VEC adjacent positions, loads gamma / beta
+// once and walks its sample range four samples at a time (loads issued before the math).
 template <typename T, int VEC>
 __global__ void __launch_bounds__(kThreads)
-ln_apply_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t L, int64_t nvec_total,
+ln_apply_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int64_t L,
                     const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ mean, const float* __restrict__ rstd, int act, float slope) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec_total; i += stride) {
-    const int64_t off = i * VEC;
-    const int n = (int)(off / L);
-    const int64_t e = off - (int64_t)n * L;
-    const float mu = mean[n], rs = rstd[n];
-    float xv[VEC];
-    if (VEC > 1) { Vec<T> v; v.load(x + off); v.unpack(xv); } else xv[0] = ldf(x, off);
-    float gav[VEC], bev[VEC];
-    ldvecf<VEC>(gamma, e, gav, 1.f); ldvecf<VEC>(beta, e, bev, 0.f);
+  const int per = (N + gridDim.y - 1) / gridDim.y;
+  const int nb = blockIdx.y * per, ne = nb + per < N ? nb + per : N;
+  const int64_t nvec = L / VEC;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += stride) {
+    const int64_t e = i * VEC;
+    float ga[VEC], be[VEC];
+    ldvecf<VEC>(gamma, e, ga, 1.f); ldvecf<VEC>(beta, e, be, 0.f);
+    for (int n0 = nb; n0 < ne; n0 += 4) {
+      Pk<T, VEC> xr[4];
 #pragma unroll
-    for (int k = 0; k < VEC; k++) {
-      float z = (xv[k] - mu) * rs;
-      z = z * gav[k] + bev[k];
-      xv[k] = act_f(z, act, slope);
+      for (int u = 0; u < 4; u++)
+        if (n0 + u < ne) xr[u].load(x, (int64_t)(n0 + u) * L + e);
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (n0 + u < ne) {
+          const float mu = mean[n0 + u], rs = rstd[n0 + u];
+          float xv[VEC];
+          xr[u].unpack(xv);
+#pragma unroll
+          for (int k = 0; k < VEC; k++) xv[k] = act_f((xv[k] - mu) * rs * ga[k] + be[k], act, slope);
+          stvec<T, VEC>(y, (int64_t)(n0 + u) * L + e, xv);
+        }
     }
-    if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(y + off); } else stf(y, off, xv[0]);
   }
 }
 
 // Thread owns VEC adjacent elements e and walks the batch: dx per sample and
 // the full-shape affine gradients dgamma[e], dbeta[e] without atomics.
 template <typename T, int VEC>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 ln_apply_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __restrict__ dx, int N, int64_t L,
                     const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ mean, const float* __restrict__ rstd,
@@ -394,20 +462,27 @@ ln_apply_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __rest
     ldvecf<VEC>(gamma, e, ga, 1.f); ldvecf<VEC>(beta, e, be, 0.f);
 #pragma unroll
     for (int k = 0; k < VEC; k++) dg[k] = db[k] = 0.f;
-    for (int n = 0; n < N; n++) {
-      const int64_t off = (int64_t)n * L + e;
-      const float mu = mean[n], rs = rstd[n], a = mg[n], b = mgx[n];
-      float xv[VEC], dv[VEC];
-      if (VEC > 1) { Vec<T> v; v.load(x + off); v.unpack(xv); v.load(dy + off); v.unpack(dv); }
-      else { xv[0] = ldf(x, off); dv[0] = ldf(dy, off); }
+    for (int n0 = 0; n0 < N; n0 += 4) {
+      Pk<T, VEC> xr[4], dr[4];
 #pragma unroll
-      for (int k = 0; k < VEC; k++) {
-        float xh = (xv[k] - mu) * rs;
-        float g0 = dv[k] * act_dz(xh * ga[k] + be[k], act, slope);
-        dg[k] += g0 * xh; db[k] += g0;
-        xv[k] = rs * (g0 * ga[k] - a - xh * b);
-      }
-      if (dx) { if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(dx + off); } else stf(dx, off, xv[0]); }
+      for (int u = 0; u < 4; u++)
+        if (n0 + u < N) { xr[u].load(x, (int64_t)(n0 + u) * L + e); dr[u].load(dy, (int64_t)(n0 + u) * L + e); }
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (n0 + u < N) {
+          const int n = n0 + u;
+          const float mu = mean[n], rs = rstd[n], a = mg[n], b = mgx[n];
+          float xv[VEC], dv[VEC];
+          xr[u].unpack(xv); dr[u].unpack(dv);
+#pragma unroll
+          for (int k = 0; k < VEC; k++) {
+            float xh = (xv[k] - mu) * rs;
+            float g0 = dv[k] * act_dz(xh * ga[k] + be[k], act, slope);
+            dg[k] += g0 * xh; db[k] += g0;
+            xv[k] = rs * (g0 * ga[k] - a - xh * b);
+          }
+          if (dx) stvec<T, VEC>(dx, (int64_t)n * L + e, xv);
+        }
     }
     stvecf<VEC>(dgamma, e, dg); stvecf<VEC>(dbeta, e, db);
   }
@@ -419,6 +494,23 @@ static int ln_chunks(int64_t N, int64_t L) {
   if (want > maxc) want = maxc;
   return (int)(want < 1 ? 1 : want);
 }
+// backward statistics: position blocks per sample group (two resident blocks per SM)
+static int ln_chunks_bwd(int64_t N, int64_t L) {
+  int64_t want = cdiv((int64_t)num_sms() * 2, cdiv(N, (int64_t)kLnGroup));
+  int64_t maxc = cdiv(L, (int64_t)kThreads * 8);
+  if (want > maxc) want = maxc;
+  return (int)(want < 1 ? 1 : want);
+}
+// (position blocks, sample ranges) for the batch-walking apply kernel
+static dim3 ln_apply_grid(int64_t N, int64_t nvec) {
+  const int64_t target = (int64_t)num_sms() * 8;
+  int64_t bx = cdiv(nvec, kThreads);
+  if (bx > target) bx = target;
+  int64_t by = bx >= target / 2 ? 1 : cdiv(target / 2, bx);
+  const int64_t maxy = cdiv(N, 4);
+  if (by > maxy) by = maxy;
+  return dim3((unsigned)bx, (unsigned)(by < 1 ? 1 : by));
+}
 
 template <typename T>
 static int ln_fwd_t(const void* x, void* y, int64_t N, int64_t L, const float* gamma, const float* beta, float eps,
@@ -429,14 +521,13 @@ static int ln_fwd_t(const void* x, void* y, int64_t N, int64_t L, const float* g
   float* part = static_cast<float*>(ws);
   const bool vec = (L % V == 0) && aligned16(x) && aligned16(y);
   dim3 grid(chunks, (unsigned)N);
-  if (vec) ln_partial_kernel<T, V, false><<<grid, kThreads, 0, st>>>(xp, nullptr, L, nullptr, nullptr, nullptr, nullptr, 0, 0.f, part);
-  else     ln_partial_kernel<T, 1, false><<<grid, kThreads, 0, st>>>(xp, nullptr, L, nullptr, nullptr, nullptr, nullptr, 0, 0.f, part);
+  if (vec) ln_partial_kernel<T, V><<<grid, kThreads, 0, st>>>(xp, L, part);
+  else     ln_partial_kernel<T, 1><<<grid, kThreads, 0, st>>>(xp, L, part);
   int rc = launched(); if (rc) return rc;
   ln_finalize_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(part, chunks, (int)N, 1.0 / (double)L, eps, 0, mean, rstd);
   rc = launched(); if (rc) return rc;
-  const int64_t tot = N * L;
-  if (vec) ln_apply_fwd_kernel<T, V><<<ew_grid(tot / V), kThreads, 0, st>>>(xp, yp, L, tot / V, gamma, beta, mean, rstd, act, slope);
-  else     ln_apply_fwd_kernel<T, 1><<<ew_grid(tot), kThreads, 0, st>>>(xp, yp, L, tot, gamma, beta, mean, rstd, act, slope);
+  if (vec) ln_apply_fwd_kernel<T, V><<<ln_apply_grid(N, L / V), kThreads, 0, st>>>(xp, yp, (int)N, L, gamma, beta, mean, rstd, act, slope);
+  else     ln_apply_fwd_kernel<T, 1><<<ln_apply_grid(N, L), kThreads, 0, st>>>(xp, yp, (int)N, L, gamma, beta, mean, rstd, act, slope);
   return launched();
 }
 
@@ -446,14 +537,14 @@ static int ln_bwd_t(const void* x, const void* dy, void* dx, int64_t N, int64_t 
                     float* dbeta, void* ws, cudaStream_t st) {
   constexpr int V = Vec<T>::N;
   const T* xp = static_cast<const T*>(x); const T* dp = static_cast<const T*>(dy); T* dxp = static_cast<T*>(dx);
-  const int chunks = ln_chunks(N, L);
+  const int chunks = ln_chunks_bwd(N, L);
   float* part = static_cast<float*>(ws);
   float* mg = part + (size_t)N * chunks * 2;
   float* mgx = mg + N;
   const bool vec = (L % V == 0) && aligned16(x) && aligned16(dy) && (!dx || aligned16(dx));
-  dim3 grid(chunks, (unsigned)N);
-  if (vec) ln_partial_kernel<T, V, true><<<grid, kThreads, 0, st>>>(xp, dp, L, gamma, beta, mean, rstd, act, slope, part);
-  else     ln_partial_kernel<T, 1, true><<<grid, kThreads, 0, st>>>(xp, dp, L, gamma, beta, mean, rstd, act, slope, part);
+  dim3 grid(chunks, (unsigned)cdiv(N, (int64_t)kLnGroup));
+  if (vec) ln_partial_bwd_kernel<T, V><<<grid, kThreads, 0, st>>>(xp, dp, (int)N, L, gamma, beta, mean, rstd, act, slope, part);
+  else     ln_partial_bwd_kernel<T, 1><<<grid, kThreads, 0, st>>>(xp, dp, (int)N, L, gamma, beta, mean, rstd, act, slope, part);
   int rc = launched(); if (rc) return rc;
   ln_finalize_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(part, chunks, (int)N, 1.0 / (double)L, 0.f, 1, mg, mgx);
   rc = launched(); if (rc) return rc;
@@ -568,7 +659,8 @@ extern "C" int b2c_bn_act_bwd_apply(const void* x, const void* dy, const void* r
 
 extern "C" size_t b2c_ln_workspace(int64_t N, int64_t L) {
   if (N <= 0 || L <= 0) return 0;
-  return ((size_t)N * ln_chunks(N, L) * 2 + 2 * (size_t)N) * sizeof(float);
+  const int c1 = ln_chunks(N, L), c2 = ln_chunks_bwd(N, L);
+  return ((size_t)N * (c1 > c2 ? c1 : c2) * 2 + 2 * (size_t)N) * sizeof(float);
 }
 
 extern "C" int b2c_ln_act_fwd(const void* x, void* y, int64_t N, int64_t L, int dt, const float* gamma,
