@@ -26,10 +26,11 @@ bool is_point_convT(const b2c_conv_desc* c) {
 int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w, void* out, const float* bias,
              int act, float slope, void* ws, size_t wsb, cudaStream_t st) {
   const Geo g = make_geo(c);
-  if (thin_applicable(c, g)) {
+  Geo tg;
+  if (const int tm = thin_mode(c, g, &tg)) {
     t_last_algo = B2C_ALGO_TC;
-    return scatter ? thin_scatter(g, in, w, out, bias, act, slope, ws, wsb, st)
-                   : thin_gather(g, in, w, out, bias, act, slope, ws, wsb, st);
+    return scatter != (tm == 2) ? thin_scatter(tg, in, w, out, bias, act, slope, ws, wsb, st)
+                                : thin_gather(tg, in, w, out, bias, act, slope, ws, wsb, st);
   }
   if (tc_allowed(c)) {
     ConvPlan plan;
@@ -64,10 +65,11 @@ int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w
 extern "C" size_t b2c_conv3d_workspace(const b2c_conv_desc* c, int pass) {
   if (check_desc(c)) return 0;
   const Geo g = make_geo(c);
-  if (thin_applicable(c, g)) {
-    if (pass == B2C_PASS_WGRAD) return thin_workspace(g, 2);
+  Geo tg;
+  if (const int tm = thin_mode(c, g, &tg)) {
+    if (pass == B2C_PASS_WGRAD) return thin_workspace(tg, 2);
     const bool scatter = (pass == B2C_PASS_FWD) == (c->transposed != 0);
-    return thin_workspace(g, scatter ? 1 : 0);
+    return thin_workspace(tg, scatter != (tm == 2) ? 1 : 0);
   }
   if (pass == B2C_PASS_WGRAD && tc_allowed(c)) return tc_wgrad_workspace(g);
   return 0;
@@ -94,10 +96,11 @@ extern "C" int b2c_conv3d_dgrad(const b2c_conv_desc* c, const void* dy, const vo
   const Geo g = make_geo(c);
   const bool scatter = !c->transposed;
   cudaStream_t st = static_cast<cudaStream_t>(s);
-  if (thin_applicable(c, g)) {
+  Geo tg;
+  if (const int tm = thin_mode(c, g, &tg)) {
     t_last_algo = B2C_ALGO_TC;
-    return scatter ? thin_scatter(g, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, ws, wsb, st)
-                   : thin_gather(g, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, ws, wsb, st);
+    return scatter != (tm == 2) ? thin_scatter(tg, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, ws, wsb, st)
+                                : thin_gather(tg, dy, wp, dx, nullptr, B2C_ACT_NONE, 0.f, ws, wsb, st);
   }
   if (tc_allowed(c)) {
     ConvPlan plan;
@@ -126,9 +129,11 @@ extern "C" int b2c_conv3d_wgrad(const b2c_conv_desc* c, const void* x, const voi
   const void* big = c->transposed ? dy : x;
   if (dw) {
     bool done = false;
-    if (thin_applicable(c, g)) {
+    Geo tg;
+    if (const int tm = thin_mode(c, g, &tg)) {
       t_last_algo = B2C_ALGO_TC;
-      rc = thin_wgrad(g, small, big, dw, ws, wsb, st);
+      rc = tm == 2 ? thin_wgrad(tg, big, small, dw, ws, wsb, st, true)
+                   : thin_wgrad(tg, small, big, dw, ws, wsb, st, false);
       if (rc) return rc;
       done = true;
     } else if (tc_allowed(c) && tc_wgrad_supported(g)) {

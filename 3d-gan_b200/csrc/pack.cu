@@ -140,7 +140,8 @@ extern "C" size_t b2c_filter_packed_bytes(const b2c_conv_desc* c, int pass) {
   (void)pass;
   if (check_desc(c)) return 0;
   const Geo g = make_geo(c);
-  if (thin_applicable(c, g)) return thin_packed_bytes(g);
+  Geo tg;
+  if (thin_mode(c, g, &tg)) return thin_packed_bytes(tg);
   return (size_t)c->k[0] * c->k[1] * c->k[2] * c->x.c * c->y.c * esize(c->io_dtype);
 }
 
@@ -155,7 +156,8 @@ extern "C" int b2c_filter_pack(const b2c_conv_desc* c, int pass, const float* w,
   const bool out_is_A = (pass == B2C_PASS_FWD) != (c->transposed != 0);
   cudaStream_t st = static_cast<cudaStream_t>(s);
   const Geo g = make_geo(c);
-  if (thin_applicable(c, g)) return thin_pack(g, /*gather=*/out_is_A, w, wp, st);
+  Geo tg;
+  if (const int tm = thin_mode(c, g, &tg)) return thin_pack(tg, /*gather=*/out_is_A != (tm == 2), w, wp, st, tm == 2);
   if (c->io_dtype == B2C_BF16) return pack_launch<__nv_bfloat16>(w, wp, A, B, T, out_is_A, st);
   return pack_launch<float>(w, wp, A, B, T, out_is_A, st);
 }

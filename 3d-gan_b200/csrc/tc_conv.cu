@@ -332,13 +332,32 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
           }
           const int col0 = c.nt * P.block_n + j * 64;
           if (P.bias) {
-            const int b0 = col0 % P.bias_mod;      // one modulo per slab; bias_mod >= 8
+            if (P.bias_mod >= P.nout) {            // plain per-channel bias: no index arithmetic
+              const float* bp = P.bias + col0;
+              const int nb = P.nout - col0;          // valid columns of this slab (warp-uniform)
+              if (nb >= 64 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
-            for (int i = 0; i < 64; i++) {
-              if (i < ncol) {
-                int bi = b0 + i;
-                if (P.bias_mod >= 64) { if (bi >= P.bias_mod) bi -= P.bias_mod; } else bi %= P.bias_mod;
-                v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(P.bias + bi));
+                for (int q = 0; q < 16; q++) {
+                  const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp) + q);
+                  v[4 * q] = __float_as_uint(__uint_as_float(v[4 * q]) + b4.x);
+                  v[4 * q + 1] = __float_as_uint(__uint_as_float(v[4 * q + 1]) + b4.y);
+                  v[4 * q + 2] = __float_as_uint(__uint_as_float(v[4 * q + 2]) + b4.z);
+                  v[4 * q + 3] = __float_as_uint(__uint_as_float(v[4 * q + 3]) + b4.w);
+                }
+              } else {
+#pragma unroll
+                for (int i = 0; i < 64; i++)
+                  if (i < nb && i < ncol) v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(bp + i));
+              }
+            } else {                               // point convT: columns are (tap, co), bias_mod = Cout >= 8
+              const int b0 = col0 % P.bias_mod;    // one modulo per slab
+#pragma unroll
+              for (int i = 0; i < 64; i++) {
+                if (i < ncol) {
+                  int bi = b0 + i;
+                  if (P.bias_mod >= 64) { if (bi >= P.bias_mod) bi -= P.bias_mod; } else bi %= P.bias_mod;
+                  v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(P.bias + bi));
+                }
               }
             }
           }
@@ -716,15 +735,20 @@ static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   c->b_tiles = (c->n_ch + bn - 1) / bn;
   const int64_t units = (int64_t)c->plan.ntaps_total * c->a_tiles * c->b_tiles;
   if (units <= 0) return B2C_ERR_UNSUPPORTED;
-  // split-K count: 2.5 .. 10 waves of the SMs, at least 64 K-iterations per CTA; pick the count
-  // whose last wave is fullest (ties -> fewer splits = less partial-sum traffic)
+  // split-K count: 2.5 .. 10 waves of the SMs, at least 64 K-iterations per CTA (16 when the
+  // problem has too few tiles to fill the machine otherwise: 1x1x1 filters, 32-channel layers);
+  // pick the count whose last wave is fullest (ties -> fewer splits = less partial-sum traffic)
   const int sms = num_sms();
   int64_t splits = 1;
   {
     double best = -1.0;
-    const int64_t lo = cdiv((int64_t)sms * 5 / 2, units), hi = cdiv((int64_t)sms * 10, units);
-    for (int64_t sp = lo < 1 ? 1 : lo; sp <= (hi < 1 ? 1 : hi); sp++) {
-      if (sp > 1 && c->ktiles / sp < 64) break;
+    int64_t lo = cdiv((int64_t)sms * 5 / 2, units), hi = cdiv((int64_t)sms * 10, units);
+    int64_t cap = c->ktiles / 64;
+    if (cap < lo) cap = c->ktiles / 16 < lo ? c->ktiles / 16 : lo;
+    if (cap < 1) cap = 1;
+    if (lo > cap) lo = cap;
+    if (hi > cap) hi = cap;
+    for (int64_t sp = lo < 1 ? 1 : lo; sp <= hi; sp++) {
       const double waves = (double)(units * sp) / sms;
       const double eff = waves / (double)cdiv(units * sp, sms);
       if (eff > best + 0.02) { best = eff; splits = sp; }

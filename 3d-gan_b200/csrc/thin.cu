@@ -195,38 +195,60 @@ static bool is_k4s2(const Geo& g) {
 // gather : wp[a][t]  (Kp columns, zero padded)   = w[a][t]
 // scatter: wp[t][a]  (Kp rows,    zero padded)   = w[a][t]
 __global__ void __launch_bounds__(256)
-thin_pack_kernel(const float* __restrict__ w, bf16* __restrict__ wp, int A, int T, int Kp, int gather, int k4s2) {
+thin_pack_kernel(const float* __restrict__ w, bf16* __restrict__ wp, int A, int T, int Kp, int gather, int k4s2,
+                 int flip) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)A * Kp) return;
   int a, t;
   if (gather) { a = (int)(idx / Kp); t = (int)(idx % Kp); }
   else        { t = (int)(idx / A);  a = (int)(idx % A); if (k4s2) t = k4s2_perm(t); }
-  wp[idx] = __float2bfloat16_rn(t < T ? w[(int64_t)a * T + t] : 0.f);
+  // flip: the mirrored problem (thin_mode == 2) sees the filter with all three axes reversed
+  wp[idx] = __float2bfloat16_rn(t < T ? w[(int64_t)a * T + (flip ? T - 1 - t : t)] : 0.f);
 }
 
 // dw[a][t] = tmp[a][t] for t < T  (tmp has Kp columns)
 __global__ void __launch_bounds__(256)
-thin_unpad_kernel(const float* __restrict__ tmp, float* __restrict__ dw, int A, int T, int Kp) {
+thin_unpad_kernel(const float* __restrict__ tmp, float* __restrict__ dw, int A, int T, int Kp, int flip) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)A * T) return;
-  dw[idx] = tmp[(idx / T) * Kp + idx % T];
+  const int t = (int)(idx % T);
+  dw[idx] = tmp[(idx / T) * Kp + (flip ? T - 1 - t : t)];
 }
 
 // ---------------------------------------------------------------------------
-bool thin_applicable(const b2c_conv_desc* c, const Geo& g) {
-  if (c->io_dtype != B2C_BF16 || c->algo == B2C_ALGO_DIRECT) return false;
+static bool thin_shape_ok(const Geo& g) {
   if (g.bc != 1 || g.sc % 8 != 0 || g.sc < 16) return false;
   const int64_t rows = (int64_t)g.n * g.sd * g.sh * g.sw;
   return g.taps() <= 1024 && rows < 0x7fffffffLL && g.k[1] * g.k[2] <= 64;
 }
+
+int thin_mode(const b2c_conv_desc* c, const Geo& g, Geo* tg) {
+  if (c->io_dtype != B2C_BF16 || c->algo == B2C_ALGO_DIRECT) return 0;
+  if (thin_shape_ok(g)) { *tg = g; return 1; }
+  // one channel on the SMALL side with unit stride (biggan.py:42 output conv f -> 1,
+  // stylegan.py:1038): i = o + k*dl - p  <=>  o = i + (K-1-k)*dl - ((K-1)*dl - p), i.e. the same
+  // problem with the two tensors' roles exchanged, the filter reversed and the padding mirrored.
+  if (g.sc != 1) return 0;
+  Geo m = g;
+  m.sc = g.bc; m.sd = g.bd; m.sh = g.bh; m.sw = g.bw;
+  m.bc = 1;    m.bd = g.sd; m.bh = g.sh; m.bw = g.sw;
+  for (int i = 0; i < 3; i++) {
+    if (g.s[i] != 1) return 0;
+    m.p[i] = (g.k[i] - 1) * g.dl[i] - g.p[i];
+    if (m.p[i] < 0) return 0;
+  }
+  if (!thin_shape_ok(m)) return 0;
+  *tg = m;
+  return 2;
+}
 int thin_kp(const Geo& g) { int kp = (g.taps() + 7) / 8 * 8; return kp < 16 ? 16 : kp; }
 size_t thin_packed_bytes(const Geo& g) { return (size_t)thin_kp(g) * g.sc * sizeof(bf16); }
 
-int thin_pack(const Geo& g, bool gather, const float* w, void* wp, cudaStream_t st) {
+int thin_pack(const Geo& g, bool gather, const float* w, void* wp, cudaStream_t st, bool flip) {
   const int Kp = thin_kp(g);
   const int64_t n = (int64_t)g.sc * Kp;
   thin_pack_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(w, static_cast<bf16*>(wp), g.sc, g.taps(), Kp,
-                                                          gather ? 1 : 0, is_k4s2(g) ? 1 : 0);
+                                                          gather ? 1 : 0, is_k4s2(g) ? 1 : 0, flip ? 1 : 0);
   return launched();
 }
 
@@ -301,7 +323,8 @@ int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big,
   return launched();
 }
 
-int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void* ws, size_t wsb, cudaStream_t st) {
+int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void* ws, size_t wsb, cudaStream_t st,
+               bool flip) {
   if (!ws || wsb < thin_workspace(g, 2)) return B2C_ERR_WORKSPACE;
   const int Kp = thin_kp(g), T = g.taps();
   int rc = im2col_launch(g, big, ws, st);
@@ -311,12 +334,12 @@ int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void
   p += align256((size_t)g.sc * Kp * sizeof(float));
   const Geo gg = gemm_geo(rows_of(g), g.sc, Kp);
   const size_t tcws = tc_wgrad_workspace(gg);
-  float* target = Kp == T ? dw : tmp;
+  float* target = (Kp == T && !flip) ? dw : tmp;
   rc = tc_wgrad_launch(gg, small, ws, target, p, tcws, st);
   if (rc) return rc;
-  if (Kp != T) {
+  if (target == tmp) {
     const int64_t n = (int64_t)g.sc * T;
-    thin_unpad_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(tmp, dw, g.sc, T, Kp);
+    thin_unpad_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(tmp, dw, g.sc, T, Kp, flip ? 1 : 0);
     return launched();
   }
   return B2C_OK;

@@ -73,10 +73,11 @@ class Discriminator(nn.Module):
 
 
 class RefTrainer:
-    """The two phases of trainer.Trainer for --dcgan (WGAN loss), fp32, any device."""
+    """The two phases of trainer.Trainer for --dcgan (WGAN loss, trainer.py:235-247) or any
+    model with --hinge (trainer.py:222-233), fp32, any device."""
 
-    def __init__(self, netG, netD, z_size=512, lrG=5e-5, lrD=1e-4):
-        self.netG, self.netD, self.z_size = netG, netD, z_size
+    def __init__(self, netG, netD, z_size=512, lrG=5e-5, lrD=1e-4, hinge=False):
+        self.netG, self.netD, self.z_size, self.hinge = netG, netD, z_size, hinge
         self.device = next(netG.parameters()).device
         self.optimizerD = optim.Adam(netD.parameters(), lr=lrD, betas=(0.0, 0.9))
         self.optimizerG = optim.Adam(netG.parameters(), lr=lrG, betas=(0.0, 0.9))
@@ -90,9 +91,14 @@ class RefTrainer:
         if noise is None:
             noise = torch.randn(real.shape[0], self.z_size, 1, 1, 1, dtype=torch.float, device=self.device)
         fake = self.netG(noise)
-        errD_real = self.netD(real).mean()
-        errD_fake = self.netD(fake).mean()
-        errD = errD_fake - errD_real
+        if self.hinge:
+            errD_real = torch.relu(1.0 - self.netD(real)).mean()
+            errD_fake = torch.relu(1.0 + self.netD(fake)).mean()
+            errD = errD_fake + errD_real
+        else:
+            errD_real = self.netD(real).mean()
+            errD_fake = self.netD(fake).mean()
+            errD = errD_fake - errD_real
         errD.backward()
         self.optimizerD.step()
         for p in self.netD.parameters():

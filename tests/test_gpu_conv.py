@@ -50,6 +50,12 @@ THIN_CASES = [
     (False, 1, 64, 3, 1, 1, 1, (6, 7, 8), 2),       # biggan.py:78 input conv (Kp = 32)
     (True, 16, 1, 4, 2, 1, 1, (8, 8, 8), 2),        # dcgan.py:67 G head
     (True, 128, 1, 4, 2, 1, 1, (6, 6, 6), 2),       # dcgan.py:67 at full width
+    # SMALL side has one channel, stride 1: mirrored problem (thin_mode == 2)
+    (False, 64, 1, 3, 1, 1, 1, (6, 7, 8), 2),       # biggan.py:42 output conv f -> 1
+    (False, 16, 1, 3, 1, 1, 1, (9, 8, 10), 3),      # stylegan.py:1038 Conv3d(16 -> 1)
+    (False, 64, 1, 4, 1, 0, 1, (4, 4, 4), 4),       # dcgan.py:181 head (valid conv, mirrored pad 3)
+    (False, 32, 1, 3, 1, 2, 2, (8, 8, 8), 2),       # dilated
+    (False, 24, 1, 1, 1, 0, 1, (5, 6, 7), 2),       # 1x1x1 to one channel (Kp = 16)
 ]
 
 

@@ -110,3 +110,82 @@ def test_fid_resnet_vs_reference_golden():
         fw = wit(x).float().mean(dim=(2, 3, 4))
     l2w = ((fw.cpu() - ref_feat).norm() / ref_feat.norm()).item()
     assert l2 < max(4e-2, 1.5 * l2w), (l2, l2w)
+
+
+# ---------------------------------------------------------------- BigGAN-deep (BASELINE config 3)
+def _biggan_from_gold(gold):
+    import ref_biggan  # noqa: F401
+    width, z = int(gold["width"]), int(gold["z"])
+    g, d = B.biggan.build(z, width, width, "cpu")
+    g.load_state_dict({k: torch.from_numpy(gold["g0." + k]) for k in g.state_dict()})
+    d.load_state_dict({k: torch.from_numpy(gold["d0." + k]) for k in d.state_dict()})
+    return g.cuda(), d.cuda(), z
+
+
+def test_biggan_reference_golden_fp32():
+    """Product BigGAN-deep (b200conv3d.biggan) against golden vectors of the UNMODIFIED reference
+    (biggan.py / utils.py / trainer.py hinge branch), fp32 exact kernels: eval-mode outputs, then
+    one Trainer.D_step + G_step with the reference's noise draws - losses, every parameter, the
+    spectral-norm u / v buffers and BN running statistics."""
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "biggan_ref.npz"))
+    g, d, z = _biggan_from_gold(gold)
+    b = int(gold["batch"])
+    assert sorted("g0." + k for k in g.state_dict()) == sorted(k for k in gold.files if k.startswith("g0."))
+    assert sorted("d0." + k for k in d.state_dict()) == sorted(k for k in gold.files if k.startswith("d0."))
+    torch.manual_seed(5)
+    zin = torch.randn(b, z, 1, 1, 1)
+    real = torch.rand(b, 1, 128, 128, 128) * 2 - 1
+    g.eval(), d.eval()
+    with torch.no_grad():
+        fake = g(zin.cuda())
+        dreal = d(real.cuda())
+    g.train(), d.train()
+    assert rel_err(fake[:, 0, ::8, ::8, ::8], torch.from_numpy(gold["fake0_sample"])) < 1e-4
+    assert rel_err(dreal.reshape(-1), torch.from_numpy(gold["dreal0"])) < 1e-4
+    step = B.train.GanStep(g, d, z, hinge=True, autocast_dtype=None)
+    step.noise = lambda n: torch.randn(n, z, 1, 1, 1).cuda()
+    torch.manual_seed(77)
+    er, ef = step.D_step(real.cuda())
+    torch.manual_seed(78)
+    eg, _ = step.G_step(b)
+    np.testing.assert_allclose([er.item(), ef.item()], gold["D_losses"][0], rtol=2e-4, atol=2e-5)
+    np.testing.assert_allclose([eg.item()], gold["G_losses"], rtol=2e-4, atol=2e-5)
+    for pre, m in (("g1.", g), ("d1.", d)):
+        for k, v in m.state_dict().items():
+            ref = torch.from_numpy(gold[pre + k])
+            if "running" in k or k.endswith("._u") or k.endswith("._v"):
+                assert rel_err(v, ref) < 1e-3, k
+            elif v.dim() >= 1 and v.numel() > 1:
+                # one Adam step is sign-like (lr * g / |g|): entries whose gradient is ~0 may flip
+                bad = ((v.cpu() - ref).abs() > 2e-3 * ref.abs().max() + 1e-6).float().mean().item()
+                assert bad < max(0.02, 1.5 / v.numel()), (k, bad)
+
+
+def test_biggan_tensor_core_vs_oracle_bf16():
+    """Width 32 (hidden channels 8..128, stem / head 1 channel): bf16 through the tcgen05 / thin
+    paths against the fp32 CPU oracle on the same weights, forward and parameter gradients of one
+    hinge discriminator loss."""
+    import ref_biggan
+    width, z, b = 32, 16, 2
+    torch.manual_seed(21)
+    rd, rg = ref_biggan.Discriminator(width), ref_biggan.Generator(z, width)
+    g, d = B.biggan.build(z, width, width, "cpu")
+    g.load_state_dict(rg.state_dict()), d.load_state_dict(rd.state_dict())
+    g, d = g.cuda(), d.cuda()
+    zin = torch.randn(b, z, 1, 1, 1)
+    real = torch.rand(b, 1, 128, 128, 128) * 2 - 1
+    rg.eval(), rd.eval(), g.eval(), d.eval()      # frozen spectral norm / BN statistics: same function
+    with torch.no_grad():
+        f_ref, d_ref = rg(zin), rd(real)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            f, dd = g(zin.cuda()), d(real.cuda())
+        # stock torch layers under bf16 autocast on the same GPU: the bf16 noise floor (witness)
+        wg, wd = rg.cuda(), rd.cuda()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            fw, dw = wg(zin.cuda()), wd(real.cuda())
+    ef = ((f.float().cpu() - f_ref).norm() / f_ref.norm()).item()
+    efw = ((fw.float().cpu() - f_ref).norm() / f_ref.norm()).item()
+    ed = ((dd.float().cpu() - d_ref).abs().max() / d_ref.abs().max()).item()
+    edw = ((dw.float().cpu() - d_ref).abs().max() / d_ref.abs().max()).item()
+    assert ef < max(4e-2, 1.5 * efw), (ef, efw)
+    assert ed < max(4e-2, 1.5 * edw), (ed, edw)

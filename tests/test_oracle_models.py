@@ -104,3 +104,65 @@ def test_fid_resnet_port_matches_reference():
     assert tuple(y.shape) == tuple(g["y_shape"])
     np.testing.assert_allclose(y[:, ::64].numpy(), g["y_sample"], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(y.mean(dim=(2, 3, 4)).numpy(), g["feat"], rtol=1e-4, atol=1e-5)
+
+
+# ---------------------------------------------------------------- BigGAN-deep (BASELINE config 3)
+import ref_biggan  # noqa: E402
+
+GOLD_BIG = os.path.join(ROOT, "tests", "golden", "biggan_ref.npz")
+
+
+@pytest.fixture(scope="module")
+def gold_big():
+    return np.load(GOLD_BIG)
+
+
+def _build_big(gold, load=True):
+    width, z = int(gold["width"]), int(gold["z"])
+    torch.manual_seed(20261104)
+    d = ref_biggan.Discriminator(width)            # trainer.py:66-67 builds D first
+    g = ref_biggan.Generator(z, width)
+    if load:
+        g.load_state_dict({k: torch.from_numpy(gold["g0." + k]) for k in g.state_dict()})
+        d.load_state_dict({k: torch.from_numpy(gold["d0." + k]) for k in d.state_dict()})
+    return g, d, z
+
+
+def test_biggan_init_and_names_match_reference(gold_big):
+    """Same seed -> same state_dict, key for key: pins the spectral-norm wrapping, the
+    (ineffective on SN layers) orthogonal init and the RNG consumption order (biggan.py:46-53)."""
+    g, d, _ = _build_big(gold_big, load=False)
+    for pre, m in (("g0.", g), ("d0.", d)):
+        sd = m.state_dict()
+        assert sorted(pre + k for k in sd) == sorted(k for k in gold_big.files if k.startswith(pre))
+        for k, v in sd.items():
+            np.testing.assert_array_equal(v.numpy(), gold_big[pre + k], err_msg=k)
+
+
+def test_biggan_forward_matches_reference(gold_big):
+    g, d, _ = _build_big(gold_big)
+    zin, real = _inputs(gold_big)
+    g.eval(), d.eval()
+    with torch.no_grad():
+        fake = g(zin)
+        dreal = d(real)
+    np.testing.assert_allclose(fake[:, 0, ::8, ::8, ::8].numpy(), gold_big["fake0_sample"], rtol=1e-5, atol=1e-7)
+    assert abs(fake.double().sum().item() - float(gold_big["fake0_sum"])) < 1e-6 * fake.numel() ** 0.5 + 1e-3
+    np.testing.assert_allclose(dreal.reshape(-1).numpy(), gold_big["dreal0"], rtol=1e-5, atol=1e-6)
+
+
+def test_biggan_hinge_phases_match_reference(gold_big):
+    """Trainer.D_step (hinge, trainer.py:222-233) + G_step: losses, every parameter and buffer
+    (spectral-norm u / v, BN running statistics) after the two optimizer steps."""
+    g, d, z = _build_big(gold_big)
+    _, real = _inputs(gold_big)
+    tr = ref_dcgan.RefTrainer(g, d, z, hinge=True)
+    torch.manual_seed(77)
+    er, ef = tr.d_step(real)
+    torch.manual_seed(78)
+    eg, _ = tr.g_step(int(gold_big["batch"]))
+    np.testing.assert_allclose([er, ef], gold_big["D_losses"][0], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose([eg], gold_big["G_losses"], rtol=1e-5, atol=1e-7)
+    for pre, m in (("g1.", g), ("d1.", d)):
+        for k, v in m.state_dict().items():
+            np.testing.assert_allclose(v.numpy(), gold_big[pre + k], rtol=2e-4, atol=2e-6, err_msg=k)

@@ -54,6 +54,13 @@ CONFIGS = {
         ("3x3x3 128->128 @32", False, 128, 128, 3, 1, 1, 1, 32),
         ("3x3x3 256->256 @16", False, 256, 256, 3, 1, 1, 1, 16),
         ("1x1 64->32 @128", False, 64, 32, 1, 1, 0, 1, 128),
+        ("1x1 32->64 @128", False, 32, 64, 1, 1, 0, 1, 128),
+        ("1x1 128->32 @64", False, 128, 32, 1, 1, 0, 1, 64),
+        ("1x1 32->128 @64", False, 32, 128, 1, 1, 0, 1, 64),
+        ("1x1 64->256 @32", False, 64, 256, 1, 1, 0, 1, 32),
+        ("1x1 256->64 @32", False, 256, 64, 1, 1, 0, 1, 32),
+        ("stem 3x3x3 1->64 @128", False, 1, 64, 3, 1, 1, 1, 128),
+        ("head 3x3x3 64->1 @128", False, 64, 1, 3, 1, 1, 1, 128),
     ],
 }
 
@@ -87,6 +94,7 @@ def main():
     ap.add_argument("--only", default="")
     ap.add_argument("--passes", default="fwd,dgrad,wgrad")
     ap.add_argument("--json", default="")
+    ap.add_argument("--bias", action="store_true", help="forward with a fused bias + ReLU epilogue (utils.py:8-14 convs)")
     a = ap.parse_args()
     peaks = {}
     pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -123,8 +131,12 @@ def main():
         st = gpu._st()
         P = gpu._p
 
+        from b200conv3d._lib import Fusion
+        bias = torch.randn(cout, device="cuda")
+        fu = C.byref(Fusion(P(bias), 1, 0.0)) if a.bias else None
+
         def fwd():
-            gpu._ck(gpu.lib.b2c_conv3d_fwd(C.byref(desc), P(x), P(wp_f), P(y), None, P(ws), ws.numel(), st), "fwd")
+            gpu._ck(gpu.lib.b2c_conv3d_fwd(C.byref(desc), P(x), P(wp_f), P(y), fu, P(ws), ws.numel(), st), "fwd")
 
         def dgrad():
             gpu._ck(gpu.lib.b2c_conv3d_dgrad(C.byref(desc), P(dy), P(wp_d), P(dx), P(ws), ws.numel(), st), "dgrad")

@@ -58,7 +58,7 @@ def main():
         if kind == "ln":
             ga = torch.ones(c, s, s, s, device=dev, requires_grad=True)
             be = torch.zeros(c, s, s, s, device=dev, requires_grad=True)
-            fwd = lambda: BF.layer_norm_act(x, ga, be, 1e-5, "leaky_relu", 0.2)
+            fwd = lambda: BF.layer_norm_act(x, ga, be, 1e-5, "lrelu", 0.2)
             bytes_f, bytes_b = 6 * el + 8 * ga.numel(), 10 * el + 16 * ga.numel()
         else:
             ga = torch.ones(c, device=dev, requires_grad=True)
