@@ -69,6 +69,10 @@ _SIGNATURES = {
                               _i32, _f32, _vp, _vp, _vp, _sz, _vp]),
     "b2c_act_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _f32, _vp]),
     "b2c_act_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _f32, _vp]),
+    "b2c_upsample2x_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b2c_upsample2x_bwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b2c_avgpool2_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b2c_avgpool2_bwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
 EXPORTS = tuple(_SIGNATURES)
 

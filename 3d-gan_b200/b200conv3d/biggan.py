@@ -14,8 +14,10 @@ What runs where:
     (a fresh weight tensor per forward, re-packed by the layer; utils.py:13);
   * BatchNorm3d + ReLU pairs (utils.py:68-84, biggan.py:40-41) -> one fused b2c_bn_act pass;
   * the pre-activation ReLUs of DBlockDeep (utils.py:120-125) -> b2c_act;
-  * nearest x2, AvgPool3d(2), channel slice / cat, the attention bmm / softmax / max-pool and
-    the two linears stay ATen ops on NDHWC tensors ("next").
+  * channel drop + nearest x2 (utils.py:76-80) -> b2c_upsample2x; AvgPool3d(2) -> b2c_avgpool2
+    (ATen has no channels-last 3-D kernels for either: it would convert to NCDHW and back);
+  * residual adds, the shortcut cat, the attention bmm / softmax / max-pool and the two linears
+    stay ATen ops on NDHWC tensors ("next").
 """
 import functools
 
@@ -89,10 +91,11 @@ class GBlockDeep(tnn.Module):
     def forward(self, x):
         h = self.conv1(self.bn1(x))
         h = self.bn2(h)
-        if self.in_channels != self.out_channels:
+        if self.upsample:          # utils.py:76-80: channel drop + nearest x2 of h and x, one pass each
+            h = BF.upsample_nearest2x(h)
+            x = BF.upsample_nearest2x(x, self.out_channels)
+        elif self.in_channels != self.out_channels:
             x = x[:, :self.out_channels]
-        if self.upsample:
-            h, x = self.upsample(h), self.upsample(x)
         h = self.conv2(h)
         h = self.conv3(self.bn3(h))
         h = self.conv4(self.bn4(h))
@@ -191,9 +194,9 @@ class Discriminator(tnn.Module):
         stages = []
         for i in range(5):
             if biggan:
-                stage = [DBlockDeep(cin[i], cout[i], downsample=tnn.AvgPool3d(2)), DBlockDeep(cout[i], cout[i])]
+                stage = [DBlockDeep(cin[i], cout[i], downsample=BN.AvgPool3d(2)), DBlockDeep(cout[i], cout[i])]
             else:
-                stage = [DBlockDeep(cin[i], cout[i], downsample=tnn.AvgPool3d(2))]
+                stage = [DBlockDeep(cin[i], cout[i], downsample=BN.AvgPool3d(2))]
             if (sagan or biggan) and res[i] == 16:
                 stage.append(Attention(cout[i]))
             stages.append(tnn.ModuleList(stage))

@@ -619,3 +619,77 @@ class _ActFn(Function):
 
 def activation(x, act, slope=0.0, inplace=False):
     return _ActFn.apply(x, _act_id(act), slope, inplace)
+
+
+# --------------------------------------------------------------- x2 resampling (NDHWC)
+def _keep_dtype(x):
+    return x.dtype if x.dtype in (torch.bfloat16, torch.float32) else torch.float32
+
+
+class _Up2Fn(Function):
+    """`x[:, :channels]` + F.interpolate(scale_factor=2) (nearest) of utils.py:76-80 in one
+    NDHWC pass; backward sums 2x2x2 blocks and zero-fills the dropped channels."""
+
+    @staticmethod
+    def forward(ctx, x, channels):
+        _check_device(x)
+        cd = _keep_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, cx = xb.shape
+        c = cx if channels is None else int(channels)
+        if not 0 < c <= cx:
+            raise ValueError("channels=%r out of range for a %d-channel tensor" % (channels, cx))
+        yl, y = alloc_out(n, 2 * d, 2 * h, 2 * w, c, cd, x.device)
+        with _dev(x):
+            check(_lib.lib().b2c_upsample2x_fwd(_ptr(xb), _ptr(y), n, d, h, w, cx, 0, c, _dt(cd), _stream(x)),
+                  "upsample2x_fwd")
+        ctx.geo, ctx.cd, ctx.x_dtype = (n, d, h, w, cx, c), cd, x.dtype
+        return yl
+
+    @staticmethod
+    def backward(ctx, gy):
+        n, d, h, w, cx, c = ctx.geo
+        gyb = to_ndhwc(gy, ctx.cd)
+        dxl, dx = alloc_out(n, d, h, w, cx, ctx.cd, gy.device)
+        with _dev(gy):
+            check(_lib.lib().b2c_upsample2x_bwd(_ptr(gyb), _ptr(dx), n, d, h, w, cx, 0, c, _dt(ctx.cd),
+                                                _stream(gy)), "upsample2x_bwd")
+        return (dxl if ctx.x_dtype == ctx.cd else dxl.to(ctx.x_dtype)), None
+
+
+def upsample_nearest2x(x, channels=None):
+    """Drop-in for ``F.interpolate(x[:, :channels], scale_factor=2)`` (nearest) on 5-D tensors."""
+    return _Up2Fn.apply(x, channels)
+
+
+class _AvgPool2Fn(Function):
+    """nn.AvgPool3d(2) (utils.py:113-116,128-129; biggan.py:86,92) on NDHWC storage."""
+
+    @staticmethod
+    def forward(ctx, x):
+        _check_device(x)
+        cd = _keep_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, c = xb.shape
+        if min(d, h, w) < 2:
+            raise ValueError("AvgPool3d(2) needs every spatial extent >= 2, got %s" % ((d, h, w),))
+        yl, y = alloc_out(n, d // 2, h // 2, w // 2, c, cd, x.device)
+        with _dev(x):
+            check(_lib.lib().b2c_avgpool2_fwd(_ptr(xb), _ptr(y), n, d, h, w, c, _dt(cd), _stream(x)), "avgpool2_fwd")
+        ctx.geo, ctx.cd, ctx.x_dtype = (n, d, h, w, c), cd, x.dtype
+        return yl
+
+    @staticmethod
+    def backward(ctx, gy):
+        n, d, h, w, c = ctx.geo
+        gyb = to_ndhwc(gy, ctx.cd)
+        dxl, dx = alloc_out(n, d, h, w, c, ctx.cd, gy.device)
+        with _dev(gy):
+            check(_lib.lib().b2c_avgpool2_bwd(_ptr(gyb), _ptr(dx), n, d, h, w, c, _dt(ctx.cd), _stream(gy)),
+                  "avgpool2_bwd")
+        return dxl if ctx.x_dtype == ctx.cd else dxl.to(ctx.x_dtype)
+
+
+def avg_pool2(x):
+    """Drop-in for ``nn.AvgPool3d(2)(x)``."""
+    return _AvgPool2Fn.apply(x)

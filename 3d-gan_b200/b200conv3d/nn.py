@@ -110,6 +110,17 @@ class Tanh(_TTanh):
         return BF.activation(x, "tanh", 0.0, False)
 
 
+class AvgPool3d(tnn.AvgPool3d):
+    """nn.AvgPool3d(2) of the BigGAN discriminator blocks (utils.py:113-116, biggan.py:86,92) as
+    one NDHWC pass.  Other pooling configurations are not on the reference's path: they raise."""
+
+    def forward(self, x):
+        k, s, p = BF._triple(self.kernel_size), BF._triple(self.stride), BF._triple(self.padding)
+        if k != (2, 2, 2) or s != (2, 2, 2) or p != (0, 0, 0) or self.ceil_mode or self.divisor_override:
+            raise ValueError("b200conv3d.nn.AvgPool3d implements kernel_size=2, stride=2, padding=0 only")
+        return BF.avg_pool2(x)
+
+
 class FusedAway(tnn.Identity):
     """Placeholder left where an activation was folded into the previous layer
     by :func:`b200conv3d.patch.fuse`; keeps nn.Sequential indices (and thus

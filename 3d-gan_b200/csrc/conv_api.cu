@@ -62,16 +62,26 @@ int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w
 
 }  // namespace
 
+namespace {
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+// filter-gradient part of the wgrad workspace; the dbias scratch follows it (256-byte aligned)
+size_t wgrad_core_ws(const b2c_conv_desc* c, const Geo& g) {
+  Geo tg;
+  if (thin_mode(c, g, &tg)) return thin_workspace(tg, 2);
+  return tc_allowed(c) ? tc_wgrad_workspace(g) : 0;
+}
+int64_t y_rows(const b2c_conv_desc* c) { return (int64_t)c->y.n * c->y.d * c->y.h * c->y.w; }
+}  // namespace
+
 extern "C" size_t b2c_conv3d_workspace(const b2c_conv_desc* c, int pass) {
   if (check_desc(c)) return 0;
   const Geo g = make_geo(c);
+  if (pass == B2C_PASS_WGRAD) return align256(wgrad_core_ws(c, g)) + channel_sum_workspace(y_rows(c), c->y.c);
   Geo tg;
   if (const int tm = thin_mode(c, g, &tg)) {
-    if (pass == B2C_PASS_WGRAD) return thin_workspace(tg, 2);
     const bool scatter = (pass == B2C_PASS_FWD) == (c->transposed != 0);
     return thin_workspace(tg, scatter != (tm == 2) ? 1 : 0);
   }
-  if (pass == B2C_PASS_WGRAD && tc_allowed(c)) return tc_wgrad_workspace(g);
   return 0;
 }
 
@@ -151,8 +161,9 @@ extern "C" int b2c_conv3d_wgrad(const b2c_conv_desc* c, const void* x, const voi
     }
   }
   if (dbias) {
-    const int64_t rows = (int64_t)c->y.n * c->y.d * c->y.h * c->y.w;
-    rc = channel_sum(dy, rows, c->y.c, c->io_dtype, dbias, st);
+    const size_t core = align256(wgrad_core_ws(c, g));
+    if (!ws || wsb < core) return B2C_ERR_WORKSPACE;
+    rc = channel_sum(dy, y_rows(c), c->y.c, c->io_dtype, dbias, static_cast<uint8_t*>(ws) + core, wsb - core, st);
     if (rc) return rc;
   }
   return B2C_OK;

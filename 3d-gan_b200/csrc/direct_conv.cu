@@ -245,44 +245,4 @@ int direct_wgrad(const Geo& g, int dt, const void* sm, const void* bg, float* dw
   return dt == B2C_BF16 ? wgrad_t<__nv_bfloat16>(g, sm, bg, dw, st) : wgrad_t<float>(g, sm, bg, dw, st);
 }
 
-// ---------------------------------------------------------------------------
-// dbias: out[c] = sum_r x[r][c].  Each thread walks linear indices with a
-// stride that is a multiple of C, so its channel is fixed; block partials are
-// merged in shared memory, then one atomic per (block, channel).
-template <typename T>
-__global__ void __launch_bounds__(256)
-channel_sum_kernel(const T* __restrict__ x, int64_t n, int C, int64_t stride, float* __restrict__ out) {
-  extern __shared__ float sm[];
-  for (int c = threadIdx.x; c < C; c += blockDim.x) sm[c] = 0.f;
-  __syncthreads();
-  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;   // <= stride
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < stride && base < n; base += nthreads) {
-    float acc = 0.f;
-    for (int64_t i = base; i < n; i += stride) acc += ldf(x, i);
-    atomicAdd(&sm[(int)(base % C)], acc);
-  }
-  __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) if (sm[c] != 0.f) atomicAdd(out + c, sm[c]);
-}
-
-int channel_sum(const void* x, int64_t rows, int C, int dt, float* out, cudaStream_t st) {
-  int rc = cuda_rc(cudaMemsetAsync(out, 0, (size_t)C * sizeof(float), st));
-  if (rc) return rc;
-  const int64_t n = rows * C;
-  if (n == 0) return B2C_OK;
-  if ((size_t)C * sizeof(float) > 48 * 1024) return B2C_ERR_UNSUPPORTED;
-  int64_t blocks = cdiv(n, 256);
-  const int64_t cap = (int64_t)num_sms() * 8;
-  if (blocks > cap) blocks = cap;
-  int64_t stride = blocks * 256;
-  stride = cdiv(stride, C) * C;          // multiple of C -> fixed channel per thread
-  if (dt == B2C_BF16)
-    channel_sum_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, C * sizeof(float), st>>>(
-        static_cast<const __nv_bfloat16*>(x), n, C, stride, out);
-  else
-    channel_sum_kernel<float><<<(unsigned)blocks, 256, C * sizeof(float), st>>>(static_cast<const float*>(x), n, C,
-                                                                               stride, out);
-  return launched();
-}
-
 }  // namespace b2c

@@ -14,5 +14,7 @@ int direct_scatter(const Geo& g, int dt, const void* in_small, const void* w, vo
 // dW[a][b][t] = sum small[n,o,a] * big[n,o*s+k*dl-p,b]   (torch layout, fp32, overwritten)
 int direct_wgrad(const Geo& g, int dt, const void* small, const void* big, float* dw, cudaStream_t st);
 // out[c] = sum_rows x[r][c]
-int channel_sum(const void* x, int64_t rows, int C, int dt, float* out, cudaStream_t st);
+// norm.cu: deterministic per-channel sum (dbias)
+size_t channel_sum_workspace(int64_t rows, int64_t C);
+int channel_sum(const void* x, int64_t rows, int C, int dt, float* out, void* ws, size_t wsb, cudaStream_t st);
 }  // namespace b2c

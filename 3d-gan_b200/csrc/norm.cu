@@ -40,6 +40,26 @@ __device__ __forceinline__ void stvecf(float* __restrict__ p, int64_t off, const
   }
 }
 
+template <typename T, int VEC>
+__device__ __forceinline__ void ldvec(const T* __restrict__ p, int64_t off, float* out) {
+  if (VEC > 1) { Vec<T> v; v.load(p + off); v.unpack(out); } else out[0] = ldf(p, off);
+}
+// a VEC-element load kept packed (16 bytes for bf16 x 8) until it is consumed
+template <typename T, int VEC> struct Pk {
+  Vec<T> v;
+  __device__ __forceinline__ void load(const T* __restrict__ p, int64_t off) { v.load(p + off); }
+  __device__ __forceinline__ void unpack(float* o) const { v.unpack(o); }
+};
+template <typename T> struct Pk<T, 1> {
+  float v;
+  __device__ __forceinline__ void load(const T* __restrict__ p, int64_t off) { v = ldf(p, off); }
+  __device__ __forceinline__ void unpack(float* o) const { o[0] = v; }
+};
+template <typename T, int VEC>
+__device__ __forceinline__ void stvec(T* __restrict__ p, int64_t off, float* v) {
+  if (VEC > 1) { Vec<T> o; o.pack(v); o.store(p + off); } else stf(p, off, v[0]);
+}
+
 // ===========================================================================
 // Per-channel two-value reduction over rows of an [rows][C] tensor.
 //   out0[c] = sum_r f0(r,c),  out1[c] = sum_r f1(r,c)
@@ -82,25 +102,34 @@ chan_reduce_stage1(const T* __restrict__ x, int64_t rows, int C, BnBwdF<T> f, fl
           mu[i] = f.mean[c]; is[i] = f.invstd[c]; sc[i] = f.scale[c]; sh[i] = f.shift[c];
         }
       }
-      for (int64_t r = r0 + rlane; r < r1; r += rstep) {
-        float xv[VEC], dv[VEC], rv[VEC];
-        const int64_t off = r * C + c0;
-        if (VEC > 1) {
-          Vec<T> v; v.load(x + off); v.unpack(xv);
-          if (BWD) { v.load(f.dy + off); v.unpack(dv); if (f.res) { v.load(f.res + off); v.unpack(rv); } }
-        } else {
-          xv[0] = ldf(x, off);
-          if (BWD) { dv[0] = ldf(f.dy, off); if (f.res) rv[0] = ldf(f.res, off); }
+      // four rows in flight per thread: loads first, then the math
+      for (int64_t rb = r0 + rlane; rb < r1; rb += 4 * (int64_t)rstep) {
+        Pk<T, VEC> xr[4], dr[4], rr[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int64_t r = rb + (int64_t)u * rstep;
+          if (r < r1) {
+            const int64_t off = r * C + c0;
+            xr[u].load(x, off);
+            if (BWD) { dr[u].load(f.dy, off); if (f.res) rr[u].load(f.res, off); }
+          }
         }
 #pragma unroll
-        for (int i = 0; i < VEC; i++) {
-          if (BWD) {
-            float z = xv[i] * sc[i] + sh[i];
-            if (f.res) z += rv[i];
-            float gg = dv[i] * act_dz(z, f.act, f.slope);
-            a[i] += gg; b[i] += gg * (xv[i] - mu[i]) * is[i];
-          } else {
-            a[i] += xv[i]; b[i] += xv[i] * xv[i];
+        for (int u = 0; u < 4; u++) {
+          if (rb + (int64_t)u * rstep >= r1) break;
+          float xv[VEC], dv[VEC], rv[VEC];
+          xr[u].unpack(xv);
+          if (BWD) { dr[u].unpack(dv); if (f.res) rr[u].unpack(rv); }
+#pragma unroll
+          for (int i = 0; i < VEC; i++) {
+            if (BWD) {
+              float z = xv[i] * sc[i] + sh[i];
+              if (f.res) z += rv[i];
+              float gg = dv[i] * act_dz(z, f.act, f.slope);
+              a[i] += gg; b[i] += gg * (xv[i] - mu[i]) * is[i];
+            } else {
+              a[i] += xv[i]; b[i] += xv[i] * xv[i];
+            }
           }
         }
       }
@@ -182,26 +211,44 @@ __global__ void bn_finalize_kernel(const float* sum, const float* sq, double inv
 // ===========================================================================
 // Elementwise BN apply (+residual, +act) and backward apply.
 // ===========================================================================
+// A thread's channel group is fixed whenever the grid stride is a multiple of C / VEC (always for
+// power-of-two C): the per-channel parameters are then loaded once, as 16-byte vectors, and two
+// vectors per thread are in flight per iteration.
 template <typename T, int VEC>
 __global__ void __launch_bounds__(kThreads)
 bn_act_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, const T* __restrict__ res, int64_t nvec, int C,
                   const float* __restrict__ scale, const float* __restrict__ shift, int act, float slope) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-    const int64_t off = i * VEC;
-    const int c0 = (int)(off % C);
-    float xv[VEC], rv[VEC];
-    if (VEC > 1) {
-      Vec<T> v; v.load(x + off); v.unpack(xv);
-      if (res) { v.load(res + off); v.unpack(rv); }
-    } else { xv[0] = ldf(x, off); if (res) rv[0] = ldf(res, off); }
+  float sc[VEC], sh[VEC];
+  int cc = -1;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 2 * stride) {
+    const int64_t i2 = i + stride;
+    const bool two = i2 < nvec;
+    Pk<T, VEC> xa, xb, ra, rb;
+    xa.load(x, i * VEC);
+    if (res) ra.load(res, i * VEC);
+    if (two) { xb.load(x, i2 * VEC); if (res) rb.load(res, i2 * VEC); }
 #pragma unroll
-    for (int k = 0; k < VEC; k++) {
-      float z = xv[k] * scale[c0 + k] + shift[c0 + k];
-      if (res) z += rv[k];
-      xv[k] = act_f(z, act, slope);
+    for (int u = 0; u < 2; u++) {
+      if (u == 1 && !two) break;
+      const int64_t off = (u ? i2 : i) * VEC;
+      const int c0 = (int)(off % C);
+      if (c0 != cc) {
+        if (VEC > 1) { ldvecf<VEC>(scale, c0, sc, 1.f); ldvecf<VEC>(shift, c0, sh, 0.f); }
+        else { sc[0] = scale[c0]; sh[0] = shift[c0]; }
+        cc = c0;
+      }
+      float xv[VEC], rv[VEC];
+      (u ? xb : xa).unpack(xv);
+      if (res) (u ? rb : ra).unpack(rv);
+#pragma unroll
+      for (int k = 0; k < VEC; k++) {
+        float z = xv[k] * sc[k] + sh[k];
+        if (res) z += rv[k];
+        xv[k] = act_f(z, act, slope);
+      }
+      stvec<T, VEC>(y, off, xv);
     }
-    if (VEC > 1) { Vec<T> v; v.pack(xv); v.store(y + off); } else stf(y, off, xv[0]);
   }
 }
 
@@ -213,28 +260,44 @@ bn_act_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __
                   const float* __restrict__ scale, const float* __restrict__ shift,
                   const float* __restrict__ s1, const float* __restrict__ s2, int act, float slope) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-    const int64_t off = i * VEC;
-    const int c0 = (int)(off % C);
-    float xv[VEC], dv[VEC], rv[VEC], gv[VEC];
-    if (VEC > 1) {
-      Vec<T> v; v.load(x + off); v.unpack(xv); v.load(dy + off); v.unpack(dv);
-      if (res) { v.load(res + off); v.unpack(rv); }
-    } else { xv[0] = ldf(x, off); dv[0] = ldf(dy, off); if (res) rv[0] = ldf(res, off); }
+  float sc[VEC], sh[VEC], mu[VEC], is[VEC], k1[VEC], k2[VEC];
+  int cc = -1;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 2 * stride) {
+    const int64_t i2 = i + stride;
+    const bool two = i2 < nvec;
+    Pk<T, VEC> xa, xb, da, db, ra, rb;
+    xa.load(x, i * VEC); da.load(dy, i * VEC);
+    if (res) ra.load(res, i * VEC);
+    if (two) { xb.load(x, i2 * VEC); db.load(dy, i2 * VEC); if (res) rb.load(res, i2 * VEC); }
 #pragma unroll
-    for (int k = 0; k < VEC; k++) {
-      const int c = c0 + k;
-      float z = xv[k] * scale[c] + shift[c];
-      if (res) z += rv[k];
-      float g = dv[k] * act_dz(z, act, slope);
-      float xh = (xv[k] - mean[c]) * invstd[c];
-      gv[k] = g;
-      xv[k] = scale[c] * (g - s1[c] * inv_rows - xh * s2[c] * inv_rows);
+    for (int u = 0; u < 2; u++) {
+      if (u == 1 && !two) break;
+      const int64_t off = (u ? i2 : i) * VEC;
+      const int c0 = (int)(off % C);
+      if (c0 != cc) {
+        if (VEC > 1) {
+          ldvecf<VEC>(scale, c0, sc, 1.f); ldvecf<VEC>(shift, c0, sh, 0.f); ldvecf<VEC>(mean, c0, mu, 0.f);
+          ldvecf<VEC>(invstd, c0, is, 1.f); ldvecf<VEC>(s1, c0, k1, 0.f); ldvecf<VEC>(s2, c0, k2, 0.f);
+        } else { sc[0] = scale[c0]; sh[0] = shift[c0]; mu[0] = mean[c0]; is[0] = invstd[c0]; k1[0] = s1[c0]; k2[0] = s2[c0]; }
+#pragma unroll
+        for (int k = 0; k < VEC; k++) { k1[k] *= inv_rows; k2[k] *= inv_rows; }
+        cc = c0;
+      }
+      float xv[VEC], dv[VEC], rv[VEC], gv[VEC];
+      (u ? xb : xa).unpack(xv); (u ? db : da).unpack(dv);
+      if (res) (u ? rb : ra).unpack(rv);
+#pragma unroll
+      for (int k = 0; k < VEC; k++) {
+        float z = xv[k] * sc[k] + sh[k];
+        if (res) z += rv[k];
+        float g = dv[k] * act_dz(z, act, slope);
+        float xh = (xv[k] - mu[k]) * is[k];
+        gv[k] = g;
+        xv[k] = sc[k] * (g - k1[k] - xh * k2[k]);
+      }
+      stvec<T, VEC>(dx, off, xv);
+      if (dres) stvec<T, VEC>(dres, off, gv);
     }
-    if (VEC > 1) {
-      Vec<T> v; v.pack(xv); v.store(dx + off);
-      if (dres) { v.pack(gv); v.store(dres + off); }
-    } else { stf(dx, off, xv[0]); if (dres) stf(dres, off, gv[0]); }
   }
 }
 
@@ -296,26 +359,6 @@ __device__ __forceinline__ void block_sum2(float& a, float& b) {
     a = warp_sum(a); b = warp_sum(b);
   }
   __syncthreads();
-}
-
-template <typename T, int VEC>
-__device__ __forceinline__ void ldvec(const T* __restrict__ p, int64_t off, float* out) {
-  if (VEC > 1) { Vec<T> v; v.load(p + off); v.unpack(out); } else out[0] = ldf(p, off);
-}
-// a VEC-element load kept packed (16 bytes for bf16 x 8) until it is consumed
-template <typename T, int VEC> struct Pk {
-  Vec<T> v;
-  __device__ __forceinline__ void load(const T* __restrict__ p, int64_t off) { v.load(p + off); }
-  __device__ __forceinline__ void unpack(float* o) const { v.unpack(o); }
-};
-template <typename T> struct Pk<T, 1> {
-  float v;
-  __device__ __forceinline__ void load(const T* __restrict__ p, int64_t off) { v = ldf(p, off); }
-  __device__ __forceinline__ void unpack(float* o) const { o[0] = v; }
-};
-template <typename T, int VEC>
-__device__ __forceinline__ void stvec(T* __restrict__ p, int64_t off, float* v) {
-  if (VEC > 1) { Vec<T> o; o.pack(v); o.store(p + off); } else stf(p, off, v[0]);
 }
 
 // grid (chunks, N): per-chunk (sum x, sum x^2) of one sample.
@@ -594,6 +637,28 @@ static int act_t(const void* a, const void* dy, void* out, int64_t n, int act, f
 }  // namespace b2c
 
 using namespace b2c;
+
+// dbias of b2c_conv3d_wgrad: out[c] = sum_r x[r][c] through the deterministic two-stage tree
+// (the sum-of-squares output lands in the scratch tail).  ws >= channel_sum_workspace(rows, C).
+namespace b2c {
+size_t channel_sum_workspace(int64_t rows, int64_t C) {
+  if (rows <= 0 || C <= 0) return 0;
+  return ((size_t)reduce_blocks(rows) * 2 + 1) * C * sizeof(float);
+}
+int channel_sum(const void* x, int64_t rows, int C, int dt, float* out, void* ws, size_t wsb, cudaStream_t st) {
+  if (rows <= 0 || C <= 0) return B2C_OK;
+  if (!ws || wsb < channel_sum_workspace(rows, C)) return B2C_ERR_WORKSPACE;
+  float* sq = static_cast<float*>(ws);
+  void* part = sq + C;
+  const size_t pb = wsb - (size_t)C * sizeof(float);
+  if (dt == B2C_BF16) {
+    BnBwdF<__nv_bfloat16> f{};
+    return chan_reduce<__nv_bfloat16, false>(static_cast<const __nv_bfloat16*>(x), rows, C, f, out, sq, part, pb, st);
+  }
+  BnBwdF<float> f{};
+  return chan_reduce<float, false>(static_cast<const float*>(x), rows, C, f, out, sq, part, pb, st);
+}
+}  // namespace b2c
 
 extern "C" size_t b2c_stats_workspace(int64_t rows, int64_t C) {
   if (rows <= 0 || C <= 0) return 0;

@@ -198,6 +198,22 @@ int b2c_act_fwd(const void* x, void* y, int64_t n, int dtype, int act,
 int b2c_act_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype,
                 int act, float slope, b2c_stream);
 
+/* ---- x2 resampling on NDHWC tensors ------------- *
+ * nearest x2 of the channel slice [c0, c0 + c) of x [n,d,h,w,cx] into
+ * y [n,2d,2h,2w,c]: replaces `x[:, :Cout]` + F.interpolate(scale_factor=2)
+ * (utils.py:76-80, biggan.py:26,31).  bwd: dx [n,d,h,w,cx] = 2x2x2 block
+ * sums of dy inside the slice, 0 outside.                                  */
+int b2c_upsample2x_fwd(const void* x, void* y, int64_t n, int d, int h, int w,
+                       int cx, int c0, int c, int dtype, b2c_stream);
+int b2c_upsample2x_bwd(const void* dy, void* dx, int64_t n, int d, int h,
+                       int w, int cx, int c0, int c, int dtype, b2c_stream);
+/* nn.AvgPool3d(2) (utils.py:113-116,128-129; biggan.py:86,92): x [n,d,h,w,c]
+ * -> y [n,d/2,h/2,w/2,c] (floor); bwd writes every element of dx.          */
+int b2c_avgpool2_fwd(const void* x, void* y, int64_t n, int d, int h, int w,
+                     int c, int dtype, b2c_stream);
+int b2c_avgpool2_bwd(const void* dy, void* dx, int64_t n, int d, int h, int w,
+                     int c, int dtype, b2c_stream);
+
 #ifdef __cplusplus
 }
 #endif

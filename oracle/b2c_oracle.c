@@ -477,3 +477,72 @@ int b2c_act_bwd(const void* y, const void* dy, void* dx, int64_t n, int dt, int 
   for (int64_t i = 0; i < n; i++) st(dx, i, dt, ld(dy, i, dt) * act_dy(ld(y, i, dt), act, slope));
   return B2C_OK;
 }
+
+/* ---- x2 resampling (utils.py:76-80 nearest x2 + channel drop; nn.AvgPool3d(2)) ----------- */
+int b2c_upsample2x_fwd(const void* x, void* y, int64_t n, int d, int h, int w, int cx, int c0, int c, int dt,
+                       b2c_stream s) {
+  (void)s;
+  if (!x || !y || !dt_ok(dt) || c0 < 0 || c0 + c > cx) return B2C_ERR_INVALID;
+  for (int64_t in = 0; in < n; in++)
+    for (int od = 0; od < 2 * d; od++)
+      for (int oh = 0; oh < 2 * h; oh++)
+        for (int ow = 0; ow < 2 * w; ow++)
+          for (int k = 0; k < c; k++) {
+            int64_t src = ((((int64_t)in * d + od / 2) * h + oh / 2) * w + ow / 2) * cx + c0 + k;
+            int64_t dst = ((((int64_t)in * 2 * d + od) * 2 * h + oh) * 2 * w + ow) * c + k;
+            st(y, dst, dt, ld(x, src, dt));
+          }
+  return B2C_OK;
+}
+int b2c_upsample2x_bwd(const void* dy, void* dx, int64_t n, int d, int h, int w, int cx, int c0, int c, int dt,
+                       b2c_stream s) {
+  (void)s;
+  if (!dy || !dx || !dt_ok(dt) || c0 < 0 || c0 + c > cx) return B2C_ERR_INVALID;
+  for (int64_t in = 0; in < n; in++)
+    for (int id = 0; id < d; id++)
+      for (int ih = 0; ih < h; ih++)
+        for (int iw = 0; iw < w; iw++)
+          for (int k = 0; k < cx; k++) {
+            double acc = 0.0;
+            if (k >= c0 && k < c0 + c)
+              for (int q = 0; q < 8; q++) {
+                int64_t src = ((((int64_t)in * 2 * d + 2 * id + (q >> 2)) * 2 * h + 2 * ih + ((q >> 1) & 1)) * 2 * w +
+                               2 * iw + (q & 1)) * c + (k - c0);
+                acc += ld(dy, src, dt);
+              }
+            st(dx, ((((int64_t)in * d + id) * h + ih) * w + iw) * cx + k, dt, acc);
+          }
+  return B2C_OK;
+}
+int b2c_avgpool2_fwd(const void* x, void* y, int64_t n, int d, int h, int w, int c, int dt, b2c_stream s) {
+  (void)s;
+  if (!x || !y || !dt_ok(dt) || d < 2 || h < 2 || w < 2) return B2C_ERR_INVALID;
+  int od = d / 2, oh = h / 2, ow = w / 2;
+  for (int64_t in = 0; in < n; in++)
+    for (int a = 0; a < od; a++)
+      for (int b = 0; b < oh; b++)
+        for (int e = 0; e < ow; e++)
+          for (int k = 0; k < c; k++) {
+            double acc = 0.0;
+            for (int q = 0; q < 8; q++)
+              acc += ld(x, ((((int64_t)in * d + 2 * a + (q >> 2)) * h + 2 * b + ((q >> 1) & 1)) * w + 2 * e + (q & 1)) * c + k, dt);
+            st(y, ((((int64_t)in * od + a) * oh + b) * ow + e) * c + k, dt, acc * 0.125);
+          }
+  return B2C_OK;
+}
+int b2c_avgpool2_bwd(const void* dy, void* dx, int64_t n, int d, int h, int w, int c, int dt, b2c_stream s) {
+  (void)s;
+  if (!dy || !dx || !dt_ok(dt) || d < 2 || h < 2 || w < 2) return B2C_ERR_INVALID;
+  int od = d / 2, oh = h / 2, ow = w / 2;
+  for (int64_t in = 0; in < n; in++)
+    for (int a = 0; a < d; a++)
+      for (int b = 0; b < h; b++)
+        for (int e = 0; e < w; e++)
+          for (int k = 0; k < c; k++) {
+            double v = 0.0;
+            if (a / 2 < od && b / 2 < oh && e / 2 < ow)
+              v = 0.125 * ld(dy, ((((int64_t)in * od + a / 2) * oh + b / 2) * ow + e / 2) * c + k, dt);
+            st(dx, ((((int64_t)in * d + a) * h + b) * w + e) * c + k, dt, v);
+          }
+  return B2C_OK;
+}
