@@ -34,6 +34,13 @@ class ConvDesc(C.Structure):
                 ("algo", C.c_int32)]
 
 
+class FirDesc(C.Structure):
+    """b2c_fir_desc (include/b2c.h)."""
+    _fields_ = [("n", C.c_int64), ("c", C.c_int32), ("in_", C.c_int32 * 3), ("out", C.c_int32 * 3),
+                ("k", C.c_int32 * 3), ("pad", C.c_int32 * 3), ("up", C.c_int32), ("down", C.c_int32),
+                ("dtype", C.c_int32)]
+
+
 class Fusion(C.Structure):
     _fields_ = [("bias", C.c_void_p), ("act", C.c_int32), ("slope", C.c_float)]
 
@@ -73,6 +80,8 @@ _SIGNATURES = {
     "b2c_upsample2x_bwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_avgpool2_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_avgpool2_bwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b2c_fir3d_fwd": (_i32, [C.POINTER(FirDesc), C.POINTER(C.c_float), _vp, _vp, _vp]),
+    "b2c_fir3d_bwd": (_i32, [C.POINTER(FirDesc), C.POINTER(C.c_float), _vp, _vp, _vp]),
 }
 EXPORTS = tuple(_SIGNATURES)
 

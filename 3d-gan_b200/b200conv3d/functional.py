@@ -693,3 +693,76 @@ class _AvgPool2Fn(Function):
 def avg_pool2(x):
     """Drop-in for ``nn.AvgPool3d(2)(x)``."""
     return _AvgPool2Fn.apply(x)
+
+
+# --------------------------------------------------------------- depthwise FIR resampling
+class _FirFn(Function):
+    """One NDHWC pass for pad / zero-insert / depthwise FIR / decimate (stylegan.py:172-200)."""
+
+    @staticmethod
+    def forward(ctx, x, taps, k, up, down, pad_lo, out_sp):
+        _check_device(x)
+        cd = _keep_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, c = xb.shape
+        desc = _lib.FirDesc()
+        desc.n, desc.c, desc.up, desc.down, desc.dtype = n, c, up, down, _dt(cd)
+        for i, (a, o) in enumerate(zip((d, h, w), out_sp)):
+            desc.in_[i], desc.out[i], desc.k[i], desc.pad[i] = a, o, k[i], pad_lo[i]
+        tarr = (C.c_float * len(taps))(*taps)
+        yl, y = alloc_out(n, out_sp[0], out_sp[1], out_sp[2], c, cd, x.device)
+        with _dev(x):
+            check(_lib.lib().b2c_fir3d_fwd(C.byref(desc), tarr, _ptr(xb), _ptr(y), _stream(x)), "fir3d_fwd")
+        ctx.desc, ctx.tarr, ctx.cd, ctx.x_dtype, ctx.in_shape = desc, tarr, cd, x.dtype, (n, d, h, w, c)
+        return yl
+
+    @staticmethod
+    def backward(ctx, gy):
+        n, d, h, w, c = ctx.in_shape
+        gyb = to_ndhwc(gy, ctx.cd)
+        dxl, dx = alloc_out(n, d, h, w, c, ctx.cd, gy.device)
+        with _dev(gy):
+            check(_lib.lib().b2c_fir3d_bwd(C.byref(ctx.desc), ctx.tarr, _ptr(gyb), _ptr(dx), _stream(gy)), "fir3d_bwd")
+        return (dxl if ctx.x_dtype == ctx.cd else dxl.to(ctx.x_dtype)), None, None, None, None, None, None
+
+
+def upfirdn3d(x, f, up=1, down=1, padding=0, flip_filter=False, gain=1):
+    """Drop-in for ``stylegan._upfirdn3d_ref`` (stylegan.py:172-200) for the isotropic arguments the
+    reference uses: `f` a 3-D filter (or None), integer `up` / `down`, `padding` an int, 3 or 6 ints
+    in the reference's F.pad order.  The filter carries no gradient (a constant buffer there)."""
+    if isinstance(up, (list, tuple)) or isinstance(down, (list, tuple)):
+        if len(set(up if isinstance(up, (list, tuple)) else [up])) != 1 or \
+                len(set(down if isinstance(down, (list, tuple)) else [down])) != 1:
+            raise NotImplementedError("anisotropic up / down factors are not on the reference's path")
+        up = up[0] if isinstance(up, (list, tuple)) else up
+        down = down[0] if isinstance(down, (list, tuple)) else down
+    p = padding
+    if isinstance(p, int):
+        p = [p] * 6
+    elif len(p) == 3:
+        p = [p[0], p[0], p[1], p[1], p[2], p[2]]
+    p = [int(v) for v in p]
+    if len(p) != 6:
+        raise ValueError("padding must be an int, 3 ints or 6 ints")
+    if min(p) < 0 and (len(set(p[0::2])) != 1 or len(set(p[1::2])) != 1):
+        # stylegan.py:186-187 pads (dim4, dim3, dim2) but crops (dim3, dim2, dim4): only defined alike
+        raise NotImplementedError("anisotropic negative padding (crop) is not on the reference's path")
+    if f is None:
+        taps, k = [1.0], (1, 1, 1)
+    else:
+        if f.dim() != 3:
+            raise NotImplementedError("upfirdn3d takes the reference's 3-D (4x4x4) filters")
+        ff = f.detach().float().cpu() * float(gain)
+        if not flip_filter:
+            ff = ff.flip([0, 1, 2])
+        taps, k = ff.reshape(-1).tolist(), tuple(ff.shape)
+    # F.pad order: (p[0], p[1]) -> dim 4, (p[2], p[3]) -> dim 3, (p[4], p[5]) -> dim 2
+    lo = (p[4], p[2], p[0])
+    hi = (p[5], p[3], p[1])
+    out_sp = []
+    for a, l, hh, kk in zip(x.shape[2:], lo, hi, k):
+        full = a * up + l + hh - kk + 1
+        if full <= 0:
+            raise ValueError("upfirdn3d: empty output")
+        out_sp.append(-(-full // down))
+    return _FirFn.apply(x, taps, k, int(up), int(down), lo, tuple(out_sp))

@@ -1,0 +1,119 @@
+"""The StyleGAN2 convolution funnel of the reference on the B200 path (SURVEY.md §8(a) rows
+a9-a12): every convolution of `stylegan.py` goes through `conv3d_resample`
+(stylegan.py:202-294) and, in the generator, `modulated_conv3d` (stylegan.py:396-444).
+
+Same names, argument meaning and results as the reference for the arguments its layers pass
+(isotropic int `up` / `down` / `padding`, 3-D resample filter, `groups=1`,
+`fused_modconv=False` - the grouped "fused" branch is dead code in training and crashes with
+demodulation).  What runs where:
+
+  * dense convolutions / transposed convolutions -> b2c_conv3d_* (tcgen05 path in bf16);
+  * pad + depthwise 4x4x4 FIR + decimation / zero-insertion (`_upfirdn3d_ref`,
+    stylegan.py:172-200) -> ONE b2c_fir3d pass (no materialised padding, no groups=C conv);
+  * style scaling of the input, demodulation coefficients, noise / bias / activation -> ATen
+    elementwise ops on NDHWC tensors for now (fusing them into the conv prologue / epilogue is
+    the `in_scale` / `out_scale` / `addend` extension sketched in SURVEY §8(b)).
+
+With `b200conv3d.install()` the reference's own stylegan.py reaches the same kernels through
+`F.conv3d` / `F.conv_transpose3d`, except its `groups=C` FIR call, which this module replaces.
+"""
+import torch
+
+from . import functional as BF
+
+
+def make_resample_filter(taps=(1, 3, 3, 1)):
+    """The reference's (non-separable, "odd") 4x4x4 low-pass filter, stylegan.py:462-465."""
+    f = torch.tensor([float(t) for t in taps])
+    f = (f[None, None, :] * f[None, :, None]).repeat((1, 4, 1)).reshape(4, 4, 4)
+    return f / f.sum()
+
+
+def _conv(x, w, stride=1, padding=0, transpose=False, flip_weight=True):
+    """stylegan.py:164-170.  `flip_weight=False` means true convolution: reverse the taps."""
+    if not flip_weight:
+        w = w.flip([2, 3, 4])
+    if transpose:
+        return BF.conv_transpose3d(x, w, None, stride, padding)
+    return BF.conv3d(x, w, None, stride, padding)
+
+
+def _resample_pads(fk, up, down, padding):
+    """Padding (before, after) relative to the up-sampled grid once the FIR taps are accounted
+    for (stylegan.py:228-241)."""
+    lo = hi = int(padding)
+    if up > 1:
+        lo, hi = lo + (fk + up - 1) // 2, hi + (fk - up) // 2
+    if down > 1:
+        lo, hi = lo + (fk - down + 1) // 2, hi + (fk - down) // 2
+    return lo, hi
+
+
+def conv3d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight=True, flip_filter=False):
+    if groups != 1:
+        raise NotImplementedError("grouped conv3d_resample is only reached by the dead fused_modconv branch")
+    if not all(isinstance(v, int) for v in (up, down, padding)):
+        raise NotImplementedError("the reference passes one int for up / down / padding")
+    k = int(w.shape[2])
+    fk = 1 if f is None else int(f.shape[0])
+    lo, hi = _resample_pads(fk, up, down, padding)
+    fir = lambda t, **kw: BF.upfirdn3d(t, f, flip_filter=flip_filter, **kw)   # noqa: E731
+    pads = lambda a, b: [a, b, a, b, a, b]                                    # noqa: E731
+
+    if up == 1 and down == 1:
+        if lo == hi and lo >= 0:
+            return _conv(x, w, padding=lo, flip_weight=flip_weight)
+        return _conv(BF.upfirdn3d(x, None, padding=pads(lo, hi)), w, flip_weight=flip_weight)
+    if up == 1:                                  # down-sampling
+        if k == 1:                               # decimate first, then the 1x1x1 conv (:244-247)
+            return _conv(fir(x, down=down, padding=pads(lo, hi)), w, flip_weight=flip_weight)
+        return _conv(fir(x, padding=pads(lo, hi)), w, stride=down, flip_weight=flip_weight)     # (:257-260)
+    if k == 1 and down == 1:                     # 1x1x1 conv first, then zero-insert + FIR (:250-254)
+        return fir(_conv(x, w, flip_weight=flip_weight), up=up, padding=pads(lo, hi), gain=up ** 2)
+    # up-sampling conv = transposed conv with stride `up`, then the FIR on what is left of the
+    # padding (:262-282); the reference's FIR gain is up**2 in 3-D as well - kept
+    lo, hi = lo - (k - 1), hi - (k - up)
+    trim = max(min(-lo, -hi), 0)
+    y = _conv(x, w.transpose(0, 1), stride=up, padding=trim, transpose=True, flip_weight=not flip_weight)
+    y = fir(y, padding=pads(lo + trim, hi + trim), gain=up ** 2)
+    if down > 1:
+        y = fir(y, down=down)
+    return y
+
+
+def demod_coefficients(weight, styles):
+    """dcoefs[n, o] = rsqrt(sum_{i,k} (w[o,i,k] * s[n,i])^2 + 1e-8)  (stylegan.py:419-422), as the
+    small GEMM  s^2 [N, I] x (sum_k w^2)^T [I, O]  instead of an [N, O, I, k^3] temporary."""
+    w2 = weight.float().square().sum(dim=[2, 3, 4])            # [O, I]
+    return (styles.float().square() @ w2.t() + 1e-8).rsqrt()   # [N, O]
+
+
+def modulated_conv3d(x, weight, styles, noise=None, up=1, down=1, padding=0, resample_filter=None,
+                     demodulate=True, flip_weight=True, fused_modconv=False):
+    if fused_modconv:
+        raise NotImplementedError("fused_modconv=True is the reference's grouped branch (dead in training, "
+                                  "stylegan.py:437-444); call with fused_modconv=False")
+    n = x.shape[0]
+    dcoefs = demod_coefficients(weight, styles) if demodulate else None
+    x = x * styles.to(x.dtype).reshape(n, -1, 1, 1, 1)
+    x = conv3d_resample(x, weight.to(x.dtype), f=resample_filter, up=up, down=down, padding=padding,
+                        flip_weight=flip_weight)
+    if dcoefs is not None:
+        d = dcoefs.to(x.dtype).reshape(n, -1, 1, 1, 1)
+        return torch.addcmul(noise.to(x.dtype), x, d) if noise is not None else x * d
+    return x + noise.to(x.dtype) if noise is not None else x
+
+
+def bias_act(x, b=None, dim=1, act="linear"):
+    """stylegan.py:118-124 (lrelu slope 0.2, no gain)."""
+    if b is not None:
+        x = x + b.reshape([-1 if i == dim else 1 for i in range(x.ndim)])
+    if act == "linear":
+        return x
+    if act == "lrelu":
+        return BF.activation(x, "lrelu", 0.2)
+    if act == "relu":
+        return BF.activation(x, "relu")
+    if act == "tanh":
+        return BF.activation(x, "tanh")
+    raise NotImplementedError("activation %r is not used by the reference's networks" % (act,))

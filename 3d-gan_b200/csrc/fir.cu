@@ -1,0 +1,230 @@
+// fir.cu — depthwise FIR resampling on NDHWC tensors (stylegan.py:172-200 `_upfirdn3d_ref`):
+// zero-insert upsampling, pad / crop, one [kd][kh][kw] filter shared by all channels
+// (F.conv3d(groups=C) over a repeated filter in the reference), decimation.  HBM bound.
+//
+//   y[n, o, c] = sum_k f[k] * xup[n, o*down + k - pad, c],   xup[j] = x[j / up] if up | j, else 0
+//
+// `f` arrives as CORRELATION taps (the caller has applied the reference's flip and gain).
+// Padding is never materialised (bounds checks; negative pad = crop), decimation and zero
+// insertion are index arithmetic: one read of x, one write of y.  The backward pass w.r.t. x
+// is the adjoint gather (the filter is a constant buffer in the reference, it has no gradient).
+#include "common.cuh"
+
+namespace b2c {
+namespace {
+
+constexpr int kThr = 128;
+constexpr int kMaxTaps = 64;
+
+struct FirP {
+  int64_t n;
+  int id, ih, iw, od, oh, ow, c;
+  int kd, kh, kw, up, down;
+  int pad[3];
+  float f[kMaxTaps];
+};
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <typename T, int VEC>
+__device__ __forceinline__ void fir_ld(const T* p, float* o) {
+  if (VEC > 1) { Vec<T> v; v.load(p); v.unpack(o); } else o[0] = ldf(p, 0);
+}
+template <typename T, int VEC>
+__device__ __forceinline__ void fir_st(T* p, float* o) {
+  if (VEC > 1) { Vec<T> v; v.pack(o); v.store(p); } else stf(p, 0, o[0]);
+}
+
+// generic forward: one thread per (output voxel, channel vector)
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThr) fir_fwd_kernel(const __grid_constant__ FirP P, const T* __restrict__ x,
+                                                        T* __restrict__ y, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = P.c / VEC;
+  const int c = (int)(idx % cv) * VEC;
+  int64_t v = idx / cv;
+  T* dst = y + v * (int64_t)P.c + c;
+  const int ow = (int)(v % P.ow); v /= P.ow;
+  const int oh = (int)(v % P.oh); v /= P.oh;
+  const int od = (int)(v % P.od);
+  const int64_t n = v / P.od;
+  float acc[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; i++) acc[i] = 0.f;
+  for (int a = 0; a < P.kd; a++) {
+    const int jd = od * P.down + a - P.pad[0];
+    if (jd < 0 || jd >= P.id * P.up || jd % P.up) continue;
+    for (int b = 0; b < P.kh; b++) {
+      const int jh = oh * P.down + b - P.pad[1];
+      if (jh < 0 || jh >= P.ih * P.up || jh % P.up) continue;
+      const T* row = x + ((n * P.id + jd / P.up) * P.ih + jh / P.up) * (int64_t)P.iw * P.c + c;
+      for (int e = 0; e < P.kw; e++) {
+        const int jw = ow * P.down + e - P.pad[2];
+        if (jw < 0 || jw >= P.iw * P.up || jw % P.up) continue;
+        float t[VEC];
+        fir_ld<T, VEC>(row + (int64_t)(jw / P.up) * P.c, t);
+        const float fk = P.f[(a * P.kh + b) * P.kw + e];
+#pragma unroll
+        for (int i = 0; i < VEC; i++) acc[i] += fk * t[i];
+      }
+    }
+  }
+  fir_st<T, VEC>(dst, acc);
+}
+
+// generic adjoint: dx[n, i, c] = sum over (o, k) with o*down + k - pad == i*up of f[k] * dy[n, o, c]
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThr) fir_bwd_kernel(const __grid_constant__ FirP P, const T* __restrict__ dy,
+                                                        T* __restrict__ dx, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = P.c / VEC;
+  const int c = (int)(idx % cv) * VEC;
+  int64_t v = idx / cv;
+  T* dst = dx + v * (int64_t)P.c + c;
+  const int iw = (int)(v % P.iw); v /= P.iw;
+  const int ih = (int)(v % P.ih); v /= P.ih;
+  const int id = (int)(v % P.id);
+  const int64_t n = v / P.id;
+  float acc[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; i++) acc[i] = 0.f;
+  for (int a = 0; a < P.kd; a++) {
+    const int td = id * P.up + P.pad[0] - a;
+    if (td < 0 || td % P.down || td / P.down >= P.od) continue;
+    for (int b = 0; b < P.kh; b++) {
+      const int th = ih * P.up + P.pad[1] - b;
+      if (th < 0 || th % P.down || th / P.down >= P.oh) continue;
+      const T* row = dy + ((n * P.od + td / P.down) * P.oh + th / P.down) * (int64_t)P.ow * P.c + c;
+      for (int e = 0; e < P.kw; e++) {
+        const int tw = iw * P.up + P.pad[2] - e;
+        if (tw < 0 || tw % P.down || tw / P.down >= P.ow) continue;
+        float t[VEC];
+        fir_ld<T, VEC>(row + (int64_t)(tw / P.down) * P.c, t);
+        const float fk = P.f[(a * P.kh + b) * P.kw + e];
+#pragma unroll
+        for (int i = 0; i < VEC; i++) acc[i] += fk * t[i];
+      }
+    }
+  }
+  fir_st<T, VEC>(dst, acc);
+}
+
+// up = down = 1, kw <= 4: a thread owns WB = 4 adjacent outputs along w of one channel vector and
+// loads kw + 3 input vectors per (kd, kh) line instead of 4 * kw.
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThr) fir_fwd_w4_kernel(const __grid_constant__ FirP P, const T* __restrict__ x,
+                                                           T* __restrict__ y, int64_t total) {
+  constexpr int WB = 4, KW = 4;
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = P.c / VEC;
+  const int c = (int)(idx % cv) * VEC;
+  int64_t v = idx / cv;
+  const int wblocks = (P.ow + WB - 1) / WB;
+  const int ow0 = (int)(v % wblocks) * WB; v /= wblocks;
+  const int oh = (int)(v % P.oh); v /= P.oh;
+  const int od = (int)(v % P.od);
+  const int64_t n = v / P.od;
+  float acc[WB][VEC];
+#pragma unroll
+  for (int q = 0; q < WB; q++)
+#pragma unroll
+    for (int i = 0; i < VEC; i++) acc[q][i] = 0.f;
+  for (int a = 0; a < P.kd; a++) {
+    const int jd = od + a - P.pad[0];
+    if (jd < 0 || jd >= P.id) continue;
+    for (int b = 0; b < P.kh; b++) {
+      const int jh = oh + b - P.pad[1];
+      if (jh < 0 || jh >= P.ih) continue;
+      const T* row = x + ((n * P.id + jd) * P.ih + jh) * (int64_t)P.iw * P.c + c;
+      const float* fk = P.f + (a * P.kh + b) * P.kw;
+      float in[WB + KW - 1][VEC];
+#pragma unroll
+      for (int j = 0; j < WB + KW - 1; j++) {
+        const int jw = ow0 + j - P.pad[2];
+        if (j < WB + P.kw - 1 && jw >= 0 && jw < P.iw) fir_ld<T, VEC>(row + (int64_t)jw * P.c, in[j]);
+        else {
+#pragma unroll
+          for (int i = 0; i < VEC; i++) in[j][i] = 0.f;
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < KW; e++) {
+        if (e < P.kw) {
+          const float w = fk[e];
+#pragma unroll
+          for (int q = 0; q < WB; q++)
+#pragma unroll
+            for (int i = 0; i < VEC; i++) acc[q][i] += w * in[q + e][i];
+        }
+      }
+    }
+  }
+  T* dst = y + (((n * P.od + od) * P.oh + oh) * (int64_t)P.ow + ow0) * P.c + c;
+#pragma unroll
+  for (int q = 0; q < WB; q++)
+    if (ow0 + q < P.ow) fir_st<T, VEC>(dst + (int64_t)q * P.c, acc[q]);
+}
+
+template <typename T>
+int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const bool vec = P.c % V == 0 && aligned16(a) && aligned16(b);
+  const T* ap = static_cast<const T*>(a); T* bp = static_cast<T*>(b);
+  const int cvn = P.c / (vec ? V : 1);
+  if (P.up == 1 && P.down == 1 && P.kw <= 4 && vec) {
+    // forward as is; the adjoint of a unit-rate FIR is the FIR with the filter reversed and pad' = K-1-pad
+    FirP Q = P;
+    if (bwd) {
+      Q.id = P.od; Q.ih = P.oh; Q.iw = P.ow; Q.od = P.id; Q.oh = P.ih; Q.ow = P.iw;
+      Q.pad[0] = P.kd - 1 - P.pad[0]; Q.pad[1] = P.kh - 1 - P.pad[1]; Q.pad[2] = P.kw - 1 - P.pad[2];
+      const int T_ = P.kd * P.kh * P.kw;
+      for (int t = 0; t < T_; t++) Q.f[t] = P.f[T_ - 1 - t];
+    }
+    const int64_t total = Q.n * Q.od * Q.oh * ((Q.ow + 3) / 4) * cvn;
+    if (total == 0) return B2C_OK;
+    const int64_t blocks = cdiv(total, (int64_t)kThr);
+    if (blocks > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+    fir_fwd_w4_kernel<T, V><<<(unsigned)blocks, kThr, 0, st>>>(Q, ap, bp, total);
+    return launched();
+  }
+  const int64_t total = (bwd ? P.n * P.id * P.ih * P.iw : P.n * P.od * P.oh * P.ow) * cvn;
+  if (total == 0) return B2C_OK;
+  const int64_t blocks = cdiv(total, (int64_t)kThr);
+  if (blocks > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  if (!bwd) {
+    if (vec) fir_fwd_kernel<T, V><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
+    else fir_fwd_kernel<T, 1><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
+  } else {
+    if (vec) fir_bwd_kernel<T, V><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
+    else fir_bwd_kernel<T, 1><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
+  }
+  return launched();
+}
+
+int fir_entry(bool bwd, const b2c_fir_desc* d, const float* taps, const void* a, void* b, b2c_stream s) {
+  if (!d || !taps || !a || !b || !dt_ok(d->dtype)) return B2C_ERR_INVALID;
+  const int T_ = d->k[0] * d->k[1] * d->k[2];
+  if (d->n < 0 || d->c <= 0 || d->up < 1 || d->down < 1 || T_ < 1 || T_ > kMaxTaps) return B2C_ERR_INVALID;
+  for (int i = 0; i < 3; i++) if (d->in[i] <= 0 || d->out[i] <= 0 || d->k[i] < 1) return B2C_ERR_INVALID;
+  FirP P;
+  P.n = d->n; P.id = d->in[0]; P.ih = d->in[1]; P.iw = d->in[2];
+  P.od = d->out[0]; P.oh = d->out[1]; P.ow = d->out[2]; P.c = d->c;
+  P.kd = d->k[0]; P.kh = d->k[1]; P.kw = d->k[2]; P.up = d->up; P.down = d->down;
+  for (int i = 0; i < 3; i++) P.pad[i] = d->pad[i];
+  for (int t = 0; t < kMaxTaps; t++) P.f[t] = t < T_ ? taps[t] : 0.f;      // taps: HOST pointer
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return d->dtype == B2C_BF16 ? fir_run<__nv_bfloat16>(bwd, P, a, b, st) : fir_run<float>(bwd, P, a, b, st);
+}
+
+}  // namespace
+}  // namespace b2c
+
+extern "C" int b2c_fir3d_fwd(const b2c_fir_desc* d, const float* taps, const void* x, void* y, b2c_stream s) {
+  return b2c::fir_entry(false, d, taps, x, y, s);
+}
+extern "C" int b2c_fir3d_bwd(const b2c_fir_desc* d, const float* taps, const void* dy, void* dx, b2c_stream s) {
+  return b2c::fir_entry(true, d, taps, dy, dx, s);
+}

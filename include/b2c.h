@@ -214,6 +214,23 @@ int b2c_avgpool2_fwd(const void* x, void* y, int64_t n, int d, int h, int w,
 int b2c_avgpool2_bwd(const void* dy, void* dx, int64_t n, int d, int h, int w,
                      int c, int dtype, b2c_stream);
 
+/* ---- depthwise FIR resampling (stylegan.py:172-200 `_upfirdn3d_ref`) -- *
+ * y[n,o,c] = sum_k taps[k] * xup[n, o*down + k - pad, c] with xup the
+ * zero-inserted (x up) input; x [n,in,c], y [n,out,c] dense NDHWC.  One
+ * filter for all channels (the reference repeats f over groups = C,
+ * stylegan.py:195-197).  `taps` is a HOST array of k[0]*k[1]*k[2] <= 64
+ * correlation taps: the caller applies the reference's flip and gain
+ * (stylegan.py:190-192).  pad may be negative (crop, stylegan.py:187).
+ * bwd = gradient w.r.t. x (the filter is a constant buffer).               */
+typedef struct {
+  int64_t n;
+  int32_t c, in[3], out[3], k[3], pad[3], up, down, dtype;
+} b2c_fir_desc;
+int b2c_fir3d_fwd(const b2c_fir_desc*, const float* taps, const void* x,
+                  void* y, b2c_stream);
+int b2c_fir3d_bwd(const b2c_fir_desc*, const float* taps, const void* dy,
+                  void* dx, b2c_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -546,3 +546,56 @@ int b2c_avgpool2_bwd(const void* dy, void* dx, int64_t n, int d, int h, int w, i
           }
   return B2C_OK;
 }
+
+/* ---- depthwise FIR resampling (stylegan.py:172-200) ---------------------------------------- */
+static int fir_ok(const b2c_fir_desc* d, const float* taps, const void* a, const void* b) {
+  if (!d || !taps || !a || !b || !dt_ok(d->dtype)) return 0;
+  int T = d->k[0] * d->k[1] * d->k[2];
+  return d->n >= 0 && d->c > 0 && d->up >= 1 && d->down >= 1 && T >= 1 && T <= 64;
+}
+int b2c_fir3d_fwd(const b2c_fir_desc* d, const float* taps, const void* x, void* y, b2c_stream s) {
+  (void)s;
+  if (!fir_ok(d, taps, x, y)) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < d->n; n++)
+    for (int od = 0; od < d->out[0]; od++)
+      for (int oh = 0; oh < d->out[1]; oh++)
+        for (int ow = 0; ow < d->out[2]; ow++)
+          for (int c = 0; c < d->c; c++) {
+            double acc = 0.0;
+            for (int a = 0; a < d->k[0]; a++)
+              for (int b = 0; b < d->k[1]; b++)
+                for (int e = 0; e < d->k[2]; e++) {
+                  int jd = od * d->down + a - d->pad[0], jh = oh * d->down + b - d->pad[1], jw = ow * d->down + e - d->pad[2];
+                  if (jd < 0 || jh < 0 || jw < 0 || jd % d->up || jh % d->up || jw % d->up) continue;
+                  jd /= d->up; jh /= d->up; jw /= d->up;
+                  if (jd >= d->in[0] || jh >= d->in[1] || jw >= d->in[2]) continue;
+                  acc += (double)taps[(a * d->k[1] + b) * d->k[2] + e] *
+                         ld(x, (((n * d->in[0] + jd) * d->in[1] + jh) * d->in[2] + jw) * d->c + c, d->dtype);
+                }
+            st(y, (((n * d->out[0] + od) * d->out[1] + oh) * d->out[2] + ow) * d->c + c, d->dtype, acc);
+          }
+  return B2C_OK;
+}
+int b2c_fir3d_bwd(const b2c_fir_desc* d, const float* taps, const void* dy, void* dx, b2c_stream s) {
+  (void)s;
+  if (!fir_ok(d, taps, dy, dx)) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < d->n; n++)
+    for (int id = 0; id < d->in[0]; id++)
+      for (int ih = 0; ih < d->in[1]; ih++)
+        for (int iw = 0; iw < d->in[2]; iw++)
+          for (int c = 0; c < d->c; c++) {
+            double acc = 0.0;
+            for (int a = 0; a < d->k[0]; a++)
+              for (int b = 0; b < d->k[1]; b++)
+                for (int e = 0; e < d->k[2]; e++) {
+                  int td = id * d->up + d->pad[0] - a, th = ih * d->up + d->pad[1] - b, tw = iw * d->up + d->pad[2] - e;
+                  if (td < 0 || th < 0 || tw < 0 || td % d->down || th % d->down || tw % d->down) continue;
+                  td /= d->down; th /= d->down; tw /= d->down;
+                  if (td >= d->out[0] || th >= d->out[1] || tw >= d->out[2]) continue;
+                  acc += (double)taps[(a * d->k[1] + b) * d->k[2] + e] *
+                         ld(dy, (((n * d->out[0] + td) * d->out[1] + th) * d->out[2] + tw) * d->c + c, d->dtype);
+                }
+            st(dx, (((n * d->in[0] + id) * d->in[1] + ih) * d->in[2] + iw) * d->c + c, d->dtype, acc);
+          }
+  return B2C_OK;
+}

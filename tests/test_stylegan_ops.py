@@ -1,0 +1,118 @@
+"""StyleGAN2 convolution funnel (b200conv3d/stylegan_ops.py: conv3d_resample, modulated_conv3d,
+upfirdn3d) against golden vectors of the UNMODIFIED reference functions
+(tests/golden/stylegan_ops_ref.npz, oracle/gen_golden_stylegan.py).
+
+CPU: (1) the pinned oracle restatement replays the golden file; (2) the product's HOST logic
+(padding dispatch, filter flips, demodulation GEMM) is run with the Python face bound to the
+C oracle library in a subprocess.  GPU: the same cases through the CUDA kernels, fp32 (exact
+kernels, 1e-4) and bf16 (tcgen05 / FIR kernels, 2e-2)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import ref_stylegan_ops as O  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden", "stylegan_ops_ref.npz")
+FIR_CASES = (("fir_img_up2", dict(up=2, padding=[2, 1, 2, 1, 2, 1], gain=8)),
+             ("fir_down2", dict(down=2, padding=[1, 1, 1, 1, 1, 1])),
+             ("fir_pad", dict(padding=[2, 1, 2, 1, 2, 1])),
+             ("fir_crop", dict(padding=[-1, -1, -1, -1, -1, -1])))
+
+
+def _grads(ops, case, dev, dtype=None, autocast=False):
+    name, kind = case[0], case[1]
+    x, w, s, nz, gy = O.case_inputs(*case)
+    x, w, s, gy = (t.to(dev) for t in (x, w, s, gy))
+    nz = nz.to(dev) if nz is not None else None
+    x.requires_grad_(True), w.requires_grad_(True), s.requires_grad_(True)
+    if autocast:
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            y = O.run_case(ops, case, x.bfloat16(), w, s, nz)
+        y.backward(gy.to(y.dtype))
+    else:
+        y = O.run_case(ops, case, x, w, s, nz)
+        y.backward(gy)
+    return {"y": y.detach(), "dx": x.grad, "dw": w.grad, "ds": s.grad if kind == "mod" else None}
+
+
+def _check(got, gold, name, tol):
+    for what, v in got.items():
+        if v is None:
+            continue
+        ref = torch.from_numpy(gold["%s.%s" % (name, what)])
+        err = ((v.float().cpu() - ref).abs().max() / ref.abs().max()).item()
+        assert err < tol, (name, what, err)
+
+
+@pytest.mark.parametrize("case", O.CASES, ids=[c[0] for c in O.CASES])
+def test_oracle_replays_reference_golden(case):
+    gold = np.load(GOLD)
+    _check(_grads(O, case, "cpu"), gold, case[0], 1e-5)
+
+
+def test_product_host_logic_on_oracle_library(oracle_path):
+    """Runs b200conv3d.stylegan_ops on CPU tensors with the C ABI bound to the oracle library."""
+    code = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r); sys.path.insert(0, %r)
+from b200conv3d import _lib
+_lib.use_library(%r, host=True)
+import b200conv3d.stylegan_ops as P
+import ref_stylegan_ops as O
+import test_stylegan_ops as T
+gold = np.load(T.GOLD)
+for case in O.CASES:
+    T._check(T._grads(P, case, "cpu"), gold, case[0], 1e-4)
+import b200conv3d.functional as BF
+f = P.make_resample_filter()
+assert torch.equal(f, O.make_filter())
+for name, kw in T.FIR_CASES:
+    y = BF.upfirdn3d(torch.from_numpy(gold[name + ".x"]), f, **kw)
+    assert (y - torch.from_numpy(gold[name + ".y"])).abs().max() < 1e-5, name
+print("HOST-OK")
+''' % (os.path.join(ROOT, "3d-gan_b200"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests"), oracle_path)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert "HOST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", O.CASES, ids=[c[0] for c in O.CASES])
+def test_gpu_stylegan_ops_fp32(case):
+    import b200conv3d.stylegan_ops as P
+    _check(_grads(P, case, "cuda"), np.load(GOLD), case[0], 1e-4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", O.CASES, ids=[c[0] for c in O.CASES])
+def test_gpu_stylegan_ops_bf16(case):
+    import b200conv3d.stylegan_ops as P
+    got = _grads(P, case, "cuda", autocast=True)
+    _check(got, np.load(GOLD), case[0], 3e-2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gpu_fir_vs_reference_golden(dtype):
+    import b200conv3d.functional as BF
+    import b200conv3d.stylegan_ops as P
+    gold = np.load(GOLD)
+    f = P.make_resample_filter()
+    for name, kw in FIR_CASES:
+        x = torch.from_numpy(gold[name + ".x"]).cuda().to(dtype).requires_grad_(True)
+        y = BF.upfirdn3d(x, f, **kw)
+        ref = torch.from_numpy(gold[name + ".y"])
+        tol = 1e-5 if dtype == torch.float32 else 2e-2
+        assert ((y.float().cpu() - ref).abs().max() / ref.abs().max()).item() < tol, name
+        # adjoint identity <fir(x), g> == <x, fir^T(g)> ties the backward kernel to the forward one
+        g = torch.randn_like(y)
+        y.backward(g)
+        lhs = (y.detach().float() * g.float()).sum().item()
+        rhs = (x.detach().float() * x.grad.float()).sum().item()
+        scale = (y.detach().float().norm() * g.float().norm()).item()       # Cauchy-Schwarz bound of either side
+        assert abs(lhs - rhs) < (1e-5 if dtype == torch.float32 else 1e-2) * scale, (name, lhs, rhs, scale)
