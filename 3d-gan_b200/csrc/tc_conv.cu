@@ -40,6 +40,7 @@ struct alignas(64) TcConvParams {
   uint32_t idesc, tmem_cols;
   const float* bias;
   int32_t bias_mod;      // bias index = column % bias_mod (point-convT: columns are (tap, co))
+  int32_t kb;            // channels per stage: 64 (128-B rows, SWIZZLE_128B) or 32 (64-B rows, SWIZZLE_64B)
   int32_t act;
   float slope;
   int32_t swap;          // 1: channels on UMMA M (filter tile = A), voxels on N: D^T = W * X^T (narrow Cout)
@@ -131,9 +132,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
   const uint32_t sbase = (raw + 1023u) & ~1023u;               // SW128 needs 1024-B alignment
   uint8_t* sgen = smem_raw + (sbase - raw);
   const int stages = P.stages;
-  const uint32_t a_bytes = (uint32_t)P.mt * kABytes;
+  const uint32_t row_bytes = (uint32_t)P.kb * 2u;              // 128 or 64
+  const uint32_t a_sub = (uint32_t)kBlockM * row_bytes;        // one 128-row sub-tile
+  const uint32_t a_bytes = (uint32_t)P.mt * a_sub;
   const uint32_t b_rows = (uint32_t)P.w_rows / NCTA;           // pair: each CTA stages half of the filter tile
-  const uint32_t b_bytes = b_rows * 128u;
+  const uint32_t b_bytes = b_rows * row_bytes;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t staging = sbase + stages * stage_bytes;
   const uint32_t bar0 = staging + kStagingBytes;                // full[stages], empty[stages], tfull[2], tempty[2]
@@ -184,15 +187,15 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
               // both CTAs of the pair complete the LEADER's full barrier; only the leader arms it
               const uint32_t fb = mapa_u32(full_bar(s), 0);
               if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * stage_bytes);
-              tma_load_5d_pair(a_dst, im, fb, kc * kBlockK, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
+              tma_load_5d_pair(a_dst, im, fb, kc * P.kb, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
                                c.q[1] + tp.off_d, c.q[0]);
-              tma_load_3d_pair(a_dst + a_bytes, &P.w_map, fb, kc * kBlockK, c.nt * P.block_n + rank * (int)b_rows,
+              tma_load_3d_pair(a_dst + a_bytes, &P.w_map, fb, kc * P.kb, c.nt * P.block_n + rank * (int)b_rows,
                                tp.wtap);
             } else {
               mbar_arrive_expect_tx(full_bar(s), stage_bytes);
-              tma_load_5d(a_dst, im, full_bar(s), kc * kBlockK, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
+              tma_load_5d(a_dst, im, full_bar(s), kc * P.kb, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
                           c.q[1] + tp.off_d, c.q[0]);
-              tma_load_3d(a_dst + a_bytes, &P.w_map, full_bar(s), kc * kBlockK, c.nt * P.block_n, tp.wtap);
+              tma_load_3d(a_dst + a_bytes, &P.w_map, full_bar(s), kc * P.kb, c.nt * P.block_n, tp.wtap);
             }
           }
         }
@@ -201,7 +204,9 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
   } else if (warp == 1) {
     // ===== MMA issuer (single thread; in a pair only the leader CTA issues) =====
     if (lane == 0 && rank == 0) {
-      constexpr uint64_t hi = smem_desc_hi(16, 1024, 2);         // K-major, SWIZZLE_128B
+      // K-major: SWIZZLE_128B (8-row atoms of 1024 B) or, for 32-channel stages, SWIZZLE_64B (512 B)
+      const uint64_t hi = P.kb == 32 ? smem_desc_hi(16, 512, 4) : smem_desc_hi(16, 1024, 2);
+      const int nk = P.kb / 16;
       uint32_t it = 0, tcount = 0;
       bool ok = true;
       for (int tile = first_tile; tile < P.num_tiles && ok; tile += tile_step, tcount++) {
@@ -222,13 +227,15 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
             // narrow Cout: the filter tile is the M = 128 operand, all 128*mt voxel rows are N
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; k++)
-              umma_f16(d_tmem, smem_desc(b_addr + k * 32, hi), smem_desc(a_addr + k * 32, hi), P.idesc,
-                       (i | k) != 0 ? 1u : 0u);
+              if (k < nk)
+                umma_f16(d_tmem, smem_desc(b_addr + k * 32, hi), smem_desc(a_addr + k * 32, hi), P.idesc,
+                         (i | k) != 0 ? 1u : 0u);
           } else
           for (int m = 0; m < P.mt; m++) {
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; k++) {
-              const uint64_t ad = smem_desc(a_addr + m * kABytes + k * 32, hi), bd = smem_desc(b_addr + k * 32, hi);
+              if (k >= nk) break;
+              const uint64_t ad = smem_desc(a_addr + m * a_sub + k * 32, hi), bd = smem_desc(b_addr + k * 32, hi);
               if (NCTA == 2) umma_f16_pair(d_tmem + m * P.block_n, ad, bd, P.idesc, (i | k) != 0 ? 1u : 0u);
               else umma_f16(d_tmem + m * P.block_n, ad, bd, P.idesc, (i | k) != 0 ? 1u : 0u);
             }
@@ -422,6 +429,8 @@ struct alignas(64) TcWgradParams {
   int32_t ktiles, ktiles_per_split, splits;
   int32_t a_ch, b_ch, a_tiles, b_tiles, block_n;   // M side (128-row tiles) / N side (block_n columns)
   int32_t m_big;                     // 1: M side = big tensor (tap-shifted), N side = small tensor
+  int32_t tpack;                     // > 1: narrow big tensor (<= 64 ch): N = tpack taps x one 64-column slab each
+  int32_t ngroups;                   // tap groups = ceil(ntaps / tpack)
   int32_t stages;
   uint32_t idesc, tmem_cols;
   float* ws;
@@ -446,9 +455,9 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
   int id = blockIdx.x;
   const int bt = id % P.b_tiles; id /= P.b_tiles;
   const int at = id % P.a_tiles; id /= P.a_tiles;
-  const int ti = id % P.ntaps;
-  const int sp = id / P.ntaps;
-  const TapDesc tp = P.taps[ti];
+  const int ti = id % P.ngroups;             // tap (tpack == 1) or tap group
+  const int sp = id / P.ngroups;
+  const TapDesc tp = P.taps[ti * P.tpack];
   const int kt0 = sp * P.ktiles_per_split;
   const int kt1 = kt0 + P.ktiles_per_split < P.ktiles ? kt0 + P.ktiles_per_split : P.ktiles;
   const int iters = kt1 - kt0;
@@ -487,6 +496,16 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
         const int nw = tp.off_w - mw, nh = tp.off_h - mh, nd = tp.off_d - md;
         for (int j = 0; j < 2; j++)
           tma_load_5d(a_dst + j * kSlabBytes, mm, full_bar(s), at * 128 + j * 64, q0w + mw, q0h + mh, q0d + md, q0n);
+        if (P.tpack > 1) {
+          // slab j = tap (group * tpack + j) of the <= 64-channel big tensor (a short last group
+          // re-reads its last tap; the epilogue drops those columns)
+          for (int j = 0; j < b_slabs; j++) {
+            const int tj = ti * P.tpack + j < P.ntaps ? ti * P.tpack + j : P.ntaps - 1;
+            const TapDesc tq = P.taps[tj];
+            tma_load_5d(a_dst + a_bytes + j * kSlabBytes, &P.b_maps[tq.map], full_bar(s), 0, q0w + tq.off_w,
+                        q0h + tq.off_h, q0d + tq.off_d, q0n);
+          }
+        } else
         for (int j = 0; j < b_slabs; j++)
           tma_load_5d(a_dst + a_bytes + j * kSlabBytes, nm, full_bar(s), bt * P.block_n + j * 64, q0w + nw, q0h + nh,
                       q0d + nd, q0n);
@@ -526,6 +545,17 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
       else {
 #pragma unroll
         for (int j = 0; j < 16; j++) v[j] = 0u;
+      }
+      if (P.tpack > 1) {
+        const int tap = ti * P.tpack + (c0 >> 6), col = c0 & 63;
+        if (valid && tap < P.ntaps) {
+          float* prow = P.ws + (((int64_t)sp * P.ntaps + tap) * P.a_ch + a) * P.b_ch;
+#pragma unroll
+          for (int j = 0; j < 16; j += 4)
+            if (col + j < P.b_ch)
+              *reinterpret_cast<uint4*>(prow + col + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+        continue;
       }
       const int col = bt * P.block_n + c0;
       if (valid) {
@@ -593,7 +623,8 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// bf16 view `m` of `base`, box = {64 channels, box[1..rank-1]}, 128-B swizzle, zero OOB fill.
+// bf16 view `m` of `base`, box = {64 (or 32) channels, box[1..rank-1]}, swizzle span = the box row
+// (128 B, or 64 B for 32-channel boxes), zero OOB fill.
 static int encode_map(CUtensorMap* out, const void* base, const MapDesc& m, int rank, const int* box) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return B2C_ERR_NO_DEVICE;
@@ -607,8 +638,8 @@ static int encode_map(CUtensorMap* out, const void* base, const MapDesc& m, int 
   }
   void* addr = const_cast<void*>(static_cast<const void*>(static_cast<const __nv_bfloat16*>(base) + m.base));
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, addr, dims, strides, bx, es,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, box[0] == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? B2C_OK : B2C_ERR_CUDA;
 }
 
@@ -619,7 +650,7 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
                    int act, float slope, cudaStream_t st) {
   TcConvParams P;
   memset(&P, 0, sizeof(P));
-  const int abox[5] = {kBlockK, p.box[3], p.box[2], p.box[1], p.box[0]};
+  const int abox[5] = {p.kb, p.box[3], p.box[2], p.box[1], p.box[0]};
   for (int i = 0; i < p.nmaps; i++) {
     int rc = encode_map(&P.in_maps[i], in, p.maps[i], 5, abox);
     if (rc) return rc;
@@ -653,7 +684,7 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   wm.dims[0] = p.kin; wm.dims[1] = p.nout; wm.dims[2] = T;
   wm.strides[0] = 1; wm.strides[1] = p.kin; wm.strides[2] = (int64_t)p.kin * p.nout;
   const int w_rows = p.swap ? 128 : p.block_n;
-  const int wbox[3] = {kBlockK, w_rows / ncta, 1};
+  const int wbox[3] = {p.kb, w_rows / ncta, 1};
   int rc = encode_map(&P.w_map, w, wm, 3, wbox);
   if (rc) return rc;
   memcpy(P.subs, p.subs, sizeof(P.subs));
@@ -662,11 +693,12 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   for (int i = 0; i < 4; i++) P.box[i] = p.box[i];
   P.mt = p.mt; P.split_dim = p.split_dim; P.sub_ext = p.sub_ext;
   P.nout = p.nout; P.block_n = p.block_n; P.tiles_n = p.tiles_n; P.kchunks = p.kchunks;
-  const uint32_t stage_bytes = (uint32_t)p.mt * kABytes + (uint32_t)(w_rows / ncta) * 128u;
-  P.swap = p.swap; P.w_rows = w_rows;
+  const uint32_t stage_bytes = ((uint32_t)p.mt * kBlockM + (uint32_t)(w_rows / ncta)) * (uint32_t)p.kb * 2u;
+  P.swap = p.swap; P.w_rows = w_rows; P.kb = p.kb;
   const int fixed = 1024 /*alignment slack*/ + (int)kStagingBytes + 256 /*barriers + tmem slot*/;
   int stages = (kSmemBudget - fixed) / (int)stage_bytes;
   if (stages > 8) stages = 8;
+  if (const char* e = getenv("B2C_STAGES")) { const int v = atoi(e); if (v >= 2 && v < stages) stages = v; }   // experiments
   if (stages < 2) return B2C_ERR_UNSUPPORTED;
   P.stages = stages;
   P.idesc = p.swap ? idesc_bf16(128, 128 * p.mt, 0, 0) : idesc_bf16(kBlockM * ncta, p.block_n, 0, 0);
@@ -705,7 +737,7 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
 }
 
 // ---- wgrad ---------------------------------------------------------------------
-struct WgradCfg { ConvPlan plan; int box[4], tiles[4]; int ktiles, splits, kps, a_tiles, b_tiles, block_n, m_big, m_ch, n_ch; };
+struct WgradCfg { ConvPlan plan; int box[4], tiles[4]; int ktiles, splits, kps, a_tiles, b_tiles, block_n, m_big, m_ch, n_ch, tpack, ngroups; };
 
 static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   if (g.sc % 8 != 0 || g.bc % 8 != 0 || g.sc < 16 || g.bc < 16) return B2C_ERR_UNSUPPORTED;
@@ -729,11 +761,22 @@ static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   c->m_big = ru64(g.sc) > ru64(g.bc) ? 1 : 0;
   c->m_ch = c->m_big ? g.bc : g.sc;
   c->n_ch = c->m_big ? g.sc : g.bc;
-  const int bn = ru64(c->n_ch);
+  int bn = ru64(c->n_ch);
+  c->tpack = 1;
+  c->ngroups = c->plan.ntaps_total;
+  if (g.bc <= 64 && c->plan.ntaps_total >= 2) {
+    // narrow big tensor (utils.py hidden 32 / 64-channel 3^3 layers): one tap would fill a single
+    // 64-column slab, so up to four taps share a CTA - the small tensor's tile is read once for
+    // all of them and N = 256 keeps the tensor pipe on its efficient shape
+    c->m_big = 0; c->m_ch = g.sc; c->n_ch = g.bc;
+    c->tpack = c->plan.ntaps_total >= 4 ? 4 : c->plan.ntaps_total;
+    c->ngroups = (c->plan.ntaps_total + c->tpack - 1) / c->tpack;
+    bn = 64 * c->tpack;
+  }
   c->block_n = bn;
   c->a_tiles = (c->m_ch + 127) / 128;
-  c->b_tiles = (c->n_ch + bn - 1) / bn;
-  const int64_t units = (int64_t)c->plan.ntaps_total * c->a_tiles * c->b_tiles;
+  c->b_tiles = c->tpack > 1 ? 1 : (c->n_ch + bn - 1) / bn;
+  const int64_t units = (int64_t)c->ngroups * c->a_tiles * c->b_tiles;
   if (units <= 0) return B2C_ERR_UNSUPPORTED;
   // split-K count: 2.5 .. 10 waves of the SMs, at least 64 K-iterations per CTA (16 when the
   // problem has too few tiles to fill the machine otherwise: 1x1x1 filters, 32-channel layers);
@@ -799,7 +842,7 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
   for (int i = 0; i < 4; i++) { P.box[i] = c.box[i]; P.tiles[i] = c.tiles[i]; }
   P.ktiles = c.ktiles; P.ktiles_per_split = c.kps; P.splits = c.splits;
   P.a_ch = c.m_ch; P.b_ch = c.n_ch; P.a_tiles = c.a_tiles; P.b_tiles = c.b_tiles; P.block_n = c.block_n;
-  P.m_big = c.m_big;
+  P.m_big = c.m_big; P.tpack = c.tpack; P.ngroups = c.ngroups;
   const uint32_t stage_bytes = 2 * kSlabBytes + (c.block_n / 64) * kSlabBytes;
   int stages = (kSmemBudget - 1024 - 256) / (int)stage_bytes;
   if (stages > 8) stages = 8;
@@ -810,7 +853,7 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
   if (cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
     return B2C_ERR_CUDA;
   const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
-  const int64_t grid = (int64_t)P.ntaps * c.a_tiles * c.b_tiles * c.splits;
+  const int64_t grid = (int64_t)c.ngroups * c.a_tiles * c.b_tiles * c.splits;
   tc_wgrad_kernel<<<(unsigned)grid, kThreadsTc, smem, st>>>(P);
   rc = launched();
   if (rc) return rc;

@@ -1,6 +1,8 @@
 // tc_plan.cpp — see tc_plan.h.
 #include "tc_plan.h"
 
+#include <cstdlib>
+
 #include <string.h>
 
 namespace b2c {
@@ -21,7 +23,8 @@ static void choose_box(const int ext[4], int box[4], int rows) {
 static int finish(ConvPlan* p, int kin, int nout) {
   if (kin % 8 != 0 || nout % 8 != 0 || kin < 16) return B2C_ERR_UNSUPPORTED;  // 16-B TMA strides / vector stores
   p->kin = kin; p->nout = nout;
-  p->kchunks = (kin + kBlockK - 1) / kBlockK;
+  p->kb = kin <= 32 ? 32 : kBlockK;       // 32-channel layers (utils.py hidden convs): no zero-padded half rows
+  p->kchunks = (kin + p->kb - 1) / p->kb;
   int bn = ((nout + 15) / 16) * 16;
   if (bn > 256) bn = 256;
   // A UMMA with M = 128 costs about the same for N = 32 .. 128 as for N = 256, so narrow
@@ -31,7 +34,9 @@ static int finish(ConvPlan* p, int kin, int nout) {
   // keep the direct epilogue.)
   int min_taps = p->nsubs > 0 ? p->subs[0].ntaps : 0;
   for (int s = 1; s < p->nsubs; s++) if (p->subs[s].ntaps < min_taps) min_taps = p->subs[s].ntaps;
-  p->swap = (bn <= 128 && (int64_t)min_taps * p->kchunks >= 8) ? 1 : 0;
+  int swap_min = 0;
+  if (const char* e = getenv("B2C_SWAP_MIN")) swap_min = atoi(e);
+  p->swap = (bn <= 128 && nout >= swap_min && (int64_t)min_taps * p->kchunks >= 8) ? 1 : 0;
   if (p->swap) bn = 128;
   p->block_n = bn;
   p->tiles_n = (nout + bn - 1) / bn;

@@ -47,7 +47,8 @@ struct ConvPlan {
   int32_t split_dim, sub_ext;    // sub-tile m covers box[split_dim] range [m*sub_ext, (m+1)*sub_ext)
   int32_t kin, nout;             // contracted / produced channels
   int32_t block_n, tiles_n;      // N tile and count
-  int32_t kchunks;               // ceil(kin / kBlockK)
+  int32_t kchunks;               // ceil(kin / kb)
+  int32_t kb;                    // channels per pipeline stage: kBlockK, or 32 when kin <= 32 (64-byte rows)
   int32_t m_tiles;               // total M tiles over all sub-problems
   MapDesc maps[kMaxMaps];
   SubDesc subs[kMaxSubs];
