@@ -99,3 +99,40 @@ class GanStep:
             out.append(self.D_step(real))
         errG, fake = self.G_step(batch)
         return out, errG, fake
+
+
+class DevicePrefetcher:
+    """Host -> device input pipeline for the step (trainer.py:84,300 `data.to(device)`): yields
+    device tensors while the NEXT pinned host batch is already being copied on a side stream,
+    so the copy overlaps the running D_step instead of stalling it."""
+
+    def __init__(self, batches, device):
+        self.it = iter(batches)
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+        self._next = None
+        self._preload()
+
+    def _preload(self):
+        try:
+            host = next(self.it)
+        except StopIteration:
+            self._next = None
+            return
+        with torch.cuda.stream(self.stream):
+            self._next = host.to(self.device, non_blocking=True)
+            self._ready = torch.cuda.Event()
+            self._ready.record(self.stream)
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self._next is None:
+            raise StopIteration
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self._ready)
+        out = self._next
+        out.record_stream(cur)
+        self._preload()
+        return out

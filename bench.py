@@ -201,14 +201,27 @@ def run_ours(a):
     def step_resident(i):
         step.step(resident[(i * a.iterD + j) % npool] for j in range(a.iterD))
 
+    def host_batches():
+        i = 0
+        while True:
+            yield host[i % npool]
+            i += 1
+
+    feed = [None]
+
     def step_e2e(i):
-        # what trainer.train() does per iteration: data.to(device), D_step/G_step, .item() of each loss
+        # the public API end to end: pinned host batches -> DevicePrefetcher (H2D copy of every
+        # batch inside the timed region, overlapped with the running step) -> GanStep.D_step /
+        # G_step -> the step's losses read back to the host (trainer.py:251,281 `.item()`)
+        if feed[0] is None:
+            feed[0] = B.train.DevicePrefetcher(host_batches(), dev)
+        losses = []
         for j in range(a.iterD):
-            real = host[(i * a.iterD + j) % npool].to(dev, non_blocking=True)
-            er, ef = step.D_step(real)
-            er.item(), ef.item()
+            er, ef = step.D_step(next(feed[0]))
+            losses += [er, ef]
         eg, _ = step.G_step(b)
-        eg.item()
+        losses.append(eg)
+        return torch.stack([l.float() for l in losses]).cpu().tolist()
 
     def barrier():
         if world > 1:

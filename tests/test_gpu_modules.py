@@ -171,3 +171,12 @@ def test_cpu_tensor_fails_loudly():
     conv = B.nn.Conv3d(4, 4, 3)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         conv(torch.randn(1, 4, 5, 5, 5))
+
+
+def test_device_prefetcher_order_and_values():
+    """train.DevicePrefetcher: every pinned host batch arrives once, in order, bit-exact."""
+    host = [torch.full((4, 1, 8, 8, 8), float(i)).pin_memory() for i in range(5)]
+    got = [t.clone() for t in B.train.DevicePrefetcher(iter(host), "cuda:0")]
+    assert len(got) == 5
+    for i, t in enumerate(got):
+        assert t.is_cuda and torch.equal(t.cpu(), host[i])
