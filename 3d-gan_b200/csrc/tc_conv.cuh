@@ -12,6 +12,11 @@ bool tc_wgrad_supported(const Geo& g);
 size_t tc_wgrad_workspace(const Geo& g);
 int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw, void* ws, size_t wsb,
                     cudaStream_t st);
+// Fused gather-form kernel for one-channel big tensors with <= 64 taps and <= 128 output channels
+// (no im2col matrix in HBM); wp = [sc][Kp] bf16 as packed by thin_pack(gather).
+bool tc_thin_gather_supported(const Geo& g);
+int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp, void* out_small, const float* bias,
+                          int act, float slope, cudaStream_t st);
 // Sticky device error word of the tensor-core kernels (synchronises the device).
 unsigned tc_error_fetch_clear();
 }  // namespace b2c

@@ -1,0 +1,259 @@
+// tc_thin.cuh — part of the tc_conv.cu translation unit (shares its PTX helpers, tensor-map encoder
+// and sticky error word).  Fused gather-form kernel for convolutions whose big-side tensor has ONE
+// channel and at most 64 taps (dcgan.py:161 Conv3d(1 -> ndf, k4, s2, p1); biggan.py:78 input conv):
+//
+//   out[v, c] = act(bias[c] + sum_t A[v, t] * W[c, t]),   A[v, t] = big[n, o*s + k*dl - p]  (0 outside)
+//
+// The im2col matrix A never exists in HBM: four producer warps gather one 128-voxel x 64-tap tile
+// straight into 128-byte-swizzled shared memory (the K-major operand layout tcgen05 reads), one warp
+// issues tcgen05.mma into two TMEM accumulator sets, four epilogue warps do bias / activation /
+// bf16 and hand 128 x 64 slabs to TMA stores.  HBM traffic = |big| + |out| (the roofline of this
+// layer class); the input tensor (134 MB at BASELINE config 2) stays L2 resident.
+//
+// Roles (288 threads): warps 0-3 producers, warp 4 MMA issuer, warps 5-8 epilogue.
+
+constexpr int kThinThreads = 288;
+constexpr int kThinStages = 3;            // 6 x 16 KB tiles per CTA: two CTAs fit one SM
+constexpr uint32_t kThinTile = kBlockM * 128;          // 16 KB: 128 rows x 128 B (64 taps)
+
+struct ThinTap { int8_t d, h, w, _pad; int32_t off; };      // tap offsets {kd*dl, kh*dl, kw*dl} and their element offset
+
+struct alignas(64) ThinGatherParams {
+  CUtensorMap out_map;                // [rows][sc] bf16, box {64 ch, 128 rows}
+  Geo g;
+  const __nv_bfloat16* big;
+  const __nv_bfloat16* wp;            // [sc][Kp]
+  const float* bias;
+  int64_t rows;
+  int32_t Kp, T, sc, block_n, num_tiles, fast_k4s2, act, dbg;
+  float slope;
+  uint32_t idesc, tmem_cols;
+  ThinTap tap[64];
+};
+
+// element t (0..63) of row r lives at r*128 + ((t/8) ^ (r & 7))*16 + (t % 8)*2  (SWIZZLE_128B)
+__device__ __forceinline__ uint32_t thin_chunk(uint32_t tile, int r, int c) {
+  return tile + (uint32_t)r * 128u + ((uint32_t)(c ^ (r & 7)) << 4);
+}
+
+// One im2col row through the tap table, branch free: every load is unconditional (an out-of-range tap
+// reads element 0 and is masked afterwards), so the compiler issues all of them before the first use.
+template <int TMAX>
+__device__ __forceinline__ void thin_gather_row(const ThinGatherParams& P, const uint16_t* __restrict__ xb, int base,
+                                                int id0, int ih0, int iw0, uint32_t* pk) {
+  const Geo& g = P.g;
+  uint32_t e[TMAX];
+#pragma unroll
+  for (int t = 0; t < TMAX; t++) {
+    const ThinTap tp = P.tap[t];
+    const int id = id0 + tp.d, ih = ih0 + tp.h, iw = iw0 + tp.w;
+    const bool ok = t < P.T && id >= 0 && id < g.bd && ih >= 0 && ih < g.bh && iw >= 0 && iw < g.bw;
+    const uint32_t val = (uint32_t)__ldg(xb + (ok ? base + tp.off : 0));
+    e[t] = ok ? val : 0u;
+  }
+#pragma unroll
+  for (int i = 0; i < 32; i++) pk[i] = 2 * i + 1 < TMAX ? (e[2 * i] | (e[2 * i + 1] << 16)) : 0u;
+}
+
+__global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __grid_constant__ ThinGatherParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t sbase = (raw + 1023u) & ~1023u;
+  uint8_t* sgen = smem_raw + (sbase - raw);
+  const uint32_t w_tile = sbase;                                   // 128 x 64 filter tile (zero padded)
+  const uint32_t a_ring = sbase + kThinTile;                       // kThinStages A tiles
+  const uint32_t staging = a_ring + kThinStages * kThinTile;       // two output slabs
+  const uint32_t bar0 = staging + 2 * kThinTile;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sgen + (bar0 - sbase) + (2 * kThinStages + 4) * 8);
+  auto afull = [&](int s) { return bar0 + 8u * s; };
+  auto aempty = [&](int s) { return bar0 + 8u * (kThinStages + s); };
+  auto tfull = [&](int a) { return bar0 + 8u * (2 * kThinStages + a); };
+  auto tempty = [&](int a) { return bar0 + 8u * (2 * kThinStages + 2 + a); };
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const Geo& g = P.g;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kThinStages; s++) { mbar_init(afull(s), 4); mbar_init(aempty(s), 1); }
+    for (int a = 0; a < 2; a++) { mbar_init(tfull(a), 1); mbar_init(tempty(a), 4); }
+    fence_barrier_init();
+    prefetch_tmap(&P.out_map);
+  }
+  if (warp == 4) { tmem_alloc(smem_u32(tmem_slot), P.tmem_cols); tmem_relinquish(); }
+  if (warp < 4) {
+    // filter tile: row = channel (zero rows beyond sc), 8 chunks of 8 taps (zero beyond Kp)
+    const int r = threadIdx.x;
+    for (int c = 0; c < 8; c++) {
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (r < P.sc && c * 8 < P.Kp) v = __ldg(reinterpret_cast<const uint4*>(P.wp + (int64_t)r * P.Kp + c * 8));
+      st_shared_v4(thin_chunk(w_tile, r, c), v.x, v.y, v.z, v.w);
+    }
+    fence_proxy_async();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  if (warp < 4) {
+    // ===== producers: thread r builds row r of every A tile =====
+    const int r = threadIdx.x;
+    const uint16_t* xb = reinterpret_cast<const uint16_t*>(P.big);
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+      const uint32_t s = it % kThinStages, ph = (it / kThinStages) & 1u;
+      mbar_wait(aempty(s), ph ^ 1u);
+      const uint32_t dst = a_ring + s * kThinTile;
+      const int64_t v = (int64_t)tile * kBlockM + r;
+      if (P.dbg & 32) {
+      } else if (P.fast_k4s2 == 2) {
+        // k = 4, stride 2, pad 1, sw % 32 == 0: the 32 lanes of a warp are 32 consecutive ow of ONE (n, od, oh)
+        // line (rows % 32 == 0, so a warp is all valid or all tail).  Taps (kd, kh, 0..3) = input elements
+        // 2*ow-1 .. 2*ow+2: each lane loads only its aligned middle pair (2*ow, 2*ow+1) per line - 16
+        // independent loads issued back to back - and takes the outer two elements from its neighbours'
+        // pairs through warp shuffles.  All index arithmetic is 32-bit and warp-uniform where possible.
+        const uint32_t v0 = (uint32_t)tile * kBlockM + (uint32_t)(warp * 32);        // < 2^31 (host check)
+        if (v0 >= (uint32_t)P.rows) {
+#pragma unroll
+          for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);
+        } else {
+          uint32_t t = v0 / (uint32_t)g.sw;
+          const int ow = (int)(v0 - t * (uint32_t)g.sw) + lane;
+          const uint32_t t2 = t / (uint32_t)g.sh;
+          const int oh = (int)(t - t2 * (uint32_t)g.sh);
+          const uint32_t n = t2 / (uint32_t)g.sd;
+          const int od = (int)(t2 - n * (uint32_t)g.sd);
+          const int id0 = 2 * od - 1, ih0 = 2 * oh - 1;
+          const int sH = g.bw, sD = g.bh * g.bw;
+          // element offset of (n, id0, ih0, 2*ow); lines with id / ih out of range are never dereferenced
+          const int base = ((int)n * g.bd + id0) * sD + ih0 * sH + 2 * ow;
+          // all loads of the tile row are issued before anything consumes them: the middle pairs, and on
+          // the two edge lanes the one element their missing neighbour would have supplied
+          uint32_t mid[16], edge[16];
+          const bool left = lane == 0 && ow > 0, right = lane == 31 && 2 * ow + 2 < g.bw;
+#pragma unroll
+          for (int l = 0; l < 16; l++) {
+            const int id = id0 + (l >> 2), ih = ih0 + (l & 3);
+            const bool ok = id >= 0 && id < g.bd && ih >= 0 && ih < g.bh && !(P.dbg & 2);   // warp-uniform
+            const uint16_t* px = xb + base + (l >> 2) * sD + (l & 3) * sH;
+            mid[l] = ok ? __ldg(reinterpret_cast<const uint32_t*>(px)) : 0u;
+            edge[l] = 0u;
+            if (ok && left) edge[l] = (uint32_t)__ldg(px - 1);
+            if (ok && right) edge[l] = (uint32_t)__ldg(px + 2);
+          }
+          uint32_t w4[4];
+#pragma unroll
+          for (int l = 0; l < 16; l++) {
+            uint32_t e0 = __shfl_up_sync(0xffffffffu, mid[l], 1) >> 16;                 // x[2*ow - 1]
+            uint32_t e3 = __shfl_down_sync(0xffffffffu, mid[l], 1) & 0xffffu;           // x[2*ow + 2]
+            if (lane == 0) e0 = edge[l];
+            if (lane == 31) e3 = edge[l];
+            w4[(l & 1) * 2] = e0 | (mid[l] << 16);
+            w4[(l & 1) * 2 + 1] = (mid[l] >> 16) | (e3 << 16);
+            if (l & 1) st_shared_v4(thin_chunk(dst, r, l >> 1), w4[0], w4[1], w4[2], w4[3]);
+          }
+        }
+      } else
+      if (v >= P.rows) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);
+      } else {
+        // any geometry with <= 64 taps (host-built tap table, 32-bit indices): all predicated loads of the
+        // row are issued before the first store consumes one
+        uint32_t q = (uint32_t)v;
+        uint32_t t1 = q / (uint32_t)g.sw;
+        const int ow = (int)(q - t1 * (uint32_t)g.sw);
+        uint32_t t2 = t1 / (uint32_t)g.sh;
+        const int oh = (int)(t1 - t2 * (uint32_t)g.sh);
+        const uint32_t n = t2 / (uint32_t)g.sd;
+        const int od = (int)(t2 - n * (uint32_t)g.sd);
+        const int id0 = od * g.s[0] - g.p[0], ih0 = oh * g.s[1] - g.p[1], iw0 = ow * g.s[2] - g.p[2];
+        const int base = (((int)n * g.bd + id0) * g.bh + ih0) * g.bw + iw0;
+        uint32_t pk[32];
+        if (P.T <= 32) thin_gather_row<32>(P, xb, base, id0, ih0, iw0, pk);
+        else thin_gather_row<64>(P, xb, base, id0, ih0, iw0, pk);
+#pragma unroll
+        for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      }
+      if (!(P.dbg & 16)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+      __syncwarp();
+      if (lane == 0) mbar_arrive(afull(s));
+    }
+  } else if (warp == 4) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint64_t hi = smem_desc_hi(16, 1024, 2);
+      uint32_t it = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < P.num_tiles && ok; tile += gridDim.x, it++) {
+        const uint32_t s = it % kThinStages, ph = (it / kThinStages) & 1u;
+        const uint32_t acc = it & 1u, aph = (it >> 1) & 1u;
+        ok = mbar_wait(tempty(acc), aph ^ 1u);
+        ok = ok && mbar_wait(afull(s), ph);
+        tc_fence_after();
+        const uint32_t a_addr = a_ring + s * kThinTile;
+        const uint32_t d_tmem = tmem_base + acc * (uint32_t)P.block_n;
+        const int nk = (P.Kp + 15) / 16;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+          if (k < nk && !(P.dbg & 8)) umma_f16(d_tmem, smem_desc(a_addr + k * 32, hi), smem_desc(w_tile + k * 32, hi), P.idesc, k ? 1u : 0u);
+        umma_commit(aempty(s));
+        umma_commit(tfull(acc));
+      }
+    }
+  } else {
+    // ===== epilogue =====
+    const int grp = warp & 3;
+    const int row = grp * 32 + lane;
+    const int et = threadIdx.x - 160;                    // 0..127
+    const uint32_t lane_off = (uint32_t)(grp * 32) << 16;
+    const int nslab = (P.block_n + 63) >> 6;
+    uint32_t it = 0, slab_count = 0;
+    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+      const uint32_t acc = it & 1u, aph = (it >> 1) & 1u;
+      mbar_wait(tfull(acc), aph);
+      tc_fence_after();
+      for (int j = 0; j < nslab; j++, slab_count++) {
+        const uint32_t sbuf = staging + (slab_count & 1u) * kThinTile;
+        if (et == 0) tma_store_wait_read<1>();
+        named_bar_sync(2, 128);
+        uint32_t v[64];
+        const int ncol = P.block_n - j * 64 < 64 ? P.block_n - j * 64 : 64;
+        if (P.dbg & 4) continue;
+        const uint32_t tcol = tmem_base + lane_off + acc * (uint32_t)P.block_n + j * 64;
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if (q * 16 < ncol) tmem_ld16(tcol + q * 16, v + q * 16);
+        tmem_ld_wait();
+        if (P.bias) {
+          const float* bp = P.bias + j * 64;
+          const int nb = P.sc - j * 64;
+#pragma unroll
+          for (int i = 0; i < 64; i++)
+            if (i < nb && i < ncol) v[i] = __float_as_uint(__uint_as_float(v[i]) + __ldg(bp + i));
+        }
+        apply_act64(v, P.act, P.slope);
+#pragma unroll
+        for (int ch = 0; ch < 8; ch++)
+          if (ch * 8 < ncol)
+            st_shared_v4(sbuf + row * 128 + ((ch ^ (row & 7)) << 4),
+                         pack_bf16x2(__uint_as_float(v[ch * 8 + 0]), __uint_as_float(v[ch * 8 + 1])),
+                         pack_bf16x2(__uint_as_float(v[ch * 8 + 2]), __uint_as_float(v[ch * 8 + 3])),
+                         pack_bf16x2(__uint_as_float(v[ch * 8 + 4]), __uint_as_float(v[ch * 8 + 5])),
+                         pack_bf16x2(__uint_as_float(v[ch * 8 + 6]), __uint_as_float(v[ch * 8 + 7])));
+        fence_proxy_async();
+        named_bar_sync(2, 128);
+        if (et == 0 && !(P.dbg & 1)) {
+          tma_store_2d(&P.out_map, sbuf, j * 64, tile * kBlockM);
+          tma_store_commit();
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty(acc));
+    }
+    if (et == 0) tma_store_wait<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem_base, P.tmem_cols);
+}

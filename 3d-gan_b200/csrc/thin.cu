@@ -1,6 +1,8 @@
 // thin.cu — see thin.cuh.
 #include "thin.cuh"
 
+#include <cstdlib>
+
 #include "tc_conv.cuh"
 
 namespace b2c {
@@ -292,6 +294,10 @@ static int im2col_launch(const Geo& g, const void* big, void* col, cudaStream_t 
 
 int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, const float* bias, int act,
                 float slope, void* ws, size_t wsb, cudaStream_t st) {
+  if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
+    const int rc = tc_thin_gather_launch(g, big, wp, thin_kp(g), out_small, bias, act, slope, st);
+    if (rc != B2C_ERR_UNSUPPORTED) return rc;
+  }
   if (!ws || wsb < thin_workspace(g, 0)) return B2C_ERR_WORKSPACE;
   int rc = im2col_launch(g, big, ws, st);
   if (rc) return rc;
