@@ -872,45 +872,56 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
 bool tc_thin_gather_supported(const Geo& g) {
   if (g.bc != 1 || g.sc % 8 != 0 || g.sc < 16 || g.sc > 128 || g.taps() > 64) return false;
   const int64_t rows = (int64_t)g.n * g.sd * g.sh * g.sw;
+  if ((int64_t)g.n * g.bd * g.bh * g.bw >= 0x7fffffffLL) return false;                  // 32-bit element offsets
+  for (int i = 0; i < 3; i++)
+    if ((g.k[i] - 1) * g.dl[i] > 127) return false;
   return rows > 0 && rows < 0x7fffffffLL - kBlockM;
+}
+
+// how the producer warps cut im2col rows out of the one-channel tensor
+static int thin_src_fill(const Geo& g, const void* big, ThinSrc* S) {
+  if (!tc_thin_gather_supported(g)) return B2C_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(big) & 3) != 0) return B2C_ERR_UNSUPPORTED;
+  S->g = g;
+  S->big = static_cast<const __nv_bfloat16*>(big);
+  S->rows = (int64_t)g.n * g.sd * g.sh * g.sw;
+  S->T = g.taps();
+  bool k4s2 = g.bw % 2 == 0;
+  for (int i = 0; i < 3; i++) k4s2 = k4s2 && g.k[i] == 4 && g.s[i] == 2 && g.p[i] == 1 && g.dl[i] == 1;
+  k4s2 = k4s2 && g.bd == 2 * g.sd && g.bh == 2 * g.sh && g.bw == 2 * g.sw;
+  S->fast_k4s2 = (k4s2 && g.sw % 32 == 0) ? 2 : 0;
+  for (int kd = 0, t = 0; kd < g.k[0]; kd++)
+    for (int kh = 0; kh < g.k[1]; kh++)
+      for (int kw = 0; kw < g.k[2]; kw++, t++) {
+        const int dd = kd * g.dl[0], dh = kh * g.dl[1], dw = kw * g.dl[2];
+        S->tap[t].d = (int8_t)dd; S->tap[t].h = (int8_t)dh; S->tap[t].w = (int8_t)dw;
+        S->tap[t].off = (dd * g.bh + dh) * g.bw + dw;
+      }
+  return B2C_OK;
 }
 
 int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp, void* out_small, const float* bias,
                           int act, float slope, cudaStream_t st) {
   if (!tc_thin_gather_supported(g) || Kp > 64 || Kp % 8 != 0) return B2C_ERR_UNSUPPORTED;
-  if ((reinterpret_cast<uintptr_t>(big) & 3) != 0 || (reinterpret_cast<uintptr_t>(wp) & 15) != 0) return B2C_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(wp) & 15) != 0) return B2C_ERR_UNSUPPORTED;
   ThinGatherParams P;
   memset(&P, 0, sizeof(P));
-  const int64_t rows = (int64_t)g.n * g.sd * g.sh * g.sw;
+  int rc = thin_src_fill(g, big, &P.src);
+  if (rc) return rc;
+  const int64_t rows = P.src.rows;
   MapDesc om;
   memset(&om, 0, sizeof(om));
   om.base = 0;
   om.dims[0] = g.sc; om.dims[1] = (int32_t)rows;
   om.strides[0] = 1; om.strides[1] = g.sc;
   const int obox[2] = {64, kBlockM};
-  int rc = encode_map(&P.out_map, out_small, om, 2, obox);
+  rc = encode_map(&P.out_map, out_small, om, 2, obox);
   if (rc) return rc;
-  P.g = g;
-  P.big = static_cast<const __nv_bfloat16*>(big);
   P.wp = static_cast<const __nv_bfloat16*>(wp);
-  P.bias = bias; P.rows = rows; P.Kp = Kp; P.T = g.taps(); P.sc = g.sc;
+  P.bias = bias; P.Kp = Kp; P.sc = g.sc;
   P.block_n = (g.sc + 15) / 16 * 16;
   P.num_tiles = (int32_t)cdiv(rows, (int64_t)kBlockM);
-  bool k4s2 = g.bw % 2 == 0;
-  for (int i = 0; i < 3; i++) k4s2 = k4s2 && g.k[i] == 4 && g.s[i] == 2 && g.p[i] == 1 && g.dl[i] == 1;
-  k4s2 = k4s2 && g.bd == 2 * g.sd && g.bh == 2 * g.sh && g.bw == 2 * g.sw;
-  if ((int64_t)g.n * g.bd * g.bh * g.bw >= 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;     // 32-bit element offsets
-  P.fast_k4s2 = (k4s2 && g.sw % 32 == 0) ? 2 : 0;
-  for (int kd = 0, t = 0; kd < g.k[0]; kd++)
-    for (int kh = 0; kh < g.k[1]; kh++)
-      for (int kw = 0; kw < g.k[2]; kw++, t++) {
-        const int dd = kd * g.dl[0], dh = kh * g.dl[1], dw = kw * g.dl[2];
-        if (dd > 127 || dh > 127 || dw > 127) return B2C_ERR_UNSUPPORTED;
-        P.tap[t].d = (int8_t)dd; P.tap[t].h = (int8_t)dh; P.tap[t].w = (int8_t)dw;
-        P.tap[t].off = (dd * g.bh + dh) * g.bw + dw;
-      }
   P.act = act; P.slope = slope;
-  if (const char* e = getenv("B2C_THIN_DBG")) P.dbg = atoi(e);      // experiments only
   P.idesc = idesc_bf16(kBlockM, P.block_n, 0, 0);
   P.tmem_cols = tmem_cols_for(2 * P.block_n);
   const size_t smem = 1024 + (size_t)(1 + kThinStages + 2) * kThinTile + 256;
@@ -919,6 +930,58 @@ int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp,
   const int sms = num_sms();
   const int grid = P.num_tiles < 2 * sms ? P.num_tiles : 2 * sms;        // two resident CTAs per SM
   thin_gather_kernel<<<grid, kThinThreads, smem, st>>>(P);
+  return launched();
+}
+
+// split-K over 128-voxel tiles: one CTA (= one fp32 partial) per contiguous tile range, two CTAs per SM
+static void thin_wgrad_split(const Geo& g, int* tiles, int* per_cta, int* splits) {
+  const int64_t rows = (int64_t)g.n * g.sd * g.sh * g.sw;
+  *tiles = (int)cdiv(rows, (int64_t)kBlockM);
+  const int want = 2 * num_sms();
+  *per_cta = (int)cdiv((int64_t)*tiles, (int64_t)want);
+  if (*per_cta < 1) *per_cta = 1;
+  *splits = (int)cdiv((int64_t)*tiles, (int64_t)*per_cta);
+}
+
+size_t tc_thin_wgrad_workspace(const Geo& g) {
+  if (!tc_thin_gather_supported(g)) return 0;
+  int tiles, per, splits;
+  thin_wgrad_split(g, &tiles, &per, &splits);
+  return (size_t)splits * g.sc * 64 * sizeof(float);
+}
+
+int tc_thin_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw, int flip, void* ws, size_t wsb,
+                         cudaStream_t st) {
+  if (!tc_thin_gather_supported(g)) return B2C_ERR_UNSUPPORTED;
+  if (!ws || wsb < tc_thin_wgrad_workspace(g)) return B2C_ERR_WORKSPACE;
+  ThinWgradParams P;
+  memset(&P, 0, sizeof(P));
+  int rc = thin_src_fill(g, big, &P.src);
+  if (rc) return rc;
+  MapDesc dm;
+  memset(&dm, 0, sizeof(dm));
+  dm.base = 0;
+  dm.dims[0] = g.sc; dm.dims[1] = (int32_t)P.src.rows;
+  dm.strides[0] = 1; dm.strides[1] = g.sc;
+  const int dbox[2] = {64, kWgVox};
+  rc = encode_map(&P.dy_map, small, dm, 2, dbox);
+  if (rc) return rc;
+  int splits;
+  thin_wgrad_split(g, &P.num_tiles, &P.tiles_per_cta, &splits);
+  P.ws = static_cast<float*>(ws);
+  P.sc = g.sc;
+  P.ach = g.sc > 64 ? 2 : 1;
+  P.stages = P.ach == 2 ? 2 : 3;                 // <= 96 KB of tiles: two CTAs per SM
+  P.idesc = idesc_bf16(128, 64, 1, 1);
+  P.tmem_cols = tmem_cols_for(64);
+  const size_t smem = 1024 + (size_t)P.stages * (P.ach * 2 * kSlabBytes + kThinTile) + 256;
+  if (cudaFuncSetAttribute(thin_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    return B2C_ERR_CUDA;
+  thin_wgrad_kernel<<<splits, kThinWgThreads, smem, st>>>(P);
+  rc = launched();
+  if (rc) return rc;
+  const int T = g.taps();
+  thin_wgrad_reduce_kernel<<<(unsigned)cdiv((int64_t)g.sc * T, 256), 256, 0, st>>>(P.ws, dw, g.sc, T, splits, flip);
   return launched();
 }
 

@@ -17,6 +17,10 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
 bool tc_thin_gather_supported(const Geo& g);
 int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp, void* out_small, const float* bias,
                           int act, float slope, cudaStream_t st);
+// fused weight gradient of the same layer class: dw[sc][T] fp32 (taps reversed when flip != 0)
+size_t tc_thin_wgrad_workspace(const Geo& g);
+int tc_thin_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw, int flip, void* ws, size_t wsb,
+                         cudaStream_t st);
 // Sticky device error word of the tensor-core kernels (synchronises the device).
 unsigned tc_error_fetch_clear();
 }  // namespace b2c

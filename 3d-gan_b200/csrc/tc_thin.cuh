@@ -18,17 +18,24 @@ constexpr uint32_t kThinTile = kBlockM * 128;          // 16 KB: 128 rows x 128 
 
 struct ThinTap { int8_t d, h, w, _pad; int32_t off; };      // tap offsets {kd*dl, kh*dl, kw*dl} and their element offset
 
-struct alignas(64) ThinGatherParams {
-  CUtensorMap out_map;                // [rows][sc] bf16, box {64 ch, 128 rows}
+// the one-channel source tensor and how im2col rows are cut from it (shared by the forward and the
+// weight-gradient kernels)
+struct ThinSrc {
   Geo g;
   const __nv_bfloat16* big;
+  int64_t rows;
+  int32_t T, fast_k4s2;
+  ThinTap tap[64];
+};
+
+struct alignas(64) ThinGatherParams {
+  CUtensorMap out_map;                // [rows][sc] bf16, box {64 ch, 128 rows}
+  ThinSrc src;
   const __nv_bfloat16* wp;            // [sc][Kp]
   const float* bias;
-  int64_t rows;
-  int32_t Kp, T, sc, block_n, num_tiles, fast_k4s2, act, dbg;
+  int32_t Kp, sc, block_n, num_tiles, act;
   float slope;
   uint32_t idesc, tmem_cols;
-  ThinTap tap[64];
 };
 
 // element t (0..63) of row r lives at r*128 + ((t/8) ^ (r & 7))*16 + (t % 8)*2  (SWIZZLE_128B)
@@ -39,7 +46,7 @@ __device__ __forceinline__ uint32_t thin_chunk(uint32_t tile, int r, int c) {
 // One im2col row through the tap table, branch free: every load is unconditional (an out-of-range tap
 // reads element 0 and is masked afterwards), so the compiler issues all of them before the first use.
 template <int TMAX>
-__device__ __forceinline__ void thin_gather_row(const ThinGatherParams& P, const uint16_t* __restrict__ xb, int base,
+__device__ __forceinline__ void thin_gather_row(const ThinSrc& P, const uint16_t* __restrict__ xb, int base,
                                                 int id0, int ih0, int iw0, uint32_t* pk) {
   const Geo& g = P.g;
   uint32_t e[TMAX];
@@ -53,6 +60,82 @@ __device__ __forceinline__ void thin_gather_row(const ThinGatherParams& P, const
   }
 #pragma unroll
   for (int i = 0; i < 32; i++) pk[i] = 2 * i + 1 < TMAX ? (e[2 * i] | (e[2 * i + 1] << 16)) : 0u;
+}
+
+// Row r of the 128-voxel x 64-tap im2col tile `tile`, written to the 128-byte-swizzled tile at `dst`.
+__device__ __forceinline__ void thin_build_row(const ThinSrc& S, const uint16_t* __restrict__ xb, uint32_t dst, int tile,
+                                               int r, int warp, int lane) {
+  const Geo& g = S.g;
+  const int64_t v = (int64_t)tile * kBlockM + r;
+  if (S.fast_k4s2 == 2) {
+    // k = 4, stride 2, pad 1, sw % 32 == 0: the 32 lanes of a warp are 32 consecutive ow of ONE (n, od, oh)
+    // line (rows % 32 == 0, so a warp is all valid or all tail).  Taps (kd, kh, 0..3) = input elements
+    // 2*ow-1 .. 2*ow+2: each lane loads only its aligned middle pair (2*ow, 2*ow+1) per line - 16
+    // independent loads issued back to back - and takes the outer two elements from its neighbours'
+    // pairs through warp shuffles.  All index arithmetic is 32-bit and warp-uniform where possible.
+    const uint32_t v0 = (uint32_t)tile * kBlockM + (uint32_t)(warp * 32);        // < 2^31 (host check)
+    if (v0 >= (uint32_t)S.rows) {
+#pragma unroll
+      for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);
+    } else {
+      uint32_t t = v0 / (uint32_t)g.sw;
+      const int ow = (int)(v0 - t * (uint32_t)g.sw) + lane;
+      const uint32_t t2 = t / (uint32_t)g.sh;
+      const int oh = (int)(t - t2 * (uint32_t)g.sh);
+      const uint32_t n = t2 / (uint32_t)g.sd;
+      const int od = (int)(t2 - n * (uint32_t)g.sd);
+      const int id0 = 2 * od - 1, ih0 = 2 * oh - 1;
+      const int sH = g.bw, sD = g.bh * g.bw;
+      // element offset of (n, id0, ih0, 2*ow); lines with id / ih out of range are never dereferenced
+      const int base = ((int)n * g.bd + id0) * sD + ih0 * sH + 2 * ow;
+      // all loads of the tile row are issued before anything consumes them: the middle pairs, and on
+      // the two edge lanes the one element their missing neighbour would have supplied
+      uint32_t mid[16], edge[16];
+      const bool left = lane == 0 && ow > 0, right = lane == 31 && 2 * ow + 2 < g.bw;
+#pragma unroll
+      for (int l = 0; l < 16; l++) {
+        const int id = id0 + (l >> 2), ih = ih0 + (l & 3);
+        const bool ok = id >= 0 && id < g.bd && ih >= 0 && ih < g.bh;   // warp-uniform
+        const uint16_t* px = xb + base + (l >> 2) * sD + (l & 3) * sH;
+        mid[l] = ok ? __ldg(reinterpret_cast<const uint32_t*>(px)) : 0u;
+        edge[l] = 0u;
+        if (ok && left) edge[l] = (uint32_t)__ldg(px - 1);
+        if (ok && right) edge[l] = (uint32_t)__ldg(px + 2);
+      }
+      uint32_t w4[4];
+#pragma unroll
+      for (int l = 0; l < 16; l++) {
+        uint32_t e0 = __shfl_up_sync(0xffffffffu, mid[l], 1) >> 16;                 // x[2*ow - 1]
+        uint32_t e3 = __shfl_down_sync(0xffffffffu, mid[l], 1) & 0xffffu;           // x[2*ow + 2]
+        if (lane == 0) e0 = edge[l];
+        if (lane == 31) e3 = edge[l];
+        w4[(l & 1) * 2] = e0 | (mid[l] << 16);
+        w4[(l & 1) * 2 + 1] = (mid[l] >> 16) | (e3 << 16);
+        if (l & 1) st_shared_v4(thin_chunk(dst, r, l >> 1), w4[0], w4[1], w4[2], w4[3]);
+      }
+    }
+  } else
+  if (v >= S.rows) {
+#pragma unroll
+    for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);
+  } else {
+    // any geometry with <= 64 taps (host-built tap table, 32-bit indices): all predicated loads of the
+    // row are issued before the first store consumes one
+    uint32_t q = (uint32_t)v;
+    uint32_t t1 = q / (uint32_t)g.sw;
+    const int ow = (int)(q - t1 * (uint32_t)g.sw);
+    uint32_t t2 = t1 / (uint32_t)g.sh;
+    const int oh = (int)(t1 - t2 * (uint32_t)g.sh);
+    const uint32_t n = t2 / (uint32_t)g.sd;
+    const int od = (int)(t2 - n * (uint32_t)g.sd);
+    const int id0 = od * g.s[0] - g.p[0], ih0 = oh * g.s[1] - g.p[1], iw0 = ow * g.s[2] - g.p[2];
+    const int base = (((int)n * g.bd + id0) * g.bh + ih0) * g.bw + iw0;
+    uint32_t pk[32];
+    if (S.T <= 32) thin_gather_row<32>(S, xb, base, id0, ih0, iw0, pk);
+    else thin_gather_row<64>(S, xb, base, id0, ih0, iw0, pk);
+#pragma unroll
+    for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+  }
 }
 
 __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __grid_constant__ ThinGatherParams P) {
@@ -70,7 +153,6 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
   auto tfull = [&](int a) { return bar0 + 8u * (2 * kThinStages + a); };
   auto tempty = [&](int a) { return bar0 + 8u * (2 * kThinStages + 2 + a); };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const Geo& g = P.g;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kThinStages; s++) { mbar_init(afull(s), 4); mbar_init(aempty(s), 1); }
@@ -97,84 +179,14 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
   if (warp < 4) {
     // ===== producers: thread r builds row r of every A tile =====
     const int r = threadIdx.x;
-    const uint16_t* xb = reinterpret_cast<const uint16_t*>(P.big);
+    const uint16_t* xb = reinterpret_cast<const uint16_t*>(P.src.big);
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
       const uint32_t s = it % kThinStages, ph = (it / kThinStages) & 1u;
       mbar_wait(aempty(s), ph ^ 1u);
       const uint32_t dst = a_ring + s * kThinTile;
-      const int64_t v = (int64_t)tile * kBlockM + r;
-      if (P.dbg & 32) {
-      } else if (P.fast_k4s2 == 2) {
-        // k = 4, stride 2, pad 1, sw % 32 == 0: the 32 lanes of a warp are 32 consecutive ow of ONE (n, od, oh)
-        // line (rows % 32 == 0, so a warp is all valid or all tail).  Taps (kd, kh, 0..3) = input elements
-        // 2*ow-1 .. 2*ow+2: each lane loads only its aligned middle pair (2*ow, 2*ow+1) per line - 16
-        // independent loads issued back to back - and takes the outer two elements from its neighbours'
-        // pairs through warp shuffles.  All index arithmetic is 32-bit and warp-uniform where possible.
-        const uint32_t v0 = (uint32_t)tile * kBlockM + (uint32_t)(warp * 32);        // < 2^31 (host check)
-        if (v0 >= (uint32_t)P.rows) {
-#pragma unroll
-          for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);
-        } else {
-          uint32_t t = v0 / (uint32_t)g.sw;
-          const int ow = (int)(v0 - t * (uint32_t)g.sw) + lane;
-          const uint32_t t2 = t / (uint32_t)g.sh;
-          const int oh = (int)(t - t2 * (uint32_t)g.sh);
-          const uint32_t n = t2 / (uint32_t)g.sd;
-          const int od = (int)(t2 - n * (uint32_t)g.sd);
-          const int id0 = 2 * od - 1, ih0 = 2 * oh - 1;
-          const int sH = g.bw, sD = g.bh * g.bw;
-          // element offset of (n, id0, ih0, 2*ow); lines with id / ih out of range are never dereferenced
-          const int base = ((int)n * g.bd + id0) * sD + ih0 * sH + 2 * ow;
-          // all loads of the tile row are issued before anything consumes them: the middle pairs, and on
-          // the two edge lanes the one element their missing neighbour would have supplied
-          uint32_t mid[16], edge[16];
-          const bool left = lane == 0 && ow > 0, right = lane == 31 && 2 * ow + 2 < g.bw;
-#pragma unroll
-          for (int l = 0; l < 16; l++) {
-            const int id = id0 + (l >> 2), ih = ih0 + (l & 3);
-            const bool ok = id >= 0 && id < g.bd && ih >= 0 && ih < g.bh && !(P.dbg & 2);   // warp-uniform
-            const uint16_t* px = xb + base + (l >> 2) * sD + (l & 3) * sH;
-            mid[l] = ok ? __ldg(reinterpret_cast<const uint32_t*>(px)) : 0u;
-            edge[l] = 0u;
-            if (ok && left) edge[l] = (uint32_t)__ldg(px - 1);
-            if (ok && right) edge[l] = (uint32_t)__ldg(px + 2);
-          }
-          uint32_t w4[4];
-#pragma unroll
-          for (int l = 0; l < 16; l++) {
-            uint32_t e0 = __shfl_up_sync(0xffffffffu, mid[l], 1) >> 16;                 // x[2*ow - 1]
-            uint32_t e3 = __shfl_down_sync(0xffffffffu, mid[l], 1) & 0xffffu;           // x[2*ow + 2]
-            if (lane == 0) e0 = edge[l];
-            if (lane == 31) e3 = edge[l];
-            w4[(l & 1) * 2] = e0 | (mid[l] << 16);
-            w4[(l & 1) * 2 + 1] = (mid[l] >> 16) | (e3 << 16);
-            if (l & 1) st_shared_v4(thin_chunk(dst, r, l >> 1), w4[0], w4[1], w4[2], w4[3]);
-          }
-        }
-      } else
-      if (v >= P.rows) {
-#pragma unroll
-        for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);
-      } else {
-        // any geometry with <= 64 taps (host-built tap table, 32-bit indices): all predicated loads of the
-        // row are issued before the first store consumes one
-        uint32_t q = (uint32_t)v;
-        uint32_t t1 = q / (uint32_t)g.sw;
-        const int ow = (int)(q - t1 * (uint32_t)g.sw);
-        uint32_t t2 = t1 / (uint32_t)g.sh;
-        const int oh = (int)(t1 - t2 * (uint32_t)g.sh);
-        const uint32_t n = t2 / (uint32_t)g.sd;
-        const int od = (int)(t2 - n * (uint32_t)g.sd);
-        const int id0 = od * g.s[0] - g.p[0], ih0 = oh * g.s[1] - g.p[1], iw0 = ow * g.s[2] - g.p[2];
-        const int base = (((int)n * g.bd + id0) * g.bh + ih0) * g.bw + iw0;
-        uint32_t pk[32];
-        if (P.T <= 32) thin_gather_row<32>(P, xb, base, id0, ih0, iw0, pk);
-        else thin_gather_row<64>(P, xb, base, id0, ih0, iw0, pk);
-#pragma unroll
-        for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-      }
-      if (!(P.dbg & 16)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+      thin_build_row(P.src, xb, dst, tile, r, warp, lane);
+      fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core's async proxy
       __syncwarp();
       if (lane == 0) mbar_arrive(afull(s));
     }
@@ -195,7 +207,7 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
         const int nk = (P.Kp + 15) / 16;
 #pragma unroll
         for (int k = 0; k < 4; k++)
-          if (k < nk && !(P.dbg & 8)) umma_f16(d_tmem, smem_desc(a_addr + k * 32, hi), smem_desc(w_tile + k * 32, hi), P.idesc, k ? 1u : 0u);
+          if (k < nk) umma_f16(d_tmem, smem_desc(a_addr + k * 32, hi), smem_desc(w_tile + k * 32, hi), P.idesc, k ? 1u : 0u);
         umma_commit(aempty(s));
         umma_commit(tfull(acc));
       }
@@ -218,7 +230,6 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
         named_bar_sync(2, 128);
         uint32_t v[64];
         const int ncol = P.block_n - j * 64 < 64 ? P.block_n - j * 64 : 64;
-        if (P.dbg & 4) continue;
         const uint32_t tcol = tmem_base + lane_off + acc * (uint32_t)P.block_n + j * 64;
 #pragma unroll
         for (int q = 0; q < 4; q++)
@@ -242,7 +253,7 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
                          pack_bf16x2(__uint_as_float(v[ch * 8 + 6]), __uint_as_float(v[ch * 8 + 7])));
         fence_proxy_async();
         named_bar_sync(2, 128);
-        if (et == 0 && !(P.dbg & 1)) {
+        if (et == 0) {
           tma_store_2d(&P.out_map, sbuf, j * 64, tile * kBlockM);
           tma_store_commit();
         }
@@ -256,4 +267,153 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
   tc_fence_before();
   __syncthreads();
   if (warp == 4) tmem_dealloc(tmem_base, P.tmem_cols);
+}
+
+// =============================================================================
+// Weight gradient of the same layer class, fused the same way:
+//
+//   dW[c, t] = sum_v dY[v, c] * A[v, t]
+//
+// a GEMM with the voxel index as K.  Both operands are MN-major: dY is read in its natural [voxel][channel]
+// form by TMA (64 x 64 slabs), and the im2col tile the producers build ([voxel][tap], 128-byte swizzled
+// rows) is byte for byte the tile of the forward kernel - there it is a K-major A operand, here an
+// MN-major B operand with N = 64 taps.  M = 128 channel rows (rows >= sc hold zeros or are dropped).
+// Each CTA owns a contiguous range of 128-voxel tiles and writes one fp32 partial [sc][64] to the
+// workspace; thin_wgrad_reduce_kernel sums the partials in a fixed order (deterministic) and writes
+// torch's [sc][T] layout (tap-reversed for the mirrored Cout = 1 convolutions).
+//
+// Roles (192 threads): warps 0-3 producers then epilogue, warp 4 TMA (dY), warp 5 MMA issuer.
+// =============================================================================
+constexpr int kThinWgThreads = 192;
+
+struct alignas(64) ThinWgradParams {
+  CUtensorMap dy_map;                 // [rows][sc] bf16, box {64 ch, 64 rows}
+  ThinSrc src;
+  float* ws;                          // [splits][sc][64] fp32
+  int32_t sc, ach, num_tiles, tiles_per_cta, stages;
+  uint32_t idesc, tmem_cols;
+};
+
+__global__ void __launch_bounds__(kThinWgThreads, 2) thin_wgrad_kernel(const __grid_constant__ ThinWgradParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t sbase = (raw + 1023u) & ~1023u;
+  uint8_t* sgen = smem_raw + (sbase - raw);
+  const int stages = P.stages;
+  const uint32_t a_bytes = (uint32_t)P.ach * 2u * kSlabBytes;            // 2 voxel halves x ach channel slabs
+  const uint32_t stage_bytes = a_bytes + kThinTile;
+  const uint32_t bar0 = sbase + stages * stage_bytes;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sgen + stages * stage_bytes + (2 * stages + 1) * 8);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (stages + s); };
+  const uint32_t acc_bar = bar0 + 8u * (2 * stages);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  const int t0 = blockIdx.x * P.tiles_per_cta;
+  const int t1 = t0 + P.tiles_per_cta < P.num_tiles ? t0 + P.tiles_per_cta : P.num_tiles;
+  const int iters = t1 > t0 ? t1 - t0 : 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; s++) { mbar_init(full_bar(s), 5); mbar_init(empty_bar(s), 1); }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+    prefetch_tmap(&P.dy_map);
+  }
+  if (warp == 5) { tmem_alloc(smem_u32(tmem_slot), P.tmem_cols); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  if (warp < 4) {
+    // ===== producers: thread r builds row r (one voxel, 64 taps) of every B tile =====
+    const int r = threadIdx.x;
+    const uint16_t* xb = reinterpret_cast<const uint16_t*>(P.src.big);
+    for (int it = 0; it < iters; it++) {
+      const int s = it % stages;
+      const uint32_t ph = (uint32_t)(it / stages) & 1u;
+      mbar_wait(empty_bar(s), ph ^ 1u);
+      thin_build_row(P.src, xb, sbase + s * stage_bytes + a_bytes, t0 + it, r, warp, lane);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full_bar(s));
+    }
+    // ===== epilogue: thread r owns channel r of the partial =====
+    mbar_wait(acc_bar, 0);
+    tc_fence_after();
+    const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
+    float* orow = P.ws + ((int64_t)blockIdx.x * P.sc + r) * 64;
+#pragma unroll
+    for (int c0 = 0; c0 < 64; c0 += 16) {
+      uint32_t v[16];
+      if (iters > 0) { tmem_ld16(trow + c0, v); tmem_ld_wait(); }
+      else {
+#pragma unroll
+        for (int j = 0; j < 16; j++) v[j] = 0u;
+      }
+      if (r < P.sc) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) *reinterpret_cast<uint4*>(orow + c0 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+    }
+  } else if (warp == 4) {
+    if (lane == 0) {
+      for (int it = 0; it < iters; it++) {
+        const int s = it % stages;
+        const uint32_t ph = (uint32_t)(it / stages) & 1u;
+        if (!mbar_wait(empty_bar(s), ph ^ 1u)) break;
+        mbar_arrive_expect_tx(full_bar(s), a_bytes);
+        const uint32_t a_dst = sbase + s * stage_bytes;
+        const int v0 = (t0 + it) * kBlockM;
+        for (int h = 0; h < 2; h++)
+          for (int j = 0; j < P.ach; j++)
+            tma_load_2d(a_dst + (uint32_t)(h * P.ach + j) * kSlabBytes, &P.dy_map, full_bar(s), j * 64, v0 + h * 64);
+      }
+    }
+  } else {
+    if (lane == 0) {
+      // MN-major SW128: LBO = next 64 channels (one slab on), SBO = 1024 (next 8 voxel rows).  With one
+      // channel slab (sc <= 64) accumulator rows 64..127 read whatever follows - they are never stored.
+      constexpr uint64_t hi = smem_desc_hi(kSlabBytes, 1024, 2);
+      bool ok = true;
+      for (int it = 0; it < iters && ok; it++) {
+        const int s = it % stages;
+        const uint32_t ph = (uint32_t)(it / stages) & 1u;
+        ok = mbar_wait(full_bar(s), ph);
+        tc_fence_after();
+        const uint32_t a_addr = sbase + s * stage_bytes, b_addr = a_addr + a_bytes;
+#pragma unroll
+        for (int k = 0; k < kBlockM / 16; k++)      // 16 voxel rows per MMA
+          umma_f16(tmem_base, smem_desc(a_addr + (uint32_t)((k >> 2) * P.ach) * kSlabBytes + (k & 3) * 2048, hi),
+                   smem_desc(b_addr + k * 2048, hi), P.idesc, (it | k) != 0 ? 1u : 0u);
+        umma_commit(empty_bar(s));
+      }
+      if (iters > 0) umma_commit(acc_bar);
+      else mbar_arrive(acc_bar);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem_base, P.tmem_cols);
+}
+
+// dw[c][t] = sum_split ws[split][c][flip ? T-1-t : t]
+__global__ void __launch_bounds__(256)
+thin_wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int sc, int T, int splits, int flip) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= sc * T) return;
+  const int c = idx / T, t = idx - c * T;
+  const float* p = ws + (int64_t)c * 64 + (flip ? T - 1 - t : t);
+  const int64_t pitch = (int64_t)sc * 64;
+  float acc = 0.f;
+  int s = 0;
+  for (; s + 8 <= splits; s += 8) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) v[j] = p[(s + j) * pitch];
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc += v[j];
+  }
+  for (; s < splits; s++) acc += p[s * pitch];
+  dw[idx] = acc;
 }

@@ -273,6 +273,8 @@ size_t thin_workspace(const Geo& g, int kind) {
   if (kind == 2) {
     b += align256((size_t)g.sc * thin_kp(g) * sizeof(float));
     b += tc_wgrad_workspace(gemm_geo(rows_of(g), g.sc, thin_kp(g)));
+    const size_t fused = tc_thin_wgrad_workspace(g);
+    if (fused > b) b = fused;
   }
   return b;
 }
@@ -333,6 +335,10 @@ int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void
                bool flip) {
   if (!ws || wsb < thin_workspace(g, 2)) return B2C_ERR_WORKSPACE;
   const int Kp = thin_kp(g), T = g.taps();
+  if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
+    const int frc = tc_thin_wgrad_launch(g, small, big, dw, flip ? 1 : 0, ws, wsb, st);
+    if (frc != B2C_ERR_UNSUPPORTED) return frc;
+  }
   int rc = im2col_launch(g, big, ws, st);
   if (rc) return rc;
   uint8_t* p = static_cast<uint8_t*>(ws) + col_bytes(g);
