@@ -430,7 +430,8 @@ struct alignas(64) TcWgradParams {
   int32_t a_ch, b_ch, a_tiles, b_tiles, block_n;   // M side (128-row tiles) / N side (block_n columns)
   int32_t m_big;                     // 1: M side = big tensor (tap-shifted), N side = small tensor
   int32_t tpack;                     // > 1: narrow big tensor (<= 64 ch): N = tpack taps x one 64-column slab each
-  int32_t ngroups;                   // tap groups = ceil(ntaps / tpack)
+  int32_t ngroups;                   // tap groups = ceil(ntaps / tpack), or M-unit groups = ceil(ntaps * a_tiles / mt)
+  int32_t mt;                        // M tiles (tap, a_tile) per CTA sharing one N-side tile: 1 or 2 accumulators
   int32_t stages;
   uint32_t idesc, tmem_cols;
   float* ws;
@@ -443,7 +444,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
   uint8_t* sgen = smem_raw + (sbase - raw);
   const int stages = P.stages;
   const int b_slabs = P.block_n / 64;
-  const uint32_t a_bytes = 2 * kSlabBytes, b_bytes = b_slabs * kSlabBytes;
+  const uint32_t a_tile_bytes = 2 * kSlabBytes;
+  const uint32_t a_bytes = P.mt * a_tile_bytes, b_bytes = b_slabs * kSlabBytes;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t bar0 = sbase + stages * stage_bytes;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sgen + stages * stage_bytes + (2 * stages + 1) * 8);
@@ -454,10 +456,20 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
 
   int id = blockIdx.x;
   const int bt = id % P.b_tiles; id /= P.b_tiles;
-  const int at = id % P.a_tiles; id /= P.a_tiles;
-  const int ti = id % P.ngroups;             // tap (tpack == 1) or tap group
+  int at = 0, ti, nmt = 1;                   // first M unit of this CTA and how many it owns
+  int at2 = 0, ti2 = 0;                      // second M unit (mt == 2)
+  if (P.mt > 1) {
+    const int gi = id % P.ngroups, u = gi * 2, total = P.ntaps * P.a_tiles;
+    ti = u / P.a_tiles; at = u - ti * P.a_tiles;
+    if (u + 1 < total) { nmt = 2; ti2 = (u + 1) / P.a_tiles; at2 = (u + 1) - ti2 * P.a_tiles; }
+  } else {
+    at = id % P.a_tiles; id /= P.a_tiles;
+    ti = id % P.ngroups;                     // tap (tpack == 1) or tap group
+  }
   const int sp = id / P.ngroups;
   const TapDesc tp = P.taps[ti * P.tpack];
+  const TapDesc tp2 = P.taps[ti2];
+  const uint32_t tx_bytes = stage_bytes - (uint32_t)(P.mt - nmt) * a_tile_bytes;
   const int kt0 = sp * P.ktiles_per_split;
   const int kt1 = kt0 + P.ktiles_per_split < P.ktiles ? kt0 + P.ktiles_per_split : P.ktiles;
   const int iters = kt1 - kt0;
@@ -487,7 +499,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
         const int s = it % stages;
         const uint32_t ph = (uint32_t)(it / stages) & 1u;
         if (!mbar_wait(empty_bar(s), ph ^ 1u)) break;
-        mbar_arrive_expect_tx(full_bar(s), stage_bytes);
+        mbar_arrive_expect_tx(full_bar(s), tx_bytes);
         const uint32_t a_dst = sbase + s * stage_bytes;
         // the big tensor is read at the tap-shifted voxel box, the small one at the box itself
         const CUtensorMap* mm = P.m_big ? bm : &P.s_map;
@@ -496,6 +508,14 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
         const int nw = tp.off_w - mw, nh = tp.off_h - mh, nd = tp.off_d - md;
         for (int j = 0; j < 2; j++)
           tma_load_5d(a_dst + j * kSlabBytes, mm, full_bar(s), at * 128 + j * 64, q0w + mw, q0h + mh, q0d + md, q0n);
+        if (nmt > 1) {
+          // second M tile: its own tap shift when the big tensor sits on M, else the next 128 small channels
+          const CUtensorMap* mm2 = P.m_big ? &P.b_maps[tp2.map] : &P.s_map;
+          const int w2 = P.m_big ? tp2.off_w : 0, h2 = P.m_big ? tp2.off_h : 0, d2 = P.m_big ? tp2.off_d : 0;
+          for (int j = 0; j < 2; j++)
+            tma_load_5d(a_dst + a_tile_bytes + j * kSlabBytes, mm2, full_bar(s), at2 * 128 + j * 64, q0w + w2, q0h + h2,
+                        q0d + d2, q0n);
+        }
         if (P.tpack > 1) {
           // slab j = tap (group * tpack + j) of the <= 64-channel big tensor (a short last group
           // re-reads its last tap; the epilogue drops those columns)
@@ -526,6 +546,12 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
         for (int k = 0; k < kWgVox / 16; k++)     // 16 voxel rows of 128 B per MMA
           umma_f16(tmem_base, smem_desc(a_addr + k * 2048, hi), smem_desc(b_addr + k * 2048, hi), P.idesc,
                    (it | k) != 0 ? 1u : 0u);
+        if (nmt > 1) {
+#pragma unroll
+          for (int k = 0; k < kWgVox / 16; k++)
+            umma_f16(tmem_base + (uint32_t)P.block_n, smem_desc(a_addr + a_tile_bytes + k * 2048, hi),
+                     smem_desc(b_addr + k * 2048, hi), P.idesc, (it | k) != 0 ? 1u : 0u);
+        }
         umma_commit(empty_bar(s));
       }
       if (iters > 0) umma_commit(acc_bar);
@@ -533,12 +559,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
     }
   } else {
     const int grp = warp & 3;
-    const int a = at * 128 + grp * 32 + lane;
-    const bool valid = a < P.a_ch;
-    float* orow = P.ws + (((int64_t)sp * P.ntaps + ti) * P.a_ch + a) * P.b_ch;
     mbar_wait(acc_bar, 0);
     tc_fence_after();
-    const uint32_t trow = tmem_base + ((uint32_t)(grp * 32) << 16);
+    for (int m = 0; m < nmt; m++) {
+    const int a = (m ? at2 : at) * 128 + grp * 32 + lane;
+    const bool valid = a < P.a_ch;
+    float* orow = P.ws + (((int64_t)sp * P.ntaps + (m ? ti2 : ti)) * P.a_ch + a) * P.b_ch;
+    const uint32_t trow = tmem_base + ((uint32_t)(grp * 32) << 16) + (uint32_t)(m * P.block_n);
     for (int c0 = 0; c0 < P.block_n; c0 += 16) {
       uint32_t v[16];
       if (iters > 0) { tmem_ld16(trow + c0, v); tmem_ld_wait(); }
@@ -564,6 +591,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_wgrad_kernel(const __grid_co
           if (col + j < P.b_ch)                 // b_ch % 8 == 0
             *reinterpret_cast<uint4*>(orow + col + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
       }
+    }
     }
   }
   tc_fence_before();
@@ -737,7 +765,7 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
 }
 
 // ---- wgrad ---------------------------------------------------------------------
-struct WgradCfg { ConvPlan plan; int box[4], tiles[4]; int ktiles, splits, kps, a_tiles, b_tiles, block_n, m_big, m_ch, n_ch, tpack, ngroups; };
+struct WgradCfg { ConvPlan plan; int box[4], tiles[4]; int ktiles, splits, kps, a_tiles, b_tiles, block_n, m_big, m_ch, n_ch, tpack, ngroups, mt; };
 
 static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   if (g.sc % 8 != 0 || g.bc % 8 != 0 || g.sc < 16 || g.bc < 16) return B2C_ERR_UNSUPPORTED;
@@ -776,7 +804,18 @@ static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   c->block_n = bn;
   c->a_tiles = (c->m_ch + 127) / 128;
   c->b_tiles = c->tpack > 1 ? 1 : (c->n_ch + bn - 1) / bn;
-  const int64_t units = (int64_t)c->ngroups * c->a_tiles * c->b_tiles;
+  // Two M tiles (two taps, or two 128-channel tiles of one tap) per CTA share the N-side tile: the
+  // kernel is bound by L2 -> SM bytes (measured: loads alone take as long as loads + MMAs), and
+  // (2 x 16 + 32) KB per two 128 x 256 x 64 stages is 2/3 of the bytes of (16 + 32) KB per one.
+  // With the big tensor on M any two units pair up (the small N tile does not depend on the tap);
+  // with the small tensor on M the pair must be two channel tiles of one tap.
+  c->mt = 1;
+  if (c->tpack == 1 && 2 * bn <= 512 && c->plan.ntaps_total * c->a_tiles >= 2 && (c->m_big || c->a_tiles % 2 == 0) &&
+      !getenv("B2C_WG_MT1")) {
+    c->mt = 2;
+    c->ngroups = (c->plan.ntaps_total * c->a_tiles + 1) / 2;
+  }
+  const int64_t units = (int64_t)c->ngroups * (c->mt > 1 ? 1 : c->a_tiles) * c->b_tiles;
   if (units <= 0) return B2C_ERR_UNSUPPORTED;
   // split-K count: 2.5 .. 10 waves of the SMs, at least 64 K-iterations per CTA (16 when the
   // problem has too few tiles to fill the machine otherwise: 1x1x1 filters, 32-channel layers);
@@ -804,7 +843,7 @@ static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   if (splits < 1) splits = 1;
   c->kps = (int)cdiv(c->ktiles, splits);
   c->splits = (int)cdiv(c->ktiles, c->kps);
-  if (units * c->splits > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  if (units * c->splits > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;   // grid = units * splits
   return B2C_OK;
 }
 
@@ -842,18 +881,18 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
   for (int i = 0; i < 4; i++) { P.box[i] = c.box[i]; P.tiles[i] = c.tiles[i]; }
   P.ktiles = c.ktiles; P.ktiles_per_split = c.kps; P.splits = c.splits;
   P.a_ch = c.m_ch; P.b_ch = c.n_ch; P.a_tiles = c.a_tiles; P.b_tiles = c.b_tiles; P.block_n = c.block_n;
-  P.m_big = c.m_big; P.tpack = c.tpack; P.ngroups = c.ngroups;
-  const uint32_t stage_bytes = 2 * kSlabBytes + (c.block_n / 64) * kSlabBytes;
+  P.m_big = c.m_big; P.tpack = c.tpack; P.ngroups = c.ngroups; P.mt = c.mt;
+  const uint32_t stage_bytes = c.mt * 2 * kSlabBytes + (c.block_n / 64) * kSlabBytes;
   int stages = (kSmemBudget - 1024 - 256) / (int)stage_bytes;
   if (stages > 8) stages = 8;
   P.stages = stages;
   P.idesc = idesc_bf16(128, c.block_n, 1, 1);
-  P.tmem_cols = tmem_cols_for(c.block_n);
+  P.tmem_cols = tmem_cols_for(c.mt * c.block_n);
   P.ws = static_cast<float*>(ws);
   if (cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
     return B2C_ERR_CUDA;
   const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
-  const int64_t grid = (int64_t)c.ngroups * c.a_tiles * c.b_tiles * c.splits;
+  const int64_t grid = (int64_t)c.ngroups * (c.mt > 1 ? 1 : c.a_tiles) * c.b_tiles * c.splits;
   tc_wgrad_kernel<<<(unsigned)grid, kThreadsTc, smem, st>>>(P);
   rc = launched();
   if (rc) return rc;
