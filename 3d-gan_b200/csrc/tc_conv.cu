@@ -191,6 +191,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
                                c.q[1] + tp.off_d, c.q[0]);
               tma_load_3d_pair(a_dst + a_bytes, &P.w_map, fb, kc * P.kb, c.nt * P.block_n + rank * (int)b_rows,
                                tp.wtap);
+            } else if (P.dbg & 16) {
+              mbar_arrive(full_bar(s));
             } else {
               mbar_arrive_expect_tx(full_bar(s), stage_bytes);
               tma_load_5d(a_dst, im, full_bar(s), kc * P.kb, c.q[3] + tp.off_w, c.q[2] + tp.off_h,
@@ -237,7 +239,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
               if (k >= nk) break;
               const uint64_t ad = smem_desc(a_addr + m * a_sub + k * 32, hi), bd = smem_desc(b_addr + k * 32, hi);
               if (NCTA == 2) umma_f16_pair(d_tmem + m * P.block_n, ad, bd, P.idesc, (i | k) != 0 ? 1u : 0u);
-              else umma_f16(d_tmem + m * P.block_n, ad, bd, P.idesc, (i | k) != 0 ? 1u : 0u);
+              else if (!(P.dbg & 8) || (i | k) == 0) umma_f16(d_tmem + m * P.block_n, ad, bd, P.idesc, (i | k) != 0 ? 1u : 0u);
             }
           }
           // frees the smem slot (in both CTAs of a pair) when these MMAs retire
@@ -726,6 +728,7 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   const int fixed = 1024 /*alignment slack*/ + (int)kStagingBytes + 256 /*barriers + tmem slot*/;
   int stages = (kSmemBudget - fixed) / (int)stage_bytes;
   if (stages > 8) stages = 8;
+  if (const char* e = getenv("B2C_DBG")) P.dbg = atoi(e);      // timing experiments only (8: no MMAs, 16: no loads)
   if (const char* e = getenv("B2C_STAGES")) { const int v = atoi(e); if (v >= 2 && v < stages) stages = v; }   // experiments
   if (stages < 2) return B2C_ERR_UNSUPPORTED;
   P.stages = stages;
