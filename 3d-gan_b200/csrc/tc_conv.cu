@@ -45,6 +45,7 @@ struct alignas(64) TcConvParams {
   float slope;
   int32_t swap;          // 1: channels on UMMA M (filter tile = A), voxels on N: D^T = W * X^T (narrow Cout)
   int32_t w_rows;        // filter rows staged per stage
+  int32_t nacc;          // TMEM accumulator sets: 2 (epilogue of tile i overlaps tile i+1) or 1 (256 x 256 tiles)
   int32_t dbg;           // B2C_DBG env (diagnostics only): 1 no TMA store, 2 no tcgen05.ld, 4 no st.shared
 };
 
@@ -213,8 +214,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
       bool ok = true;
       for (int tile = first_tile; tile < P.num_tiles && ok; tile += tile_step, tcount++) {
         const TileCoord c = decode_tile<NCTA>(P, tile, 0);
-        const uint32_t acc = tcount & 1u;
-        const uint32_t aph = (tcount >> 1) & 1u;
+        const uint32_t acc = P.nacc == 2 ? (tcount & 1u) : 0u;
+        const uint32_t aph = (P.nacc == 2 ? (tcount >> 1) : tcount) & 1u;
         // the epilogues (of both CTAs) have drained this accumulator set
         ok = NCTA == 2 ? mbar_wait_cluster(tempty_bar(acc), aph ^ 1u) : mbar_wait(tempty_bar(acc), aph ^ 1u);
         tc_fence_after();
@@ -264,8 +265,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
     // named barriers of the 128 epilogue threads stay matched and the kernel drains.
     for (int tile = first_tile; tile < P.num_tiles; tile += tile_step, tcount++) {
       const TileCoord c = decode_tile<NCTA>(P, tile, rank);
-      const uint32_t acc = tcount & 1u;
-      const uint32_t aph = (tcount >> 1) & 1u;
+      const uint32_t acc = P.nacc == 2 ? (tcount & 1u) : 0u;
+      const uint32_t aph = (P.nacc == 2 ? (tcount >> 1) : tcount) & 1u;
       if (NCTA == 2) mbar_wait_cluster(tfull_bar(acc), aph); else mbar_wait(tfull_bar(acc), aph);
       tc_fence_after();
       const CUtensorMap* om = &P.out_maps[c.si];
@@ -733,7 +734,8 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   if (stages < 2) return B2C_ERR_UNSUPPORTED;
   P.stages = stages;
   P.idesc = p.swap ? idesc_bf16(128, 128 * p.mt, 0, 0) : idesc_bf16(kBlockM * ncta, p.block_n, 0, 0);
-  P.tmem_cols = tmem_cols_for(2 * p.mt * p.block_n);
+  P.nacc = p.mt * p.block_n > 256 ? 1 : 2;
+  P.tmem_cols = tmem_cols_for(P.nacc * p.mt * p.block_n);
   if (P.tmem_cols > 512) return B2C_ERR_UNSUPPORTED;
   P.bias = bias; P.bias_mod = bias_mod > 0 ? bias_mod : p.nout; P.act = act; P.slope = slope;
   const size_t smem = (size_t)stages * stage_bytes + fixed;

@@ -50,25 +50,45 @@ static int finish(ConvPlan* p, int kin, int nout) {
   int64_t vox = 1;
   for (int i = 0; i < 4; i++) vox *= pow2ceil(ext[i] > 0 ? ext[i] : 1);
   while (mt > 1 && vox < (int64_t)kBlockM * mt) mt >>= 1;
-  for (;; mt >>= 1) {
-    choose_box(ext, p->box, kBlockM * mt);
+  // box / sub-tile split / tile counts for `m` sub-tiles per CTA; false if the box cannot be split
+  auto layout = [&](int m) -> bool {
+    choose_box(ext, p->box, kBlockM * m);
     int sd = 0;
     while (sd < 3 && p->box[sd] == 1) sd++;
-    if (p->box[sd] >= mt && p->box[sd] % mt == 0) { p->split_dim = sd; p->sub_ext = p->box[sd] / mt; break; }
+    if (p->box[sd] < m || p->box[sd] % m != 0) return false;
+    p->split_dim = sd; p->sub_ext = p->box[sd] / m; p->mt = m;
+    int64_t t0 = 0;
+    for (int s = 0; s < p->nsubs; s++) {
+      SubDesc& sub = p->subs[s];
+      int64_t nt = 1;
+      for (int i = 0; i < 4; i++) { sub.tiles[i] = (sub.ext[i] + p->box[i] - 1) / p->box[i]; nt *= sub.tiles[i]; }
+      sub.tile0 = (int32_t)t0;
+      t0 += nt;
+    }
+    p->m_tiles = (int32_t)t0;
+    return t0 * p->tiles_n <= 0x7fffffffLL;
+  };
+  for (;; mt >>= 1) {
+    if (layout(mt)) break;
     if (mt == 1) return B2C_ERR_UNSUPPORTED;
   }
-  p->mt = mt;
-  for (int i = 0; i < 4; i++) if (p->box[i] > 256) return B2C_ERR_UNSUPPORTED;
-  int64_t t0 = 0;
-  for (int s = 0; s < p->nsubs; s++) {
-    SubDesc& sd = p->subs[s];
-    int64_t nt = 1;
-    for (int i = 0; i < 4; i++) { sd.tiles[i] = (sd.ext[i] + p->box[i] - 1) / p->box[i]; nt *= sd.tiles[i]; }
-    sd.tile0 = (int32_t)t0;
-    t0 += nt;
-    if (t0 * p->tiles_n > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  // Wide N (256 columns): a 256 x 256 tile on ONE accumulator set moves 2/3 of the L2 -> SM bytes per
+  // MAC of a 128 x 256 tile (the kernel is bound by those bytes and by the power they cost), at the
+  // price of an exposed epilogue and half as many tiles: taken when the reduction is long and the
+  // last wave of the persistent grid does not get much emptier (measured gain ~1.2x per tile).
+  if (bn == 256 && mt == 1 && !p->swap && (int64_t)min_taps * p->kchunks >= 32 && vox >= 2 * kBlockM &&
+      !getenv("B2C_MT1")) {
+    const int sms = num_sms();
+    auto eff = [&](int64_t t) { return (double)t / (double)(((t + sms - 1) / sms) * sms); };
+    const int64_t tiles1 = (int64_t)p->m_tiles * p->tiles_n;
+    if (layout(2)) {
+      const int64_t tiles2 = (int64_t)p->m_tiles * p->tiles_n;
+      if (1.2 * eff(tiles2) < eff(tiles1)) layout(1);
+    } else if (!layout(1)) {
+      return B2C_ERR_UNSUPPORTED;
+    }
   }
-  p->m_tiles = (int32_t)t0;
+  for (int i = 0; i < 4; i++) if (p->box[i] > 256) return B2C_ERR_UNSUPPORTED;
   return B2C_OK;
 }
 
