@@ -29,13 +29,20 @@ def make_resample_filter(taps=(1, 3, 3, 1)):
     return f / f.sum()
 
 
-def _conv(x, w, stride=1, padding=0, transpose=False, flip_weight=True):
-    """stylegan.py:164-170.  `flip_weight=False` means true convolution: reverse the taps."""
+_ACT = {"linear": (None, 0.0), "lrelu": ("lrelu", 0.2), "relu": ("relu", 0.0), "tanh": ("tanh", 0.0)}
+
+
+def _conv(x, w, stride=1, padding=0, transpose=False, flip_weight=True, bias=None, act="linear"):
+    """stylegan.py:164-170.  `flip_weight=False` means true convolution: reverse the taps.
+    `bias` / `act` ride in the GEMM epilogue (bias_act of stylegan.py:118-124 fused)."""
     if not flip_weight:
         w = w.flip([2, 3, 4])
+    if act not in _ACT:
+        raise NotImplementedError("activation %r is not used by the reference's networks" % (act,))
+    a, slope = _ACT[act]
     if transpose:
-        return BF.conv_transpose3d(x, w, None, stride, padding)
-    return BF.conv3d(x, w, None, stride, padding)
+        return BF.conv_transpose3d(x, w, bias, stride, padding, act=a, slope=slope)
+    return BF.conv3d(x, w, bias, stride, padding, act=a, slope=slope)
 
 
 def _resample_pads(fk, up, down, padding):
@@ -49,7 +56,11 @@ def _resample_pads(fk, up, down, padding):
     return lo, hi
 
 
-def conv3d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight=True, flip_filter=False):
+def conv3d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight=True, flip_filter=False,
+                    bias=None, act="linear"):
+    """stylegan.py:202-294.  Extension: `bias` / `act` = the `bias_act` the calling layer applies to
+    the result (stylegan.py:485); fused into the convolution's epilogue whenever the convolution is
+    the last operation of the funnel, applied as a separate pass after the FIR otherwise."""
     if groups != 1:
         raise NotImplementedError("grouped conv3d_resample is only reached by the dead fused_modconv branch")
     if not all(isinstance(v, int) for v in (up, down, padding)):
@@ -60,16 +71,18 @@ def conv3d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight
     fir = lambda t, **kw: BF.upfirdn3d(t, f, flip_filter=flip_filter, **kw)   # noqa: E731
     pads = lambda a, b: [a, b, a, b, a, b]                                    # noqa: E731
 
+    ep = dict(bias=bias, act=act)
     if up == 1 and down == 1:
         if lo == hi and lo >= 0:
-            return _conv(x, w, padding=lo, flip_weight=flip_weight)
-        return _conv(BF.upfirdn3d(x, None, padding=pads(lo, hi)), w, flip_weight=flip_weight)
+            return _conv(x, w, padding=lo, flip_weight=flip_weight, **ep)
+        return _conv(BF.upfirdn3d(x, None, padding=pads(lo, hi)), w, flip_weight=flip_weight, **ep)
     if up == 1:                                  # down-sampling
         if k == 1:                               # decimate first, then the 1x1x1 conv (:244-247)
-            return _conv(fir(x, down=down, padding=pads(lo, hi)), w, flip_weight=flip_weight)
-        return _conv(fir(x, padding=pads(lo, hi)), w, stride=down, flip_weight=flip_weight)     # (:257-260)
+            return _conv(fir(x, down=down, padding=pads(lo, hi)), w, flip_weight=flip_weight, **ep)
+        return _conv(fir(x, padding=pads(lo, hi)), w, stride=down, flip_weight=flip_weight, **ep)   # (:257-260)
     if k == 1 and down == 1:                     # 1x1x1 conv first, then zero-insert + FIR (:250-254)
-        return fir(_conv(x, w, flip_weight=flip_weight), up=up, padding=pads(lo, hi), gain=up ** 2)
+        y = fir(_conv(x, w, flip_weight=flip_weight), up=up, padding=pads(lo, hi), gain=up ** 2)
+        return bias_act(y, bias, act=act)
     # up-sampling conv = transposed conv with stride `up`, then the FIR on what is left of the
     # padding (:262-282); the reference's FIR gain is up**2 in 3-D as well - kept
     lo, hi = lo - (k - 1), hi - (k - up)
@@ -78,7 +91,7 @@ def conv3d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight
     y = fir(y, padding=pads(lo + trim, hi + trim), gain=up ** 2)
     if down > 1:
         y = fir(y, down=down)
-    return y
+    return bias_act(y, bias, act=act)
 
 
 def demod_coefficients(weight, styles):
@@ -104,10 +117,17 @@ def modulated_conv3d(x, weight, styles, noise=None, up=1, down=1, padding=0, res
     return x + noise.to(x.dtype) if noise is not None else x
 
 
+def synthesis_conv(x, weight, styles, noise, bias, up=1, padding=1, resample_filter=None, act="lrelu"):
+    """One SynthesisLayer body (stylegan.py:526-531): modulated conv (+ noise), bias, activation."""
+    x = modulated_conv3d(x=x, weight=weight, styles=styles, noise=noise, up=up, padding=padding,
+                         resample_filter=resample_filter, flip_weight=(up == 1), fused_modconv=False)
+    return bias_act(x, bias, act=act)
+
+
 def bias_act(x, b=None, dim=1, act="linear"):
     """stylegan.py:118-124 (lrelu slope 0.2, no gain)."""
     if b is not None:
-        x = x + b.reshape([-1 if i == dim else 1 for i in range(x.ndim)])
+        x = x + b.to(x.dtype).reshape([-1 if i == dim else 1 for i in range(x.ndim)])
     if act == "linear":
         return x
     if act == "lrelu":

@@ -1,0 +1,304 @@
+"""StyleGAN networks and losses: b200conv3d/stylegan.py and
+oracle/ref_stylegan.py against golden vectors of the UNMODIFIED reference classes
+(tests/golden/stylegan_net_ref.npz, oracle/gen_golden_stylegan_net.py).
+
+CPU: (1) the oracle restatement replays the golden file; (2) the product model built under the
+reference's seed has the reference's state_dict key for key, bit for bit; (3) the product's host
+logic (layer wiring, freeze pattern, R1 / path-length terms) runs with the C ABI bound to the oracle
+library in a subprocess.  GPU: the same through the CUDA kernels in fp32 (exact kernels) and, at a
+width that reaches the tcgen05 path, in bf16 against the fp32 oracle with stock torch bf16 autocast
+on the same GPU as the witness of what bf16 costs."""
+import argparse
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import ref_stylegan as R  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden", "stylegan_net_ref.npz")
+
+
+def _cfg(gold):
+    return {k: int(gold["cfg." + k]) for k in ("res", "cb", "w_dim", "z", "batch", "seed")}
+
+
+def _inputs(c):
+    torch.manual_seed(5)
+    z = torch.randn(c["batch"], c["z"], 1, 1, 1)
+    real = torch.rand(c["batch"], 1, c["res"], c["res"], c["res"]) * 2 - 1
+    return z, real
+
+
+def _noises(res_list, batch):
+    return [[torch.randn(batch, 1, r, r, r) for _ in range(1 if r == 4 else 2)] for r in res_list]
+
+
+def _set_noise_strength(net, v=0.1):
+    with torch.no_grad():
+        for k, p in net.named_parameters():
+            if k.endswith("noise_strength"):
+                p.fill_(v)
+
+
+def _relerr(a, ref):
+    ref = torch.as_tensor(ref)
+    return ((a.detach().float().cpu() - ref).abs().max() / ref.abs().max().clamp_min(1e-30)).item()
+
+
+def _check_grads(named_params, gold, prefix, tol):
+    n = 0
+    for k, p in named_params:
+        key = prefix + k
+        if key not in gold.files:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+            continue
+        ref = torch.from_numpy(gold[key])
+        if float(ref.abs().max()) == 0.0:
+            assert p.grad is None or float(p.grad.abs().max()) < 1e-12, k
+        else:
+            assert _relerr(p.grad, ref) < tol, (k, _relerr(p.grad, ref))
+        n += 1
+    assert n > 10
+
+
+# ------------------------------------------------------------------ oracle vs golden (CPU)
+def test_oracle_stylegan2_replays_reference_golden():
+    gold = np.load(GOLD)
+    c = _cfg(gold)
+    torch.manual_seed(c["seed"])
+    D = R.Discriminator(c["cb"], img_resolution=c["res"])
+    G = R.Generator(c["z"], c["cb"], w_dim=c["w_dim"], img_resolution=c["res"])
+    for pre, m in (("g0.", G), ("d0.", D)):
+        sd = m.state_dict()
+        assert sorted(pre + k for k in sd) == sorted(k for k in gold.files if k.startswith(pre))
+        for k, v in sd.items():
+            np.testing.assert_array_equal(v.numpy(), gold[pre + k], err_msg=k)
+    _set_noise_strength(G)
+    z, real = _inputs(c)
+    with torch.no_grad():
+        img, ws = G(z, noise_mode="const")
+        assert _relerr(img[:, 0, ::2, ::2, ::2], gold["img_const"]) < 1e-5
+        assert _relerr(ws[:, 0], gold["ws"]) < 1e-5
+        assert _relerr(D(img), gold["logits"]) < 1e-5
+        torch.manual_seed(6)
+        img_r, _ = G(z, noises=_noises(G.synthesis.res, c["batch"]))
+        assert _relerr(img_r[:, 0, ::2, ::2, ::2], gold["img_random"]) < 1e-5
+    for q in list(G.parameters()) + list(D.parameters()):
+        q.requires_grad = False
+    for q in D.parameters():
+        q.requires_grad = True
+    lr, lg = R.step_D(G, D, 0, real, z, noise_mode="const")
+    np.testing.assert_allclose([lr.item(), lg.item()], gold["D_losses"], rtol=1e-5)
+    _check_grads(D.named_parameters(), gold, "dgrad.", 1e-4)
+    for q in D.parameters():
+        q.requires_grad, q.grad = False, None
+    for q in G.parameters():
+        q.requires_grad = True
+    pl_mean = torch.zeros([])
+    pl_noise = torch.randn(c["batch"] // 2, 1, c["res"], c["res"], c["res"], generator=torch.Generator().manual_seed(8))
+    lG, _ = R.step_G(G, D, 0, torch.from_numpy(gold["z2"]), pl_mean, pl_noise=pl_noise, noise_mode="const")
+    np.testing.assert_allclose(lG.item(), float(gold["G_loss"]), rtol=1e-5)
+    np.testing.assert_allclose(pl_mean.item(), float(gold["pl_mean"]), rtol=1e-4)
+    _check_grads(G.named_parameters(), gold, "ggrad.", 1e-4)
+
+
+def _v1_check(G1, gold, dev, tol, with_grads=True):
+    z1 = torch.from_numpy(gold["v1_z"]).to(dev)
+    G1.eval()
+    with torch.no_grad():
+        y = G1(z1)
+    assert _relerr(y[:, 0, ::8, ::8, ::8], gold["v1_eval"]) < tol
+    if not with_grads:
+        return
+    G1.train()
+    torch.manual_seed(10)                     # swap point and batch permutation come from the CPU RNG
+    y = G1(z1)
+    assert _relerr(y[:, 0, ::8, ::8, ::8], gold["v1_train"]) < tol
+    y.float().square().mean().backward()
+    params = dict(G1.named_parameters())
+    for key in (k for k in gold.files if k.startswith("v1grad.")):
+        g = params[key[len("v1grad."):]].grad.float().reshape(-1)
+        ref = torch.from_numpy(gold[key])
+        assert _relerr(g[:: max(1, g.numel() // 4096)], ref) < 20 * tol, key
+        norm = float(gold["v1gradnorm." + key[len("v1grad."):]])
+        assert abs(g.double().norm().item() - norm) < 20 * tol * norm, key
+
+
+def test_oracle_stylegan1_replays_reference_golden():
+    gold = np.load(GOLD)
+    torch.manual_seed(int(gold["v1_seed"]))
+    _v1_check(R.StyleGen1(), gold, "cpu", 1e-5, with_grads=False)
+
+
+# ------------------------------------------------------------------ product, host side (CPU)
+def _params(c, device):
+    return argparse.Namespace(z_size=c["z"], filterG=c["cb"], filterD=c["cb"], device=device, stylegan2=True,
+                              stylegan=False)
+
+
+def test_product_stylegan_init_equals_reference():
+    import b200conv3d as B
+    gold = np.load(GOLD)
+    c = _cfg(gold)
+    p = _params(c, "cpu")
+    torch.manual_seed(c["seed"])
+    D = B.stylegan.Discriminator(p, img_resolution=c["res"])            # trainer.py:59-60: D first
+    G = B.stylegan.Generator(p, w_dim=c["w_dim"], img_resolution=c["res"])
+    for pre, m in (("g0.", G), ("d0.", D)):
+        sd = m.state_dict()
+        assert sorted(pre + k for k in sd) == sorted(k for k in gold.files if k.startswith(pre))
+        for k, v in sd.items():
+            np.testing.assert_array_equal(v.numpy(), gold[pre + k], err_msg=k)
+    torch.manual_seed(int(gold["v1_seed"]))
+    g1 = B.stylegan.styleGAN_gen(argparse.Namespace(z_size=512))
+    torch.manual_seed(int(gold["v1_seed"]))
+    o1 = R.StyleGen1()
+    assert list(g1.state_dict()) == list(o1.state_dict())
+    assert all(torch.equal(a, b) for a, b in zip(g1.state_dict().values(), o1.state_dict().values()))
+    assert all(isinstance(m, B.nn.Conv3d) for m in g1.modules() if isinstance(m, torch.nn.Conv3d))
+
+
+def product_from_gold(gold, device):
+    """The product networks with the reference's initial state (from the golden file)."""
+    import b200conv3d as B
+    c = _cfg(gold)
+    p = _params(c, device)
+    D = B.stylegan.Discriminator(p, img_resolution=c["res"])
+    G = B.stylegan.Generator(p, w_dim=c["w_dim"], img_resolution=c["res"])
+    G.load_state_dict({k: torch.from_numpy(gold["g0." + k]) for k in G.state_dict()})
+    D.load_state_dict({k: torch.from_numpy(gold["d0." + k]) for k in D.state_dict()})
+    _set_noise_strength(G)
+    return G.to(device), D.to(device), p, c
+
+
+def product_vs_golden(gold, device, tol):
+    """Forward (const and explicit random noise), one step_D and one step_G at step 0 of the product
+    StyleGAN2Loss under the Trainer's freeze pattern, all against the reference's numbers."""
+    import functools
+
+    import b200conv3d as B
+    G, D, p, c = product_from_gold(gold, device)
+    z, real = _inputs(c)
+    z, real = z.to(device), real.to(device)
+    with torch.no_grad():
+        img, ws = G(z, noise_mode="const")
+        assert _relerr(img[:, 0, ::2, ::2, ::2], gold["img_const"]) < tol
+        assert _relerr(ws[:, 0], gold["ws"]) < tol
+        assert _relerr(D(img), gold["logits"]) < tol
+        torch.manual_seed(6)
+        nz = [[t.to(device) for t in blk] for blk in _noises(G.synthesis.block_resolutions, c["batch"])]
+        img_r, _ = G(z, noises=nz)
+        assert _relerr(img_r[:, 0, ::2, ::2, ::2], gold["img_random"]) < tol
+    loss = B.stylegan.StyleGAN2Loss(p, G.mapping, functools.partial(G.synthesis, noise_mode="const"), D,
+                                    style_mixing_prob=0)
+    for q in list(G.parameters()) + list(D.parameters()):
+        q.requires_grad = False
+    for q in D.parameters():
+        q.requires_grad = True
+    lr, lg = loss.step_D(0, real, z)
+    np.testing.assert_allclose([lr.item(), lg.item()], gold["D_losses"], rtol=10 * tol)
+    _check_grads(D.named_parameters(), gold, "dgrad.", 20 * tol)
+    for q in D.parameters():
+        q.requires_grad, q.grad = False, None
+    for q in G.parameters():
+        q.requires_grad = True
+    pl_noise = torch.randn(c["batch"] // 2, 1, c["res"], c["res"], c["res"],
+                           generator=torch.Generator().manual_seed(8)).to(device)
+    lG, _ = loss.step_G(0, torch.from_numpy(gold["z2"]).to(device), pl_noise=pl_noise)
+    np.testing.assert_allclose(lG.item(), float(gold["G_loss"]), rtol=10 * tol)
+    np.testing.assert_allclose(loss.pl_mean.item(), float(gold["pl_mean"]), rtol=100 * tol)
+    _check_grads(G.named_parameters(), gold, "ggrad.", 20 * tol)
+
+
+def test_product_host_logic_on_oracle_library(oracle_path):
+    code = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r); sys.path.insert(0, %r)
+from b200conv3d import _lib
+_lib.use_library(%r, host=True)
+import test_stylegan_net as T
+T.product_vs_golden(np.load(T.GOLD), "cpu", 1e-4)
+print("HOST-OK")
+''' % (os.path.join(ROOT, "3d-gan_b200"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests"), oracle_path)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=900)
+    assert "HOST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+# ------------------------------------------------------------------ GPU
+@pytest.mark.gpu
+def test_gpu_stylegan2_reference_golden_fp32():
+    product_vs_golden(np.load(GOLD), "cuda", 1e-4)
+
+
+@pytest.mark.gpu
+def test_gpu_stylegan1_reference_golden_fp32():
+    import b200conv3d as B
+    gold = np.load(GOLD)
+    torch.manual_seed(int(gold["v1_seed"]))
+    g1 = B.stylegan.styleGAN_gen(argparse.Namespace(z_size=512)).cuda()
+    _v1_check(g1, gold, "cuda", 2e-4)
+
+
+@pytest.mark.gpu
+def test_gpu_stylegan1_bf16_vs_golden():
+    """The v1-like generator at its hard-coded widths (512..16 channels, 128^3) in bf16 on the
+    tcgen05 path against the reference's fp32 output; witness: stock torch layers under bf16 autocast."""
+    import b200conv3d as B
+    gold = np.load(GOLD)
+    torch.manual_seed(int(gold["v1_seed"]))
+    g1 = B.stylegan.styleGAN_gen(argparse.Namespace(z_size=512)).cuda().eval()
+    wit = R.StyleGen1().cuda().eval()
+    wit.load_state_dict(g1.state_dict())
+    z1 = torch.from_numpy(gold["v1_z"]).cuda()
+    ref = torch.from_numpy(gold["v1_eval"])
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        y = g1(z1)[:, 0, ::8, ::8, ::8].float().cpu()
+        yw = wit(z1)[:, 0, ::8, ::8, ::8].float().cpu()
+    e, ew = ((y - ref).norm() / ref.norm()).item(), ((yw - ref).norm() / ref.norm()).item()
+    assert e < max(4e-2, 1.5 * ew), (e, ew)
+
+
+@pytest.mark.gpu
+def test_gpu_stylegan2_tensor_core_vs_oracle_bf16():
+    """channel_base 2048 at 64^3 (512..32 channels): every body conv takes the tcgen05 path.  bf16
+    product against the fp32 CPU oracle on the same weights: image, logits and the parameter
+    gradients of the two non-saturating losses (relative L2, bounded by the stock-torch bf16 witness)."""
+    import b200conv3d as B
+    res, cb, wd, zd, n = 64, 2048, 64, 32, 4
+    p = argparse.Namespace(z_size=zd, filterG=cb, filterD=cb, device="cuda", stylegan2=True, stylegan=False)
+    torch.manual_seed(3)
+    oD, oG = R.Discriminator(cb, img_resolution=res), R.Generator(zd, cb, w_dim=wd, img_resolution=res)
+    D, G = B.stylegan.Discriminator(p, img_resolution=res), B.stylegan.Generator(p, w_dim=wd, img_resolution=res)
+    _set_noise_strength(oG)
+    G.load_state_dict(oG.state_dict()), D.load_state_dict(oD.state_dict())
+    G, D = G.cuda(), D.cuda()
+    z = torch.randn(n, zd, 1, 1, 1)
+    real = torch.rand(n, 1, res, res, res) * 2 - 1
+
+    def run(g, d, dev, amp):
+        for q in list(g.parameters()) + list(d.parameters()):
+            q.grad = None
+        ctx = torch.autocast("cuda", dtype=torch.bfloat16) if amp else torch.autocast("cuda", enabled=False)
+        with ctx:
+            img, _ = g(z.to(dev), noise_mode="const")
+            lf, lr = d(img), d(real.to(dev))
+            (torch.nn.functional.softplus(lf.float()).mean() + torch.nn.functional.softplus(-lr.float()).mean()).backward()
+        grads = {"G." + k: q.grad for k, q in g.named_parameters()}
+        grads.update({"D." + k: q.grad for k, q in d.named_parameters()})
+        return img.detach().float().cpu(), lr.detach().float().cpu(), {k: v.float().cpu() for k, v in grads.items() if v is not None}
+
+    img0, lr0, g0 = run(oG, oD, "cpu", False)
+    img1, lr1, g1 = run(G, D, "cuda", True)
+    imgw, lrw, gw = run(oG.cuda(), oD.cuda(), "cuda", True)
+    l2 = lambda a, b: ((a - b).norm() / b.norm().clamp_min(1e-30)).item()   # noqa: E731
+    assert l2(img1, img0) < max(4e-2, 1.5 * l2(imgw, img0)), (l2(img1, img0), l2(imgw, img0))
+    assert l2(lr1, lr0) < max(4e-2, 1.5 * l2(lrw, lr0)), (l2(lr1, lr0), l2(lrw, lr0))
+    assert set(g1) == set(g0)
+    worst = max((l2(g1[k], g0[k]) / max(4e-2, 1.5 * l2(gw[k], g0[k])), k) for k in g0 if g0[k].norm() > 0)
+    assert worst[0] < 1.0, worst
