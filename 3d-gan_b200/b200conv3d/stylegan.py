@@ -375,12 +375,25 @@ class DiscriminatorEpilogue(tnn.Module):
         self.fc = FullyConnectedLayer(in_channels * (resolution ** 3), in_channels, activation=activation)
         self.out = FullyConnectedLayer(in_channels, 1)
 
+    def _conv_padded(self, x):
+        """`in_channels + 1` (513) input channels have no 16-byte channel vectors: zero-pad the
+        activation and the filter to the next multiple of 8 channels so the layer takes the
+        tcgen05 path (the padded taps multiply zeros; their gradient is sliced away by autograd)."""
+        extra = (-x.shape[1]) % 8
+        if extra == 0 or x.device.type != "cuda":
+            return self.conv(x)
+        c = self.conv
+        x = torch.cat([x, x.new_zeros(x.shape[0], extra, *x.shape[2:])], dim=1)
+        w = F.pad(c.weight * c.weight_gain, (0, 0, 0, 0, 0, 0, 0, extra))
+        return SO.conv3d_resample(x=x, w=w, f=c.resample_filter, up=c.up, down=c.down, padding=c.padding,
+                                  flip_weight=(c.up == 1), bias=c.bias, act=c.activation)
+
     def forward(self, x, img, force_fp32=False):
         if self.architecture == "skip":
             x = x + self.fromrgb(img)
         if self.mbstd is not None:
             x = self.mbstd(x)
-        x = self.conv(x)
+        x = self._conv_padded(x)
         x = self.fc(x.flatten(1).float())
         return self.out(x)
 

@@ -35,6 +35,12 @@ __device__ __forceinline__ void fir_st(T* p, float* o) {
   if (VEC > 1) { Vec<T> v; v.pack(o); v.store(p); } else stf(p, 0, o[0]);
 }
 
+// smallest k >= 0 with k == v (mod m)
+__device__ __forceinline__ int first_tap(int v, int m) {
+  const int r = v % m;
+  return r < 0 ? r + m : r;
+}
+
 // generic forward: one thread per (output voxel, channel vector)
 template <typename T, int VEC>
 __global__ void __launch_bounds__(kThr) fir_fwd_kernel(const __grid_constant__ FirP P, const T* __restrict__ x,
@@ -52,16 +58,19 @@ __global__ void __launch_bounds__(kThr) fir_fwd_kernel(const __grid_constant__ F
   float acc[VEC];
 #pragma unroll
   for (int i = 0; i < VEC; i++) acc[i] = 0.f;
-  for (int a = 0; a < P.kd; a++) {
+  // only taps with (o*down + k - pad) % up == 0 touch a real sample: start at that residue, step by up
+  const int a0 = first_tap(P.pad[0] - od * P.down, P.up), b0 = first_tap(P.pad[1] - oh * P.down, P.up),
+            e0 = first_tap(P.pad[2] - ow * P.down, P.up);
+  for (int a = a0; a < P.kd; a += P.up) {
     const int jd = od * P.down + a - P.pad[0];
-    if (jd < 0 || jd >= P.id * P.up || jd % P.up) continue;
-    for (int b = 0; b < P.kh; b++) {
+    if (jd < 0 || jd >= P.id * P.up) continue;
+    for (int b = b0; b < P.kh; b += P.up) {
       const int jh = oh * P.down + b - P.pad[1];
-      if (jh < 0 || jh >= P.ih * P.up || jh % P.up) continue;
+      if (jh < 0 || jh >= P.ih * P.up) continue;
       const T* row = x + ((n * P.id + jd / P.up) * P.ih + jh / P.up) * (int64_t)P.iw * P.c + c;
-      for (int e = 0; e < P.kw; e++) {
+      for (int e = e0; e < P.kw; e += P.up) {
         const int jw = ow * P.down + e - P.pad[2];
-        if (jw < 0 || jw >= P.iw * P.up || jw % P.up) continue;
+        if (jw < 0 || jw >= P.iw * P.up) continue;
         float t[VEC];
         fir_ld<T, VEC>(row + (int64_t)(jw / P.up) * P.c, t);
         const float fk = P.f[(a * P.kh + b) * P.kw + e];
@@ -90,16 +99,19 @@ __global__ void __launch_bounds__(kThr) fir_bwd_kernel(const __grid_constant__ F
   float acc[VEC];
 #pragma unroll
   for (int i = 0; i < VEC; i++) acc[i] = 0.f;
-  for (int a = 0; a < P.kd; a++) {
+  // only taps with (i*up + pad - k) % down == 0 reach an output: start at that residue, step by down
+  const int a0 = first_tap(id * P.up + P.pad[0], P.down), b0 = first_tap(ih * P.up + P.pad[1], P.down),
+            e0 = first_tap(iw * P.up + P.pad[2], P.down);
+  for (int a = a0; a < P.kd; a += P.down) {
     const int td = id * P.up + P.pad[0] - a;
-    if (td < 0 || td % P.down || td / P.down >= P.od) continue;
-    for (int b = 0; b < P.kh; b++) {
+    if (td < 0 || td / P.down >= P.od) continue;
+    for (int b = b0; b < P.kh; b += P.down) {
       const int th = ih * P.up + P.pad[1] - b;
-      if (th < 0 || th % P.down || th / P.down >= P.oh) continue;
+      if (th < 0 || th / P.down >= P.oh) continue;
       const T* row = dy + ((n * P.od + td / P.down) * P.oh + th / P.down) * (int64_t)P.ow * P.c + c;
-      for (int e = 0; e < P.kw; e++) {
+      for (int e = e0; e < P.kw; e += P.down) {
         const int tw = iw * P.up + P.pad[2] - e;
-        if (tw < 0 || tw % P.down || tw / P.down >= P.ow) continue;
+        if (tw < 0 || tw / P.down >= P.ow) continue;
         float t[VEC];
         fir_ld<T, VEC>(row + (int64_t)(tw / P.down) * P.c, t);
         const float fk = P.f[(a * P.kh + b) * P.kw + e];
@@ -168,6 +180,122 @@ __global__ void __launch_bounds__(kThr) fir_fwd_w4_kernel(const __grid_constant_
     if (ow0 + q < P.ow) fir_st<T, VEC>(dst + (int64_t)q * P.c, acc[q]);
 }
 
+
+// up = down = 1, 4x4x4 rank-1 filter f[a][b][e] = fd[a] * fh[b] * fw[e] (the reference's [1,3,3,1]-derived
+// filter is one: constant along d, stylegan.py:462-465).  A thread owns WB = 2 adjacent outputs along w of
+// one channel vector and marches along d over DCH outputs: every input plane is filtered along w and h in
+// registers once (4 lines x 5 loads, 4 + 4 taps) and scattered into a rolling window of 4 output
+// accumulators along d: 12 multiply-adds per output instead of 64, 10 loads per output instead of 28.
+struct FirSep { float fd[4], fh[4], fw[4]; int dch; };
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ FirP P, const __grid_constant__ FirSep S,
+                                                        const T* __restrict__ x, T* __restrict__ y, int64_t total) {
+  constexpr int WB = 2, K = 4;
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = P.c / VEC;
+  const int c = (int)(idx % cv) * VEC;
+  int64_t v = idx / cv;
+  const int wblocks = (P.ow + WB - 1) / WB;
+  const int ow0 = (int)(v % wblocks) * WB; v /= wblocks;
+  const int oh = (int)(v % P.oh); v /= P.oh;
+  const int dchunks = (P.od + S.dch - 1) / S.dch;
+  const int od0 = (int)(v % dchunks) * S.dch;
+  const int64_t n = v / dchunks;
+  const int nout = min(S.dch, P.od - od0);
+  float acc[K][WB][VEC];
+#pragma unroll
+  for (int s = 0; s < K; s++)
+#pragma unroll
+    for (int q = 0; q < WB; q++)
+#pragma unroll
+      for (int i = 0; i < VEC; i++) acc[s][q][i] = 0.f;
+  T* dst = y + (((n * P.od + od0) * P.oh + oh) * (int64_t)P.ow + ow0) * P.c + c;
+  const int64_t dst_plane = (int64_t)P.oh * P.ow * P.c;
+  for (int base = 0; base < nout + K - 1; base += K) {
+#pragma unroll
+    for (int s = 0; s < K; s++) {
+      const int r = base + s;                       // plane index relative to the chunk
+      const int jd = od0 + r - P.pad[0];
+      if (r < nout + K - 1 && jd >= 0 && jd < P.id) {
+        float p[WB][VEC];
+#pragma unroll
+        for (int q = 0; q < WB; q++)
+#pragma unroll
+          for (int i = 0; i < VEC; i++) p[q][i] = 0.f;
+#pragma unroll
+        for (int b = 0; b < K; b++) {
+          const int jh = oh + b - P.pad[1];
+          if (jh < 0 || jh >= P.ih) continue;
+          const T* row = x + ((n * P.id + jd) * P.ih + jh) * (int64_t)P.iw * P.c + c;
+          float in[WB + K - 1][VEC];
+#pragma unroll
+          for (int j = 0; j < WB + K - 1; j++) {
+            const int jw = ow0 + j - P.pad[2];
+            if (jw >= 0 && jw < P.iw) fir_ld<T, VEC>(row + (int64_t)jw * P.c, in[j]);
+            else {
+#pragma unroll
+              for (int i = 0; i < VEC; i++) in[j][i] = 0.f;
+            }
+          }
+          const float hb = S.fh[b];
+#pragma unroll
+          for (int q = 0; q < WB; q++)
+#pragma unroll
+            for (int i = 0; i < VEC; i++) {
+              float t = S.fw[0] * in[q][i];
+              t = fmaf(S.fw[1], in[q + 1][i], t);
+              t = fmaf(S.fw[2], in[q + 2][i], t);
+              t = fmaf(S.fw[3], in[q + 3][i], t);
+              p[q][i] = fmaf(hb, t, p[q][i]);
+            }
+        }
+        // plane r feeds outputs o = r - a (a = tap along d); output o lives in slot o % K
+#pragma unroll
+        for (int a = 0; a < K; a++) {
+          const float da = S.fd[a];
+#pragma unroll
+          for (int q = 0; q < WB; q++)
+#pragma unroll
+            for (int i = 0; i < VEC; i++) acc[(s - a + K) % K][q][i] = fmaf(da, p[q][i], acc[(s - a + K) % K][q][i]);
+        }
+      }
+      // output o = r - (K - 1) is complete: its slot is (s + 1) % K
+      const int o = r - (K - 1);
+      if (o >= 0 && o < nout) {
+#pragma unroll
+        for (int q = 0; q < WB; q++)
+          if (ow0 + q < P.ow) fir_st<T, VEC>(dst + o * dst_plane + (int64_t)q * P.c, acc[(s + 1) % K][q]);
+      }
+#pragma unroll
+      for (int q = 0; q < WB; q++)
+#pragma unroll
+        for (int i = 0; i < VEC; i++) acc[(s + 1) % K][q][i] = 0.f;
+    }
+  }
+}
+
+// f[a][b][e] == fd[a] * fh[b] * fw[e]?  (host; 64 taps)
+bool factor_rank1(const float* f, FirSep* S) {
+  int pa = 0, pb = 0, pe = 0;
+  float best = 0.f;
+  for (int t = 0; t < 64; t++)
+    if (fabsf(f[t]) > best) { best = fabsf(f[t]); pa = t / 16; pb = (t / 4) % 4; pe = t % 4; }
+  if (best == 0.f) return false;
+  const float piv = f[(pa * 4 + pb) * 4 + pe];
+  for (int k = 0; k < 4; k++) {
+    S->fd[k] = f[(k * 4 + pb) * 4 + pe] / piv;
+    S->fh[k] = f[(pa * 4 + k) * 4 + pe] / piv;
+    S->fw[k] = f[(pa * 4 + pb) * 4 + k];
+  }
+  for (int a = 0; a < 4; a++)
+    for (int b = 0; b < 4; b++)
+      for (int e = 0; e < 4; e++)
+        if (fabsf(S->fd[a] * S->fh[b] * S->fw[e] - f[(a * 4 + b) * 4 + e]) > 1e-6f * best) return false;
+  return true;
+}
+
 template <typename T>
 int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
   constexpr int V = Vec<T>::N;
@@ -182,6 +310,16 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
       Q.pad[0] = P.kd - 1 - P.pad[0]; Q.pad[1] = P.kh - 1 - P.pad[1]; Q.pad[2] = P.kw - 1 - P.pad[2];
       const int T_ = P.kd * P.kh * P.kw;
       for (int t = 0; t < T_; t++) Q.f[t] = P.f[T_ - 1 - t];
+    }
+    FirSep S;
+    if (Q.kd == 4 && Q.kh == 4 && Q.kw == 4 && factor_rank1(Q.f, &S)) {
+      S.dch = Q.od >= 64 ? 32 : 16;
+      const int64_t tot = Q.n * ((Q.od + S.dch - 1) / S.dch) * Q.oh * ((Q.ow + 1) / 2) * cvn;
+      if (tot == 0) return B2C_OK;
+      const int64_t blk = cdiv(tot, (int64_t)kThr);
+      if (blk > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+      fir_sep_kernel<T, V><<<(unsigned)blk, kThr, 0, st>>>(Q, S, ap, bp, tot);
+      return launched();
     }
     const int64_t total = Q.n * Q.od * Q.oh * ((Q.ow + 3) / 4) * cvn;
     if (total == 0) return B2C_OK;

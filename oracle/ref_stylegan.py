@@ -245,7 +245,7 @@ class StyleGen1(nn.Module):
         mix = self.mixing and self.training
         swap = torch.randint(6, (1, 1, 1)).item() if mix else -1
         w = self.latentMapping(z.squeeze())
-        h = adain(torch.ones(z.shape[0], 512, 4, 4, 4, dtype=z.dtype), self.A1(w))
+        h = adain(torch.ones(z.shape[0], 512, 4, 4, 4, dtype=z.dtype, device=z.device), self.A1(w))
         point = 0
         for i in range(1, 11):
             h = getattr(self, "C%d" % i)(h)

@@ -116,3 +116,43 @@ def test_gpu_fir_vs_reference_golden(dtype):
         rhs = (x.detach().float() * x.grad.float()).sum().item()
         scale = (y.detach().float().norm() * g.float().norm()).item()       # Cauchy-Schwarz bound of either side
         assert abs(lhs - rhs) < (1e-5 if dtype == torch.float32 else 1e-2) * scale, (name, lhs, rhs, scale)
+
+
+FIR_SHAPES = (
+    # name, (n, c, d, h, w), kwargs of upfirdn3d  -- ragged extents: odd w, d not a multiple of the 16 / 32 chunk
+    ("unit_up_conv", (2, 32, 33, 17, 19), dict(padding=[1, 1, 1, 1, 1, 1], gain=4)),        # after an up conv (:281)
+    ("unit_pre_down", (1, 16, 70, 12, 9), dict(padding=[2, 2, 2, 2, 2, 2])),               # before a stride-2 conv (:258)
+    ("unit_crop", (2, 8, 21, 10, 11), dict(padding=[-1, -1, -1, -1, -1, -1])),
+    ("unit_odd_channels", (1, 3, 9, 8, 7), dict(padding=[2, 1, 2, 1, 2, 1])),
+    ("decimate", (2, 16, 18, 14, 10), dict(down=2, padding=[1, 1, 1, 1, 1, 1])),             # skip path (:246)
+    ("zero_insert", (2, 8, 6, 5, 7), dict(up=2, padding=[2, 1, 2, 1, 2, 1], gain=8)),        # image up-sampling (:634)
+    ("zero_insert_1ch", (2, 1, 8, 8, 8), dict(up=2, padding=[2, 1, 2, 1, 2, 1], gain=8)),
+)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("case", FIR_SHAPES, ids=[c[0] for c in FIR_SHAPES])
+def test_gpu_fir_vs_oracle_ragged(case, dtype):
+    """Every FIR kernel variant (separable sliding window, w4, generic with strided taps, adjoints)
+    against the pinned torch restatement of `_upfirdn3d_ref` on ragged shapes, forward and gradient.
+    A second, non-separable filter sends the unit-rate cases through the non-separable kernel."""
+    import b200conv3d.functional as BF
+    name, shape, kw = case
+    g = torch.Generator().manual_seed(sum(map(ord, name)))
+    x = torch.randn(*shape, generator=g)
+    f_sep = O.make_filter()
+    f_full = f_sep + 0.05 * torch.rand(4, 4, 4, generator=g)
+    for f in (f_sep, f_full):
+        xr = x.clone().requires_grad_(True)
+        p = kw["padding"]
+        yr = O.upfirdn3d(xr, f, up=kw.get("up", 1), down=kw.get("down", 1), pad=(p[0], p[1]), gain=kw.get("gain", 1))
+        gy = torch.randn(*yr.shape, generator=g)
+        yr.backward(gy)
+        xg = x.cuda().to(dtype).requires_grad_(True)
+        y = BF.upfirdn3d(xg, f, **kw)
+        y.backward(gy.cuda().to(dtype))
+        tol = 1e-5 if dtype == torch.float32 else 2e-2
+        assert y.shape == yr.shape
+        assert ((y.float().cpu() - yr.detach()).abs().max() / yr.abs().max()).item() < tol, name
+        assert ((xg.grad.float().cpu() - xr.grad).abs().max() / xr.grad.abs().max()).item() < tol, name
