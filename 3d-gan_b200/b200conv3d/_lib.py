@@ -82,6 +82,12 @@ _SIGNATURES = {
     "b2c_avgpool2_bwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_fir3d_fwd": (_i32, [C.POINTER(FirDesc), C.POINTER(C.c_float), _vp, _vp, _vp]),
     "b2c_fir3d_bwd": (_i32, [C.POINTER(FirDesc), C.POINTER(C.c_float), _vp, _vp, _vp]),
+    "b2c_mod_workspace": (_sz, [_i64, _i64, _i64]),
+    "b2c_modulate_fwd": (_i32, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp]),
+    "b2c_modulate_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp, _sz, _vp]),
+    "b2c_mod_epilogue_fwd": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _f32, _vp]),
+    "b2c_mod_epilogue_bwd": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32,
+                                    _f32, _vp, _sz, _vp]),
 }
 EXPORTS = tuple(_SIGNATURES)
 

@@ -766,3 +766,120 @@ def upfirdn3d(x, f, up=1, down=1, padding=0, flip_filter=False, gain=1):
             raise ValueError("upfirdn3d: empty output")
         out_sp.append(-(-full // down))
     return _FirFn.apply(x, taps, k, int(up), int(down), lo, tuple(out_sp))
+
+
+# --------------------------------------------------------------- style modulation glue (NDHWC)
+def mod_supported(c, dtype):
+    """b2c_modulate_* / b2c_mod_epilogue_* take whole 16-byte channel vectors, at most 256 of them."""
+    vec = 8 if dtype == torch.bfloat16 else 4
+    return c % vec == 0 and c // vec <= 256
+
+
+def _f32c(t):
+    return None if t is None else t.detach().to(torch.float32).contiguous()
+
+
+class _ModulateFn(Function):
+    """xs = x * s[n, c]  (stylegan.py:427); backward: dx = g * s, ds[n,c] = sum_v g * x, one pass."""
+
+    @staticmethod
+    def forward(ctx, x, s):
+        _check_device(x)
+        cd = compute_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, c = xb.shape
+        sf = _f32c(s).reshape(n, c)
+        yl, y = alloc_out(n, d, h, w, c, cd, x.device)
+        with _dev(x):
+            check(_lib.lib().b2c_modulate_fwd(_ptr(xb), _ptr(sf), _ptr(y), n, d * h * w, c, _dt(cd), _stream(x)),
+                  "modulate_fwd")
+        ctx.save_for_backward(xb, sf)
+        ctx.x_dtype, ctx.s_dtype, ctx.s_shape, ctx.cd = x.dtype, s.dtype, s.shape, cd
+        return yl
+
+    @staticmethod
+    def backward(ctx, gy):
+        xb, sf = ctx.saved_tensors
+        n, d, h, w, c = xb.shape
+        g = to_ndhwc(gy, ctx.cd)
+        dxl, dx = alloc_out(n, d, h, w, c, ctx.cd, gy.device)
+        ds = torch.empty(n, c, dtype=torch.float32, device=gy.device)
+        L = _lib.lib()
+        ws = _ws(L.b2c_mod_workspace(n, d * h * w, c), gy)
+        with _dev(gy):
+            check(L.b2c_modulate_bwd(_ptr(xb), _ptr(g), _ptr(sf), _ptr(dx), _ptr(ds), n, d * h * w, c, _dt(ctx.cd),
+                                     _ptr(ws), ws.numel(), _stream(gy)), "modulate_bwd")
+        return (dxl if ctx.x_dtype == ctx.cd else dxl.to(ctx.x_dtype)), ds.reshape(ctx.s_shape).to(ctx.s_dtype)
+
+
+def modulate(x, s):
+    """x [N,C,D,H,W] * s [N,C] broadcast over the voxels; one NDHWC pass each way."""
+    return _ModulateFn.apply(x, s)
+
+
+class _ModEpilogueFn(Function):
+    """out = act(y * d[n,c] + strength * field[n|0, v] + bias[c])  (stylegan.py:429-432, 522-524, 531);
+    backward: dy = g * d, dd[n,c] = sum_v g * y, dbias[c] = sum g, dstrength = sum g * field with
+    g = gout * act'(out) - one pass over (y, out, gout) instead of a dozen ATen passes."""
+
+    @staticmethod
+    def forward(ctx, y, d, field, strength, bias, act, slope):
+        _check_device(y)
+        cd = compute_dtype(y)
+        yb = to_ndhwc(y.detach(), cd)
+        n, dd_, h, w, c = yb.shape
+        v = dd_ * h * w
+        df, bf = _f32c(d), _f32c(bias)
+        ff = sf = None
+        fn = 0
+        if field is not None:
+            ff = _f32c(field).reshape(-1, v)
+            fn = ff.shape[0]
+            if fn not in (1, n):
+                raise ValueError("noise field batch must be 1 or N")
+            sf = _f32c(strength).reshape(1)
+        outl, out = alloc_out(n, dd_, h, w, c, cd, y.device)
+        with _dev(y):
+            check(_lib.lib().b2c_mod_epilogue_fwd(_ptr(yb), _ptr(df), _ptr(ff), fn, _ptr(sf), _ptr(bf), _ptr(out), n, v,
+                                                  c, _dt(cd), int(act), float(slope), _stream(y)), "mod_epilogue_fwd")
+        need_y = d is not None and ctx.needs_input_grad[1]
+        ctx.save_for_backward(yb if need_y else None, out, df, ff)
+        ctx.meta = (cd, y.dtype, int(act), float(slope), fn,
+                    None if d is None else (d.shape, d.dtype),
+                    None if strength is None else (strength.shape, strength.dtype),
+                    None if bias is None else bias.dtype)
+        return outl
+
+    @staticmethod
+    def backward(ctx, gout):
+        yb, out, df, ff = ctx.saved_tensors
+        cd, y_dtype, act, slope, fn, dmeta, smeta, bdtype = ctx.meta
+        n, d_, h, w, c = out.shape
+        v = d_ * h * w
+        g = to_ndhwc(gout, cd)
+        dyl, dy = alloc_out(n, d_, h, w, c, cd, gout.device)
+        dev = gout.device
+        want_d = yb is not None
+        want_b = bdtype is not None and ctx.needs_input_grad[4]
+        want_s = ff is not None and smeta is not None and ctx.needs_input_grad[3]
+        dd = torch.empty(n, c, dtype=torch.float32, device=dev) if want_d else None
+        db = torch.empty(c, dtype=torch.float32, device=dev) if want_b else None
+        dst = torch.empty(1, dtype=torch.float32, device=dev) if want_s else None
+        L = _lib.lib()
+        ws = _ws(L.b2c_mod_workspace(n, v, c), gout)
+        with _dev(gout):
+            check(L.b2c_mod_epilogue_bwd(_ptr(yb), _ptr(out), _ptr(g), _ptr(df), _ptr(ff), fn, _ptr(dy), _ptr(dd),
+                                         _ptr(db), _ptr(dst), n, v, c, _dt(cd), act, slope, _ptr(ws), ws.numel(),
+                                         _stream(gout)), "mod_epilogue_bwd")
+        return ((dyl if y_dtype == cd else dyl.to(y_dtype)),
+                None if dd is None else dd.reshape(dmeta[0]).to(dmeta[1]),
+                None,
+                None if dst is None else dst.reshape(smeta[0]).to(smeta[1]),
+                None if db is None else db.to(bdtype),
+                None, None)
+
+
+def mod_epilogue(y, d=None, field=None, strength=None, bias=None, act=None, slope=0.0):
+    """y [N,C,D,H,W]; d [N,C] or None; field [N|1, 1, D,H,W] (or anything of N*V / V elements) with its
+    scalar `strength` (a tensor), or None; bias [C] or None."""
+    return _ModEpilogueFn.apply(y, d, field, strength, bias, _act_id(act), slope)

@@ -160,16 +160,15 @@ class SynthesisLayer(tnn.Module):
         """`noise` (extension, used by the parity tests): an explicit [N,1,R,R,R] N(0,1) field that
         replaces the `torch.randn` draw of noise_mode='random' (stylegan.py:522)."""
         styles = self.affine(w)
-        nz = None
+        field = None
         r = self.resolution
         if self.use_noise and noise_mode == "random":
-            if noise is None:
-                noise = torch.randn([x.shape[0], 1, r, r, r], device=x.device)
-            nz = noise * self.noise_strength
+            field = noise if noise is not None else torch.randn([x.shape[0], 1, r, r, r], device=x.device)
         if self.use_noise and noise_mode == "const":
-            nz = self.noise_const * self.noise_strength
-        return SO.synthesis_conv(x, self.weight, styles, nz, self.bias, up=self.up, padding=self.padding,
-                                 resample_filter=self.resample_filter, act=self.activation)
+            field = self.noise_const.expand(1, 1, r, r, r)          # [R, R] broadcasts over the two last axes
+        return SO.synthesis_conv(x, self.weight, styles, field, self.noise_strength if field is not None else None,
+                                 self.bias, up=self.up, padding=self.padding, resample_filter=self.resample_filter,
+                                 act=self.activation)
 
 
 class OutBlock(tnn.Module):
@@ -184,6 +183,8 @@ class OutBlock(tnn.Module):
 
     def forward(self, x, w, fused_modconv=False):
         styles = self.affine(w) * self.weight_gain
+        if BF.mod_supported(x.shape[1], BF.compute_dtype(x)):
+            return SO.conv3d_resample(BF.modulate(x, styles), self.weight, bias=self.bias)   # bias in the epilogue
         x = SO.modulated_conv3d(x=x, weight=self.weight, styles=styles, demodulate=False, fused_modconv=False)
         return SO.bias_act(x, self.bias)
 

@@ -117,11 +117,26 @@ def modulated_conv3d(x, weight, styles, noise=None, up=1, down=1, padding=0, res
     return x + noise.to(x.dtype) if noise is not None else x
 
 
-def synthesis_conv(x, weight, styles, noise, bias, up=1, padding=1, resample_filter=None, act="lrelu"):
-    """One SynthesisLayer body (stylegan.py:526-531): modulated conv (+ noise), bias, activation."""
-    x = modulated_conv3d(x=x, weight=weight, styles=styles, noise=noise, up=up, padding=padding,
-                         resample_filter=resample_filter, flip_weight=(up == 1), fused_modconv=False)
-    return bias_act(x, bias, act=act)
+def synthesis_conv(x, weight, styles, noise_field, noise_strength, bias, up=1, padding=1, resample_filter=None,
+                   act="lrelu", demodulate=True):
+    """One SynthesisLayer / OutBlock body (stylegan.py:526-531, 542-546): modulated conv, noise
+    `noise_strength * noise_field` (field [N|1,1,R,R,R] or None), bias, activation.  The style
+    scaling is ONE prologue pass (b2c_modulate), demodulation + noise + bias + activation ONE epilogue
+    pass (b2c_mod_epilogue); the small reductions of their gradients ride in the same backward passes.
+    Falls back to the elementwise formulation when the channel count has no 16-byte vectors."""
+    cin, cout = x.shape[1], weight.shape[0]
+    cd = BF.compute_dtype(x)
+    if not (BF.mod_supported(cin, cd) and BF.mod_supported(cout, cd)):
+        nz = None if noise_field is None else noise_field * noise_strength
+        y = modulated_conv3d(x=x, weight=weight, styles=styles, noise=nz, up=up, padding=padding,
+                             resample_filter=resample_filter, demodulate=demodulate, flip_weight=(up == 1),
+                             fused_modconv=False)
+        return bias_act(y, bias, act=act)
+    dcoefs = demod_coefficients(weight, styles) if demodulate else None
+    xs = BF.modulate(x, styles)
+    y = conv3d_resample(xs, weight, f=resample_filter, up=up, padding=padding, flip_weight=(up == 1))
+    a, slope = _ACT[act]
+    return BF.mod_epilogue(y, dcoefs, noise_field, noise_strength, bias, act=a, slope=slope)
 
 
 def bias_act(x, b=None, dim=1, act="linear"):

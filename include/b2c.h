@@ -231,6 +231,35 @@ int b2c_fir3d_fwd(const b2c_fir_desc*, const float* taps, const void* x,
 int b2c_fir3d_bwd(const b2c_fir_desc*, const float* taps, const void* dy,
                   void* dx, b2c_stream);
 
+/* ---- style modulation glue (stylegan.py:396-444 `modulated_conv3d`, live --- *
+ * branch, + the bias_act of the calling layer, stylegan.py:522-531) --------- *
+ * x, y, out [N, V, C] dense NDHWC (V = D*H*W voxels), bf16 or fp32.            *
+ *   modulate:  y   = x * s[n,c]                         (stylegan.py:427)      *
+ *   epilogue:  out = act(y * d[n,c] + *strength * field[n|0, v] + bias[c])     *
+ *              (demodulation :429-432, noise :522-524, bias_act :531)          *
+ * s, d [N,C] fp32; d may be NULL (demodulate=False); field [field_n, V] fp32   *
+ * with field_n = N or 1 (broadcast over the batch) or NULL; strength a DEVICE  *
+ * scalar; bias [C] fp32 or NULL.  The backward passes also produce the small   *
+ * reductions: ds[n,c] = sum_v gy*x;  dd[n,c] = sum_v g*y, dbias[c] = sum g,    *
+ * dstrength = sum g*field  with g = gout * act'(out)  (deterministic order).   *
+ * C must be a multiple of the 16-byte vector (8 bf16 / 4 fp32) and <= 2048 bf16*
+ * / 1024 fp32, else B2C_ERR_UNSUPPORTED.  Workspace: b2c_mod_workspace bytes.  */
+size_t b2c_mod_workspace(int64_t N, int64_t V, int64_t C);
+int b2c_modulate_fwd(const void* x, const float* s, void* y, int64_t N,
+                     int64_t V, int64_t C, int dtype, b2c_stream);
+int b2c_modulate_bwd(const void* x, const void* gy, const float* s, void* dx,
+                     float* ds, int64_t N, int64_t V, int64_t C, int dtype,
+                     void* ws, size_t ws_bytes, b2c_stream);
+int b2c_mod_epilogue_fwd(const void* y, const float* d, const float* field,
+                         int64_t field_n, const float* strength,
+                         const float* bias, void* out, int64_t N, int64_t V,
+                         int64_t C, int dtype, int act, float slope, b2c_stream);
+int b2c_mod_epilogue_bwd(const void* y, const void* out, const void* gout,
+                         const float* d, const float* field, int64_t field_n,
+                         void* dy, float* dd, float* dbias, float* dstrength,
+                         int64_t N, int64_t V, int64_t C, int dtype, int act,
+                         float slope, void* ws, size_t ws_bytes, b2c_stream);
+
 #ifdef __cplusplus
 }
 #endif

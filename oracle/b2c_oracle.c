@@ -599,3 +599,88 @@ int b2c_fir3d_bwd(const b2c_fir_desc* d, const float* taps, const void* dy, void
           }
   return B2C_OK;
 }
+
+/* ---- style modulation glue (stylegan.py:396-444 live branch + bias_act, :522-531) ---------- */
+size_t b2c_mod_workspace(int64_t N, int64_t V, int64_t C) { (void)N; (void)V; (void)C; return 16; }
+
+int b2c_modulate_fwd(const void* x, const float* sc, void* y, int64_t N, int64_t V, int64_t C, int dt, b2c_stream s) {
+  (void)s;
+  if (!x || !sc || !y || !dt_ok(dt)) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < N; n++)
+    for (int64_t v = 0; v < V; v++)
+      for (int64_t c = 0; c < C; c++) {
+        int64_t i = (n * V + v) * C + c;
+        st(y, i, dt, ld(x, i, dt) * (double)sc[n * C + c]);          /* stylegan.py:427 */
+      }
+  return B2C_OK;
+}
+
+int b2c_modulate_bwd(const void* x, const void* gy, const float* sc, void* dx, float* ds, int64_t N, int64_t V,
+                     int64_t C, int dt, void* ws, size_t wsb, b2c_stream s) {
+  (void)s; (void)ws; (void)wsb;
+  if (!x || !gy || !sc || !dx || !ds || !dt_ok(dt)) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < N; n++)
+    for (int64_t c = 0; c < C; c++) {
+      double acc = 0.0;
+      for (int64_t v = 0; v < V; v++) {
+        int64_t i = (n * V + v) * C + c;
+        double g = ld(gy, i, dt);
+        acc += g * ld(x, i, dt);
+        st(dx, i, dt, g * (double)sc[n * C + c]);
+      }
+      ds[n * C + c] = (float)acc;
+    }
+  return B2C_OK;
+}
+
+int b2c_mod_epilogue_fwd(const void* y, const float* d, const float* field, int64_t field_n, const float* strength,
+                         const float* bias, void* out, int64_t N, int64_t V, int64_t C, int dt, int act, float slope,
+                         b2c_stream s) {
+  (void)s;
+  if (!y || !out || !dt_ok(dt) || (field && (!strength || (field_n != 1 && field_n != N)))) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < N; n++)
+    for (int64_t v = 0; v < V; v++) {
+      double nz = field ? (double)*strength * (double)field[(field_n > 1 ? n * V : 0) + v] : 0.0;   /* :522-524 */
+      for (int64_t c = 0; c < C; c++) {
+        int64_t i = (n * V + v) * C + c;
+        double z = ld(y, i, dt) * (d ? (double)d[n * C + c] : 1.0) + nz + (bias ? (double)bias[c] : 0.0);   /* :429-432, :531 */
+        st(out, i, dt, act_f(z, act, slope));
+      }
+    }
+  return B2C_OK;
+}
+
+int b2c_mod_epilogue_bwd(const void* y, const void* out, const void* gout, const float* d, const float* field,
+                         int64_t field_n, void* dy, float* dd, float* dbias, float* dstrength, int64_t N, int64_t V,
+                         int64_t C, int dt, int act, float slope, void* ws, size_t wsb, b2c_stream s) {
+  (void)s; (void)ws; (void)wsb;
+  if (!out || !gout || !dy || !dt_ok(dt) || (dd && (!d || !y)) || (field && field_n != 1 && field_n != N))
+    return B2C_ERR_INVALID;
+  double* accb = (double*)calloc((size_t)C, sizeof(double));
+  double accs = 0.0;
+  if (!accb) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < N; n++)
+    for (int64_t c = 0; c < C; c++) {
+      double accd = 0.0;
+      for (int64_t v = 0; v < V; v++) {
+        int64_t i = (n * V + v) * C + c;
+        double o = ld(out, i, dt), dz;
+        switch (act) {                       /* derivative from the output, as the product kernels take it */
+          case B2C_ACT_RELU:  dz = o > 0 ? 1.0 : 0.0; break;
+          case B2C_ACT_LRELU: dz = o > 0 ? 1.0 : (double)slope; break;
+          case B2C_ACT_TANH:  dz = 1.0 - o * o; break;
+          default:            dz = 1.0;
+        }
+        double g = ld(gout, i, dt) * dz;
+        accb[c] += g;
+        if (dd) accd += g * ld(y, i, dt);
+        if (field) accs += g * (double)field[(field_n > 1 ? n * V : 0) + v];
+        st(dy, i, dt, g * (d ? (double)d[n * C + c] : 1.0));
+      }
+      if (dd) dd[n * C + c] = (float)accd;
+    }
+  if (dbias) for (int64_t c = 0; c < C; c++) dbias[c] = (float)accb[c];
+  if (field && dstrength) *dstrength = (float)accs;
+  free(accb);
+  return B2C_OK;
+}

@@ -156,3 +156,70 @@ def test_gpu_fir_vs_oracle_ragged(case, dtype):
         assert y.shape == yr.shape
         assert ((y.float().cpu() - yr.detach()).abs().max() / yr.abs().max()).item() < tol, name
         assert ((xg.grad.float().cpu() - xr.grad).abs().max() / xr.grad.abs().max()).item() < tol, name
+
+
+MOD_SHAPES = ((2, 8, 5, 6, 7), (3, 32, 9, 4, 11), (2, 512, 4, 4, 4), (1, 64, 17, 3, 5))
+
+
+def check_mod_ops(dev, dtype):
+    """b2c_modulate / b2c_mod_epilogue (forward and every gradient) against the elementwise formulation of
+    stylegan.py:427-432, 522-524, 531 written with stock torch ops in fp32."""
+    import b200conv3d.functional as BF
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    err = lambda a, b: ((a.float().cpu() - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()   # noqa: E731
+    for shape in MOD_SHAPES:
+        n, c = shape[:2]
+        g = torch.Generator().manual_seed(sum(shape))
+        x = torch.randn(*shape, generator=g)
+        s = torch.randn(n, c, generator=g) * 0.5 + 1
+        gy = torch.randn(*shape, generator=g)
+        xr, sr = x.clone().requires_grad_(True), s.clone().requires_grad_(True)
+        (xr * sr.reshape(n, c, 1, 1, 1)).backward(gy)
+        xg, sg = x.clone().to(dev).to(dtype).requires_grad_(True), s.clone().to(dev).requires_grad_(True)
+        y = BF.modulate(xg, sg)
+        y.backward(gy.to(dev).to(dtype))
+        assert err(y, (x * s.reshape(n, c, 1, 1, 1))) < tol
+        assert err(xg.grad, xr.grad) < tol and err(sg.grad, sr.grad) < tol, shape
+        for demod, fn, act in ((True, n, "lrelu"), (True, 1, "lrelu"), (False, 0, None), (True, 0, "tanh")):
+            d = torch.rand(n, c, generator=g) + 0.5 if demod else None
+            field = torch.randn(fn, 1, *shape[2:], generator=g) if fn else None
+            st = torch.tensor(0.3)
+            b = torch.randn(c, generator=g) * 0.1
+            ref_in = [t.clone().requires_grad_(True) if t is not None else None for t in (x, d, st if fn else None, b)]
+            z = ref_in[0] * (ref_in[1].reshape(n, c, 1, 1, 1) if demod else 1.0)
+            if fn:
+                z = z + field * ref_in[2]
+            z = z + ref_in[3].reshape(1, c, 1, 1, 1)
+            ref = torch.nn.functional.leaky_relu(z, 0.2) if act == "lrelu" else (torch.tanh(z) if act == "tanh" else z)
+            ref.backward(gy)
+            got_in = [t.detach().clone().to(dev).requires_grad_(True) if t is not None else None
+                      for t in (x.to(dtype), d, st if fn else None, b)]
+            out = BF.mod_epilogue(got_in[0], got_in[1], None if field is None else field.to(dev), got_in[2], got_in[3],
+                                  act=act, slope=0.2)
+            out.backward(gy.to(dev).to(dtype))
+            assert err(out, ref.detach()) < tol, (shape, demod, fn, act)
+            for a, r, what in zip(got_in, ref_in, ("dy", "dd", "dstrength", "dbias")):
+                if r is not None:
+                    # bf16: the kernels take act' from the rounded OUTPUT; elements within rounding of a kink may flip
+                    lim = tol if (dtype == torch.float32 or what != "dy") else 5e-2
+                    assert err(a.grad, r.grad) < lim, (shape, demod, fn, act, what, err(a.grad, r.grad))
+
+
+def test_mod_ops_oracle_library_vs_torch(oracle_path):
+    code = r'''
+import sys, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r); sys.path.insert(0, %r)
+from b200conv3d import _lib
+_lib.use_library(%r, host=True)
+import test_stylegan_ops as T
+T.check_mod_ops("cpu", torch.float32)
+print("HOST-OK")
+''' % (os.path.join(ROOT, "3d-gan_b200"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests"), oracle_path)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert "HOST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gpu_mod_ops_vs_torch(dtype):
+    check_mod_ops("cuda", dtype)
