@@ -27,10 +27,10 @@ class _timed:
     """Bracket one C-ABI conv launch with CUDA events on its stream when bench.py has
     switched per-launch profiling on (PROFILE is a list)."""
 
-    def __init__(self, pas, desc):
+    def __init__(self, pas, desc, fold=1):
         self.on = PROFILE is not None
-        if self.on:
-            self.key = (pas, bool(desc.transposed), desc.x.n, desc.x.c, desc.x.d, desc.y.c, desc.y.d,
+        if self.on:       # W-folded launches are reported with the ORIGINAL channel counts (useful FLOPs)
+            self.key = (pas, bool(desc.transposed), desc.x.n, desc.x.c // fold, desc.x.d, desc.y.c // fold, desc.y.d,
                         desc.k[0], desc.stride[0], desc.pad[0], desc.dil[0])
 
     def __enter__(self):
@@ -169,9 +169,10 @@ def _triple(v):
 
 class Geom:
     """Static geometry of one conv / conv-transpose call."""
-    __slots__ = ("transposed", "k", "stride", "pad", "dil", "out_pad")
+    __slots__ = ("transposed", "k", "stride", "pad", "dil", "out_pad", "fold")
 
     def __init__(self, transposed, k, stride, pad, dil, out_pad=(0, 0, 0)):
+        self.fold = 1                 # W-folding factor of the launch (profiling only)
         self.transposed, self.k = bool(transposed), tuple(k)
         self.stride, self.pad, self.dil = _triple(stride), _triple(pad), _triple(dil)
         self.out_pad = _triple(out_pad)
@@ -288,7 +289,7 @@ class _ConvFn(Function):
             bf = bf if bf.dtype == torch.float32 else bf.float()
         fu = Fusion(_ptr(bf), int(act), float(slope))
         ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_FWD), x)
-        with _dev(x), _timed("fwd", desc):
+        with _dev(x), _timed("fwd", desc, g.fold):
             check(L.b2c_conv3d_fwd(C.byref(desc), _ptr(xb), _ptr(wp), _ptr(y), C.byref(fu),
                                    _ptr(ws), ws.numel(), _stream(x)), "conv3d_fwd")
         ctx.g, ctx.act, ctx.slope, ctx.cd = g, int(act), float(slope), cd
@@ -317,7 +318,7 @@ class _ConvFn(Function):
             wp = _packed_filter(w, desc, PASS_DGRAD, cd)
             dxb = torch.empty_like(xb)
             ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_DGRAD), xb)
-            with _dev(xb), _timed("dgrad", desc):
+            with _dev(xb), _timed("dgrad", desc, g.fold):
                 check(L.b2c_conv3d_dgrad(C.byref(desc), _ptr(gyb), _ptr(wp), _ptr(dxb), _ptr(ws),
                                          ws.numel(), _stream(xb)), "conv3d_dgrad")
             dx = from_ndhwc(dxb)
@@ -329,7 +330,7 @@ class _ConvFn(Function):
             dw = torch.empty(w.shape, dtype=torch.float32, device=w.device) if need_w else None
             db = torch.empty(cout, dtype=torch.float32, device=w.device) if need_b else None
             ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_WGRAD), xb)
-            with _dev(xb), _timed("wgrad", desc):
+            with _dev(xb), _timed("wgrad", desc, g.fold):
                 check(L.b2c_conv3d_wgrad(C.byref(desc), _ptr(xb), _ptr(gyb), _ptr(dw), _ptr(db),
                                          _ptr(ws), ws.numel(), _stream(xb)), "conv3d_wgrad")
             if dw is not None and w.dtype != torch.float32:
@@ -352,7 +353,89 @@ def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=
     if isinstance(padding, str):
         raise NotImplementedError("b200conv3d.conv3d: string padding %r is not supported" % padding)
     g = Geom(False, tuple(weight.shape[2:]), stride, padding, dilation)
+    fold = _fold_factor(x, weight, g)
+    if fold > 1:
+        return _conv3d_folded(x, weight, bias, g, _act_id(act), slope, fold)
     return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+
+
+# ---- W-folding of narrow stride-1 convolutions ------------------------------------------------
+# The tcgen05 conv kernel fetches one TMA row per (voxel, tap) and is bound by the NUMBER of
+# L2 -> SM row requests, not by their bytes (a 3^3 conv re-fetches every input row 27 times):
+# measured, a 32-channel row (64 B) costs the same as a 128-channel row (256 B), so 32 -> 32
+# layers at 128^3 (utils.py:57-60,105-109 hidden convs, stylegan.py conv0 / conv1 at the top
+# resolution) run at 145 TFLOP/s where 128 -> 128 layers reach 1190.  Folding F adjacent voxels
+# along W into the channel axis is FREE in NDHWC storage ([N,D,H,W,C] == [N,D,H,W/F,F*C]) and
+# turns the layer into a (F*Cin) -> (F*Cout) convolution over W/F with 3 taps along W whose
+# filter has a known block-sparsity pattern: F x fewer row requests for (at most) F x the
+# tensor-core work, which the kernel has to spare.  Weight gradients come back through the
+# (index_select) expansion: every original tap is the sum of the blocks it was copied to.
+FOLD = [True]
+
+
+def _fold_factor(x, weight, g):
+    if not FOLD[0] or g.transposed or x.dim() != 5:
+        return 1
+    cout, cin, kd, kh, kw = weight.shape
+    if g.stride != (1, 1, 1) or g.dil != (1, 1, 1) or kw % 2 == 0 or kw == 1 or g.pad[2] != kw // 2:
+        return 1
+    if cin % 8 or cout % 8 or max(cin, cout) > 32 or compute_dtype(x) != torch.bfloat16:
+        return 1
+    w = x.shape[4]
+    for f in ((4, 2) if max(cin, cout) <= 16 else (2,)):
+        if w % f == 0 and w // f >= 2 and kw // 2 <= f:
+            return f
+    return 1
+
+
+_fold_index_cache = {}
+
+
+def _fold_index(f, kw, device):
+    """idx[po, pi, t] = original tap along W that connects input voxel F*(j+t-1)+pi to output voxel
+    F*j+po (pad = kw//2), or kw (a zero slot) if there is none."""
+    key = (f, kw, str(device))
+    if key not in _fold_index_cache:
+        pad = kw // 2
+        idx = torch.full((f, f, 3), kw, dtype=torch.long)
+        for po in range(f):
+            for pi in range(f):
+                for t in range(3):
+                    k = f * (t - 1) + pi - po + pad
+                    if 0 <= k < kw:
+                        idx[po, pi, t] = k
+        _fold_index_cache[key] = idx.reshape(-1).to(device)
+    return _fold_index_cache[key]
+
+
+def fold_filter(weight, f):
+    """[Cout, Cin, kd, kh, kw] -> [F*Cout, F*Cin, kd, kh, 3] (block-sparse; differentiable)."""
+    cout, cin, kd, kh, kw = weight.shape
+    wz = torch.cat([weight, weight.new_zeros(cout, cin, kd, kh, 1)], dim=4)
+    wf = wz.index_select(4, _fold_index(f, kw, weight.device)).reshape(cout, cin, kd, kh, f, f, 3)
+    return wf.permute(4, 0, 5, 1, 2, 3, 6).reshape(f * cout, f * cin, kd, kh, 3)
+
+
+def _fold_w(x, f):
+    """logical [N,C,D,H,W] -> logical [N,F*C,D,H,W/F] over the same NDHWC storage (a view)."""
+    n, c, d, h, w = x.shape
+    p = x.permute(0, 2, 3, 4, 1)
+    if not p.is_contiguous():
+        p = p.contiguous()
+    return p.reshape(n, d, h, w // f, f * c).permute(0, 4, 1, 2, 3)
+
+
+def _unfold_w(y, f):
+    n, fc, d, h, wf = y.shape
+    return y.permute(0, 2, 3, 4, 1).reshape(n, d, h, wf * f, fc // f).permute(0, 4, 1, 2, 3)
+
+
+def _conv3d_folded(x, weight, bias, g, act, slope, f):
+    w2 = fold_filter(weight, f)
+    b2 = None if bias is None else bias.repeat(f)
+    g2 = Geom(False, tuple(w2.shape[2:]), 1, (g.pad[0], g.pad[1], 1), 1)
+    g2.fold = f
+    return _unfold_w(_ConvFn.apply(_fold_w(x, f), w2, b2, g2, act, slope), f)
 
 
 def conv_transpose3d(x, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1,

@@ -180,3 +180,41 @@ def test_device_prefetcher_order_and_values():
     assert len(got) == 5
     for i, t in enumerate(got):
         assert t.is_cuda and torch.equal(t.cpu(), host[i])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", [(32, 32, 3, 24, 2), (16, 32, 3, 20, 2), (16, 8, 3, 16, 4), (8, 16, 5, 16, 4)],
+                         ids=["32to32", "16to32", "16to8_f4", "8to16_k5_f4"])
+def test_w_folded_conv_matches_plain_and_torch(cfg):
+    """Narrow stride-1 convs run W-folded (F voxels along W folded into the channel axis, block-sparse
+    expanded filter): same results as the unfolded launch and as stock torch fp32 (bf16 2e-2), forward,
+    input gradient, weight gradient (summed back through the filter expansion) and bias gradient."""
+    import b200conv3d.functional as BF
+    cin, cout, k, w, f = cfg
+    torch.manual_seed(cin * 100 + cout)
+    x = torch.randn(2, cin, 6, 10, w, device="cuda")
+    wt = torch.randn(cout, cin, k, k, k, device="cuda") * (cin * k ** 3) ** -0.5
+    b = torch.randn(cout, device="cuda") * 0.1
+    gy = torch.randn(2, cout, 6, 10, w, device="cuda")
+    assert BF._fold_factor(x.bfloat16(), wt, BF.Geom(False, (k, k, k), 1, k // 2, 1)) == f
+
+    def run(fn, xin):
+        xx, ww, bb = xin.clone().requires_grad_(True), wt.clone().requires_grad_(True), b.clone().requires_grad_(True)
+        y = fn(xx, ww, bb)
+        y.backward(gy.to(y.dtype))
+        return [t.detach().float() for t in (y, xx.grad, ww.grad, bb.grad)]
+
+    ref = run(lambda a, c, d: torch.nn.functional.leaky_relu(torch.nn.functional.conv3d(a, c, d, padding=k // 2), 0.2), x)
+    ours = run(lambda a, c, d: BF.conv3d(a, c, d, 1, k // 2, act="lrelu", slope=0.2), x.bfloat16())
+    BF.FOLD[0] = False
+    try:
+        plain = run(lambda a, c, d: BF.conv3d(a, c, d, 1, k // 2, act="lrelu", slope=0.2), x.bfloat16())
+    finally:
+        BF.FOLD[0] = True
+    from abi import kink_robust_err, rel_err
+    for i, (o, p, r) in enumerate(zip(ours, plain, ref)):
+        if i == 1:      # input gradient through the LeakyReLU kink
+            assert kink_robust_err(o, r, 2e-2) < 2e-2
+        else:
+            assert rel_err(o, r) < 2e-2, (i, rel_err(o, r))
+        assert rel_err(o, p) < 1e-2, (i, rel_err(o, p))

@@ -291,7 +291,8 @@ def test_gpu_stylegan2_tensor_core_vs_oracle_bf16():
             (torch.nn.functional.softplus(lf.float()).mean() + torch.nn.functional.softplus(-lr.float()).mean()).backward()
         grads = {"G." + k: q.grad for k, q in g.named_parameters()}
         grads.update({"D." + k: q.grad for k, q in d.named_parameters()})
-        return img.detach().float().cpu(), lr.detach().float().cpu(), {k: v.float().cpu() for k, v in grads.items() if v is not None}
+        return (img.detach().float().cpu().clone(), lr.detach().float().cpu().clone(),
+                {k: v.detach().float().cpu().clone() for k, v in grads.items() if v is not None})
 
     img0, lr0, g0 = run(oG, oD, "cpu", False)
     img1, lr1, g1 = run(G, D, "cuda", True)
