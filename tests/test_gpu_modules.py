@@ -213,8 +213,9 @@ def test_w_folded_conv_matches_plain_and_torch(cfg):
         BF.FOLD[0] = True
     from abi import kink_robust_err, rel_err
     for i, (o, p, r) in enumerate(zip(ours, plain, ref)):
-        if i == 1:      # input gradient through the LeakyReLU kink
-            assert kink_robust_err(o, r, 2e-2) < 2e-2
-        else:
+        if i == 1:      # input gradient: every element sums k^3 * Cout terms behind a LeakyReLU kink, a few of
+            # which take the other slope in bf16 (folded or not): bounded in relative L2 against fp32 ...
+            assert ((o - r).norm() / r.norm()).item() < 2e-2
+        else:           # ... and element-wise against the unfolded bf16 launch below
             assert rel_err(o, r) < 2e-2, (i, rel_err(o, r))
         assert rel_err(o, p) < 1e-2, (i, rel_err(o, p))
