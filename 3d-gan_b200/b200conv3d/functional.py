@@ -966,3 +966,76 @@ def mod_epilogue(y, d=None, field=None, strength=None, bias=None, act=None, slop
     """y [N,C,D,H,W]; d [N,C] or None; field [N|1, 1, D,H,W] (or anything of N*V / V elements) with its
     scalar `strength` (a tensor), or None; bias [C] or None."""
     return _ModEpilogueFn.apply(y, d, field, strength, bias, _act_id(act), slope)
+
+
+# --------------------------------------------------------------- AdaIN (+ trilinear x2), v1-like generator
+class _AdaINFn(Function):
+    """y = (up ? tri2x : id)((x - mean) / sqrt(var_unbiased + eps)) * s_std[n,c] + s_mean[n,c]
+    (stylegan.py:931-959 followed by F.interpolate(scale_factor=2, mode='trilinear'), :1081).
+    Forward: one statistics pass + one apply pass that reads the low-resolution tensor and writes the
+    (up-sampled) output.  Backward: one reduce pass (adjoint interpolation + per-(n,c) sums) and one
+    apply pass; the [N,C]-sized algebra between them is done in fp64 on the device by ATen."""
+
+    @staticmethod
+    def forward(ctx, x, s_mean, s_std, eps, up):
+        _check_device(x)
+        cd = compute_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, c = xb.shape
+        v = d * h * w
+        L = _lib.lib()
+        s1 = torch.empty(n, c, dtype=torch.float32, device=x.device)
+        s2 = torch.empty_like(s1)
+        ws = _ws(L.b2c_mod_workspace(n, v * (8 if up else 1), c), x)
+        with _dev(x):
+            check(L.b2c_instance_stats(_ptr(xb), _ptr(s1), _ptr(s2), n, v, c, _dt(cd), _ptr(ws), ws.numel(),
+                                       _stream(x)), "instance_stats")
+        mean = s1.double() / v
+        var = (s2.double() - v * mean * mean).clamp_min(0.0) / max(v - 1, 1)          # torch.var: unbiased
+        sigma = (var + eps).sqrt()
+        a64 = s_std.detach().double().reshape(n, c) / sigma
+        b64 = s_mean.detach().double().reshape(n, c) - mean * a64
+        a, b = a64.float().contiguous(), b64.float().contiguous()
+        f = 2 if up else 1
+        yl, y = alloc_out(n, d * f, h * f, w * f, c, cd, x.device)
+        with _dev(x):
+            check(L.b2c_adain_fwd(_ptr(xb), _ptr(a), _ptr(b), _ptr(y), n, d, h, w, c, _dt(cd), int(up), _stream(x)),
+                  "adain_fwd")
+        ctx.save_for_backward(xb, mean, sigma, s_std.detach().double().reshape(n, c))
+        ctx.meta = (cd, x.dtype, bool(up), s_mean.shape, s_mean.dtype, s_std.shape, s_std.dtype)
+        return yl
+
+    @staticmethod
+    def backward(ctx, gy):
+        xb, mean, sigma, S = ctx.saved_tensors
+        cd, x_dtype, up, m_shape, m_dtype, s_shape, s_dtype = ctx.meta
+        n, d, h, w, c = xb.shape
+        v = d * h * w
+        g = to_ndhwc(gy, cd)
+        L = _lib.lib()
+        dxl, dx = alloc_out(n, d, h, w, c, cd, gy.device)
+        r1 = torch.empty(n, c, dtype=torch.float32, device=gy.device)
+        r2 = torch.empty_like(r1)
+        ws = _ws(L.b2c_mod_workspace(n, v, c), gy)
+        with _dev(gy):
+            check(L.b2c_adain_bwd_reduce(_ptr(xb), _ptr(g), _ptr(dx) if up else None, _ptr(r1), _ptr(r2), n, d, h, w, c,
+                                         _dt(cd), int(up), _ptr(ws), ws.numel(), _stream(gy)), "adain_bwd_reduce")
+        r1d, r2d = r1.double(), r2.double()
+        gx = (r2d - mean * r1d) / sigma                   # sum_i t_i * xhat_i  = d L / d s_std
+        # dx_i = (S/sigma) [t_i - r1/V - xhat_i * gx / (V-1)],  xhat_i = (x_i - mean) / sigma
+        ct = S / sigma
+        cx = -ct * gx / (sigma * max(v - 1, 1))
+        c0 = -ct * r1d / v - cx * mean
+        t = dx if up else g
+        ctf, cxf, c0f = ct.float().contiguous(), cx.float().contiguous(), c0.float().contiguous()   # keep alive
+        with _dev(gy):
+            check(L.b2c_adain_bwd_apply(_ptr(xb), _ptr(t), _ptr(ctf), _ptr(cxf), _ptr(c0f), _ptr(dx), n, v, c,
+                                        _dt(cd), _stream(gy)), "adain_bwd_apply")
+        return ((dxl if x_dtype == cd else dxl.to(x_dtype)), r1d.reshape(m_shape).to(m_dtype),
+                gx.reshape(s_shape).to(s_dtype), None, None)
+
+
+def adain(x, s_mean, s_std, eps=1e-5, up=False):
+    """Instance-normalise x [N,C,D,H,W] per (n, c) (unbiased variance, as torch.var), scale by s_std [N,C] and
+    shift by s_mean [N,C]; with up=True the trilinear x2 interpolation that follows is folded into the pass."""
+    return _AdaINFn.apply(x, s_mean, s_std, float(eps), bool(up))

@@ -436,17 +436,20 @@ def instance_stats(f, eps=1e-5):
     return mean.view(n, c, 1, 1, 1), (var + eps).sqrt().view(n, c, 1, 1, 1)
 
 
-def AdaIN(f_content, f_style):
-    """stylegan.py:943-959: instance-normalise, then scale / shift by the style's (mean | std)
-    halves.  Folded to one multiply-add per element: y = f * a + b with a = s_std / c_std,
-    b = s_mean - c_mean * a."""
+def AdaIN(f_content, f_style, up=False):
+    """stylegan.py:943-959: instance-normalise, then scale / shift by the style's (mean | std) halves.
+    `up=True` folds the `F.interpolate(scale_factor=2, mode='trilinear')` that follows every second
+    AdaIN (stylegan.py:1081-1137) into the same pass (interpolation commutes with the per-(n,c) affine)."""
     nc = f_content.shape[1]
+    if f_content.is_cuda and BF.mod_supported(nc, BF.compute_dtype(f_content)):
+        return BF.adain(f_content, f_style[:, 0:nc], f_style[:, nc:], 1e-5, up)
     mean, std = instance_stats(f_content)
     s_mean = f_style[:, 0:nc].float()[:, :, None, None, None]
     s_std = f_style[:, nc:].float()[:, :, None, None, None]
     a = s_std / std
     b = s_mean - mean * a
-    return torch.addcmul(b.to(f_content.dtype), f_content, a.to(f_content.dtype))
+    y = torch.addcmul(b.to(f_content.dtype), f_content, a.to(f_content.dtype))
+    return F.interpolate(y, scale_factor=2, mode="trilinear") if up else y
 
 
 def conditionalSplit(w, swapPoint, layerCtr, alreadySplit):
@@ -501,9 +504,7 @@ class styleGAN_gen(tnn.Module):
             if mixing and (i % 2 == 1 or i == 10):     # after C1, C3, C5, C7, C9 and C10: style shuffle point
                 w = conditionalSplit(w, swap, ctr, False)
                 ctr += 1
-            h = AdaIN(h, getattr(self, "A%d" % (i + 1))(w))
-            if i % 2 == 1:
-                h = F.interpolate(h, scale_factor=2, mode="trilinear")
+            h = AdaIN(h, getattr(self, "A%d" % (i + 1))(w), up=(i % 2 == 1))
         return self.C_out(h)
 
 

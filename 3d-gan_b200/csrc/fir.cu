@@ -219,6 +219,22 @@ __global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ F
       const int r = base + s;                       // plane index relative to the chunk
       const int jd = od0 + r - P.pad[0];
       if (r < nout + K - 1 && jd >= 0 && jd < P.id) {
+        // all 4 x 5 row loads of the plane are issued before the first use (predicated, no branches):
+        // the kernel runs at 2-3 CTAs per SM, so memory-level parallelism has to come from each thread
+        Vec<T> raw[K][WB + K - 1];
+        const T* plane = x + (n * P.id + jd) * (int64_t)P.ih * P.iw * P.c + c;
+#pragma unroll
+        for (int b = 0; b < K; b++) {
+          const int jh = oh + b - P.pad[1];
+          const bool hok = jh >= 0 && jh < P.ih;
+#pragma unroll
+          for (int j = 0; j < WB + K - 1; j++) {
+            const int jw = ow0 + j - P.pad[2];
+            const bool ok = hok && jw >= 0 && jw < P.iw;
+            raw[b][j].load(plane + (ok ? ((int64_t)jh * P.iw + jw) * P.c : 0));     // plane[0] is always valid
+            if (!ok) raw[b][j].zero();
+          }
+        }
         float p[WB][VEC];
 #pragma unroll
         for (int q = 0; q < WB; q++)
@@ -226,19 +242,9 @@ __global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ F
           for (int i = 0; i < VEC; i++) p[q][i] = 0.f;
 #pragma unroll
         for (int b = 0; b < K; b++) {
-          const int jh = oh + b - P.pad[1];
-          if (jh < 0 || jh >= P.ih) continue;
-          const T* row = x + ((n * P.id + jd) * P.ih + jh) * (int64_t)P.iw * P.c + c;
           float in[WB + K - 1][VEC];
 #pragma unroll
-          for (int j = 0; j < WB + K - 1; j++) {
-            const int jw = ow0 + j - P.pad[2];
-            if (jw >= 0 && jw < P.iw) fir_ld<T, VEC>(row + (int64_t)jw * P.c, in[j]);
-            else {
-#pragma unroll
-              for (int i = 0; i < VEC; i++) in[j][i] = 0.f;
-            }
-          }
+          for (int j = 0; j < WB + K - 1; j++) raw[b][j].unpack(in[j]);
           const float hb = S.fh[b];
 #pragma unroll
           for (int q = 0; q < WB; q++)

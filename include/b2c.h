@@ -260,6 +260,29 @@ int b2c_mod_epilogue_bwd(const void* y, const void* out, const void* gout,
                          int64_t N, int64_t V, int64_t C, int dtype, int act,
                          float slope, void* ws, size_t ws_bytes, b2c_stream);
 
+/* ---- AdaIN of the v1-like generator (stylegan.py:931-959), optionally fused *
+ * with the trilinear x2 that follows it (stylegan.py:1081, align_corners =     *
+ * False): y = a[n,c] * (up ? tri2x(x) : x) + b[n,c], x [N, d*h*w, C] NDHWC.   *
+ * The caller derives a = s_std / sigma, b = s_mean - mean * a from            *
+ * b2c_instance_stats (sum and sum of squares per (n, c), fp32) and combines   *
+ * the backward reductions r1 = sum t, r2 = sum t*x (t = up ? tri2x^T(gy) : gy *
+ * at the INPUT resolution; for up the kernel stores t in `t`) into            *
+ * dx = ct[n,c]*t + cx[n,c]*x + c0[n,c] (b2c_adain_bwd_apply; t may alias dx). *
+ * Workspace: b2c_mod_workspace(N, V, C) bytes; same channel restrictions.     */
+int b2c_instance_stats(const void* x, float* sum, float* sqsum, int64_t N,
+                       int64_t V, int64_t C, int dtype, void* ws,
+                       size_t ws_bytes, b2c_stream);
+int b2c_adain_fwd(const void* x, const float* a, const float* b, void* y,
+                  int64_t N, int d, int h, int w, int64_t C, int dtype, int up,
+                  b2c_stream);
+int b2c_adain_bwd_reduce(const void* x, const void* gy, void* t, float* r1,
+                         float* r2, int64_t N, int d, int h, int w, int64_t C,
+                         int dtype, int up, void* ws, size_t ws_bytes,
+                         b2c_stream);
+int b2c_adain_bwd_apply(const void* x, const void* t, const float* ct,
+                        const float* cx, const float* c0, void* dx, int64_t N,
+                        int64_t V, int64_t C, int dtype, b2c_stream);
+
 #ifdef __cplusplus
 }
 #endif

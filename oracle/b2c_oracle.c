@@ -684,3 +684,109 @@ int b2c_mod_epilogue_bwd(const void* y, const void* out, const void* gout, const
   free(accb);
   return B2C_OK;
 }
+
+/* ---- AdaIN (+ trilinear x2) of the v1-like generator (stylegan.py:931-959, 1081) ------------ */
+int b2c_instance_stats(const void* x, float* sum, float* sqsum, int64_t N, int64_t V, int64_t C, int dt, void* ws,
+                       size_t wsb, b2c_stream s) {
+  (void)s; (void)ws; (void)wsb;
+  if (!x || !sum || !sqsum || !dt_ok(dt)) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < N; n++)
+    for (int64_t c = 0; c < C; c++) {
+      double a = 0.0, b = 0.0;
+      for (int64_t v = 0; v < V; v++) { double t = ld(x, (n * V + v) * C + c, dt); a += t; b += t * t; }
+      sum[n * C + c] = (float)a; sqsum[n * C + c] = (float)b;
+    }
+  return B2C_OK;
+}
+
+static inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+/* torch upsample_trilinear3d, align_corners=False, scale 2: src = (dst + .5) / 2 - .5 clamped at 0 */
+static void tri_src(int o, int n, int* i0, int* i1, double* w1) {
+  double src = (o + 0.5) / 2.0 - 0.5;
+  if (src < 0) src = 0;
+  *i0 = (int)src;
+  *i1 = *i0 + (*i0 < n - 1 ? 1 : 0);
+  *w1 = src - *i0;
+}
+
+int b2c_adain_fwd(const void* x, const float* a, const float* b, void* y, int64_t N, int d, int h, int w, int64_t C,
+                  int dt, int up, b2c_stream s) {
+  (void)s;
+  if (!x || !a || !b || !y || !dt_ok(dt)) return B2C_ERR_INVALID;
+  int f = up ? 2 : 1, od = d * f, oh = h * f, ow = w * f;
+  for (int64_t n = 0; n < N; n++)
+    for (int zd = 0; zd < od; zd++)
+      for (int zh = 0; zh < oh; zh++)
+        for (int zw = 0; zw < ow; zw++)
+          for (int64_t c = 0; c < C; c++) {
+            double v;
+            if (!up) v = ld(x, (((n * d + zd) * h + zh) * (int64_t)w + zw) * C + c, dt);
+            else {
+              int d0, d1, h0, h1, w0, w1; double fd, fh, fw;
+              tri_src(zd, d, &d0, &d1, &fd); tri_src(zh, h, &h0, &h1, &fh); tri_src(zw, w, &w0, &w1, &fw);
+              v = 0.0;
+              for (int q = 0; q < 8; q++) {
+                int dd = (q & 4) ? d1 : d0, hh = (q & 2) ? h1 : h0, ww = (q & 1) ? w1 : w0;
+                double wt = ((q & 4) ? fd : 1 - fd) * ((q & 2) ? fh : 1 - fh) * ((q & 1) ? fw : 1 - fw);
+                v += wt * ld(x, (((n * d + dd) * h + hh) * (int64_t)w + ww) * C + c, dt);
+              }
+            }
+            st(y, (((n * od + zd) * oh + zh) * (int64_t)ow + zw) * C + c, dt, v * (double)a[n * C + c] + (double)b[n * C + c]);
+          }
+  return B2C_OK;
+}
+
+int b2c_adain_bwd_reduce(const void* x, const void* gy, void* t, float* r1, float* r2, int64_t N, int d, int h, int w,
+                         int64_t C, int dt, int up, void* ws, size_t wsb, b2c_stream s) {
+  (void)s; (void)ws; (void)wsb;
+  if (!x || !gy || !r1 || !r2 || (up && !t) || !dt_ok(dt)) return B2C_ERR_INVALID;
+  int64_t V = (int64_t)d * h * w;
+  double* tt = (double*)calloc((size_t)(V * C), sizeof(double));
+  if (!tt) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < N; n++) {
+    memset(tt, 0, (size_t)(V * C) * sizeof(double));
+    if (!up) {
+      for (int64_t i = 0; i < V * C; i++) tt[i] = ld(gy, n * V * C + i, dt);
+    } else {                                   /* scatter form of the adjoint */
+      int od = 2 * d, oh = 2 * h, ow = 2 * w;
+      for (int zd = 0; zd < od; zd++)
+        for (int zh = 0; zh < oh; zh++)
+          for (int zw = 0; zw < ow; zw++) {
+            int d0, d1, h0, h1, w0, w1; double fd, fh, fw;
+            tri_src(zd, d, &d0, &d1, &fd); tri_src(zh, h, &h0, &h1, &fh); tri_src(zw, w, &w0, &w1, &fw);
+            for (int q = 0; q < 8; q++) {
+              int dd = (q & 4) ? d1 : d0, hh = (q & 2) ? h1 : h0, ww = (q & 1) ? w1 : w0;
+              double wt = ((q & 4) ? fd : 1 - fd) * ((q & 2) ? fh : 1 - fh) * ((q & 1) ? fw : 1 - fw);
+              for (int64_t c = 0; c < C; c++)
+                tt[(((int64_t)dd * h + hh) * w + ww) * C + c] +=
+                    wt * ld(gy, (((n * od + zd) * oh + zh) * (int64_t)ow + zw) * C + c, dt);
+            }
+          }
+    }
+    for (int64_t c = 0; c < C; c++) {
+      double a1 = 0.0, a2 = 0.0;
+      for (int64_t v = 0; v < V; v++) {
+        double tv = tt[v * C + c];
+        if (up) { st(t, (n * V + v) * C + c, dt, tv); }
+        a1 += tv; a2 += tv * ld(x, (n * V + v) * C + c, dt);
+      }
+      r1[n * C + c] = (float)a1; r2[n * C + c] = (float)a2;
+    }
+  }
+  free(tt);
+  return B2C_OK;
+}
+
+int b2c_adain_bwd_apply(const void* x, const void* t, const float* ct, const float* cx, const float* c0, void* dx,
+                        int64_t N, int64_t V, int64_t C, int dt, b2c_stream s) {
+  (void)s;
+  if (!x || !t || !ct || !cx || !c0 || !dx || !dt_ok(dt)) return B2C_ERR_INVALID;
+  for (int64_t n = 0; n < N; n++)
+    for (int64_t v = 0; v < V; v++)
+      for (int64_t c = 0; c < C; c++) {
+        int64_t i = (n * V + v) * C + c, k = n * C + c;
+        st(dx, i, dt, (double)ct[k] * ld(t, i, dt) + (double)cx[k] * ld(x, i, dt) + (double)c0[k]);
+      }
+  return B2C_OK;
+}

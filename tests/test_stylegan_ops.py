@@ -223,3 +223,58 @@ print("HOST-OK")
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_gpu_mod_ops_vs_torch(dtype):
     check_mod_ops("cuda", dtype)
+
+
+ADAIN_SHAPES = ((2, 8, 3, 4, 5), (3, 32, 6, 2, 7), (2, 512, 4, 4, 4), (1, 16, 1, 5, 3))
+
+
+def check_adain(dev, dtype):
+    """b2c_instance_stats / b2c_adain_* (with and without the folded trilinear x2) against the reference's
+    formulation (stylegan.py:931-959 + F.interpolate(scale_factor=2, mode='trilinear')) in stock torch fp32."""
+    import b200conv3d.functional as BF
+    tol = 2e-5 if dtype == torch.float32 else 3e-2
+    err = lambda a, b: ((a.float().cpu() - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()   # noqa: E731
+    for shape in ADAIN_SHAPES:
+        for up in (False, True):
+            n, c = shape[:2]
+            g = torch.Generator().manual_seed(sum(shape) + up)
+            x = (torch.randn(*shape, generator=g) * 1.5 + 0.7).to(dtype).float()     # the same rounded input for both
+            sm, ss = torch.randn(n, c, generator=g), torch.rand(n, c, generator=g) + 0.5
+            xr, mr, sr = (t.clone().requires_grad_(True) for t in (x, sm, ss))
+            flat = xr.reshape(n, c, -1)
+            std = (flat.var(dim=2) + 1e-5).sqrt()[:, :, None, None, None] if flat.shape[2] > 1 else None
+            if std is None:
+                continue
+            mean = flat.mean(dim=2)[:, :, None, None, None]
+            yr = (xr - mean) / std * sr[:, :, None, None, None] + mr[:, :, None, None, None]
+            if up:
+                yr = torch.nn.functional.interpolate(yr, scale_factor=2, mode="trilinear")
+            gy = torch.randn(*yr.shape, generator=g)
+            yr.backward(gy)
+            xg, mg, sg = (t.clone().to(dev).requires_grad_(True) for t in (x.to(dtype), sm, ss))
+            y = BF.adain(xg, mg, sg, 1e-5, up)
+            y.backward(gy.to(dev).to(dtype))
+            assert y.shape == yr.shape
+            assert err(y, yr.detach()) < tol, (shape, up, err(y, yr.detach()))
+            for a, r, what in ((xg, xr, "dx"), (mg, mr, "dmean"), (sg, sr, "dstd")):
+                assert err(a.grad, r.grad) < tol, (shape, up, what, err(a.grad, r.grad))
+
+
+def test_adain_oracle_library_vs_torch(oracle_path):
+    code = r'''
+import sys, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r); sys.path.insert(0, %r)
+from b200conv3d import _lib
+_lib.use_library(%r, host=True)
+import test_stylegan_ops as T
+T.check_adain("cpu", torch.float32)
+print("HOST-OK")
+''' % (os.path.join(ROOT, "3d-gan_b200"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests"), oracle_path)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert "HOST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gpu_adain_vs_torch(dtype):
+    check_adain("cuda", dtype)
