@@ -371,18 +371,21 @@ def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=
 # tensor-core work, which the kernel has to spare.  Weight gradients come back through the
 # (index_select) expansion: every original tap is the sum of the blocks it was copied to.
 FOLD = [True]
+FOLD_K1 = [True]
 
 
 def _fold_factor(x, weight, g):
     if not FOLD[0] or g.transposed or x.dim() != 5:
         return 1
     cout, cin, kd, kh, kw = weight.shape
-    if g.stride != (1, 1, 1) or g.dil != (1, 1, 1) or kw % 2 == 0 or kw == 1 or g.pad[2] != kw // 2:
+    if g.stride != (1, 1, 1) or g.dil != (1, 1, 1) or kw % 2 == 0 or g.pad[2] != kw // 2:
         return 1
-    if cin % 8 or cout % 8 or max(cin, cout) > 32 or compute_dtype(x) != torch.bfloat16:
+    # 1x1x1 convs (utils.py:55,60,101,111) are pure row traffic: fold up to 64 channels (block-diagonal filter)
+    cmax = 64 if (kd, kh, kw) == (1, 1, 1) else 32
+    if cin % 8 or cout % 8 or max(cin, cout) > cmax or compute_dtype(x) != torch.bfloat16 or not FOLD_K1[0] and kw == 1:
         return 1
     w = x.shape[4]
-    for f in ((4, 2) if max(cin, cout) <= 16 else (2,)):
+    for f in ((4, 2) if max(cin, cout) <= cmax // 2 else (2,)):
         if w % f == 0 and w // f >= 2 and kw // 2 <= f:
             return f
     return 1
@@ -397,11 +400,12 @@ def _fold_index(f, kw, device):
     key = (f, kw, str(device))
     if key not in _fold_index_cache:
         pad = kw // 2
-        idx = torch.full((f, f, 3), kw, dtype=torch.long)
+        nt, t0 = (1, 0) if kw == 1 else (3, 1)          # folded taps along W and the centre tap
+        idx = torch.full((f, f, nt), kw, dtype=torch.long)
         for po in range(f):
             for pi in range(f):
-                for t in range(3):
-                    k = f * (t - 1) + pi - po + pad
+                for t in range(nt):
+                    k = f * (t - t0) + pi - po + pad
                     if 0 <= k < kw:
                         idx[po, pi, t] = k
         _fold_index_cache[key] = idx.reshape(-1).to(device)
@@ -409,11 +413,13 @@ def _fold_index(f, kw, device):
 
 
 def fold_filter(weight, f):
-    """[Cout, Cin, kd, kh, kw] -> [F*Cout, F*Cin, kd, kh, 3] (block-sparse; differentiable)."""
+    """[Cout, Cin, kd, kh, kw] -> [F*Cout, F*Cin, kd, kh, 3] (block-sparse; differentiable); a 1x1x1 filter
+    becomes the block-diagonal [F*Cout, F*Cin, 1, 1, 1]."""
     cout, cin, kd, kh, kw = weight.shape
     wz = torch.cat([weight, weight.new_zeros(cout, cin, kd, kh, 1)], dim=4)
-    wf = wz.index_select(4, _fold_index(f, kw, weight.device)).reshape(cout, cin, kd, kh, f, f, 3)
-    return wf.permute(4, 0, 5, 1, 2, 3, 6).reshape(f * cout, f * cin, kd, kh, 3)
+    nt = 1 if kw == 1 else 3
+    wf = wz.index_select(4, _fold_index(f, kw, weight.device)).reshape(cout, cin, kd, kh, f, f, nt)
+    return wf.permute(4, 0, 5, 1, 2, 3, 6).reshape(f * cout, f * cin, kd, kh, nt)
 
 
 def _fold_w(x, f):
@@ -433,7 +439,7 @@ def _unfold_w(y, f):
 def _conv3d_folded(x, weight, bias, g, act, slope, f):
     w2 = fold_filter(weight, f)
     b2 = None if bias is None else bias.repeat(f)
-    g2 = Geom(False, tuple(w2.shape[2:]), 1, (g.pad[0], g.pad[1], 1), 1)
+    g2 = Geom(False, tuple(w2.shape[2:]), 1, (g.pad[0], g.pad[1], 1 if w2.shape[4] == 3 else 0), 1)
     g2.fold = f
     return _unfold_w(_ConvFn.apply(_fold_w(x, f), w2, b2, g2, act, slope), f)
 

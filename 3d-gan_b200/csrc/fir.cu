@@ -42,9 +42,14 @@ __device__ __forceinline__ int first_tap(int v, int m) {
 }
 
 // generic forward: one thread per (output voxel, channel vector)
-template <typename T, int VEC>
-__global__ void __launch_bounds__(kThr) fir_fwd_kernel(const __grid_constant__ FirP P, const T* __restrict__ x,
+// UP / DOWN: compile-time rates (1 or 2) so the index arithmetic is shifts; 0 = take them from P.
+template <typename T, int VEC, int UP, int DOWN>
+__global__ void __launch_bounds__(kThr) fir_fwd_kernel(const __grid_constant__ FirP Pin, const T* __restrict__ x,
                                                         T* __restrict__ y, int64_t total) {
+  const FirP& P0 = Pin;
+  struct { int64_t n; int id, ih, iw, od, oh, ow, c, kd, kh, kw, up, down; int pad[3]; const float* f; } P =
+      {P0.n, P0.id, P0.ih, P0.iw, P0.od, P0.oh, P0.ow, P0.c, P0.kd, P0.kh, P0.kw, UP ? UP : P0.up, DOWN ? DOWN : P0.down,
+       {P0.pad[0], P0.pad[1], P0.pad[2]}, P0.f};
   const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
   if (idx >= total) return;
   const int cv = P.c / VEC;
@@ -83,9 +88,13 @@ __global__ void __launch_bounds__(kThr) fir_fwd_kernel(const __grid_constant__ F
 }
 
 // generic adjoint: dx[n, i, c] = sum over (o, k) with o*down + k - pad == i*up of f[k] * dy[n, o, c]
-template <typename T, int VEC>
-__global__ void __launch_bounds__(kThr) fir_bwd_kernel(const __grid_constant__ FirP P, const T* __restrict__ dy,
+template <typename T, int VEC, int UP, int DOWN>
+__global__ void __launch_bounds__(kThr) fir_bwd_kernel(const __grid_constant__ FirP Pin, const T* __restrict__ dy,
                                                         T* __restrict__ dx, int64_t total) {
+  const FirP& P0 = Pin;
+  struct { int64_t n; int id, ih, iw, od, oh, ow, c, kd, kh, kw, up, down; int pad[3]; const float* f; } P =
+      {P0.n, P0.id, P0.ih, P0.iw, P0.od, P0.oh, P0.ow, P0.c, P0.kd, P0.kh, P0.kw, UP ? UP : P0.up, DOWN ? DOWN : P0.down,
+       {P0.pad[0], P0.pad[1], P0.pad[2]}, P0.f};
   const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
   if (idx >= total) return;
   const int cv = P.c / VEC;
@@ -188,10 +197,12 @@ __global__ void __launch_bounds__(kThr) fir_fwd_w4_kernel(const __grid_constant_
 // accumulators along d: 12 multiply-adds per output instead of 64, 10 loads per output instead of 28.
 struct FirSep { float fd[4], fh[4], fw[4]; int dch; };
 
-template <typename T, int VEC>
+// DOWN = 2 (decimating FIR of the discriminator's skip path, stylegan.py:244-247): the same march with input
+// rows / columns / planes at stride 2; a plane feeds K / DOWN = 2 outputs along d.
+template <typename T, int VEC, int DOWN>
 __global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ FirP P, const __grid_constant__ FirSep S,
                                                         const T* __restrict__ x, T* __restrict__ y, int64_t total) {
-  constexpr int WB = 2, K = 4;
+  constexpr int WB = 2, K = 4, NACC = K / DOWN, NCOL = DOWN * (WB - 1) + K;
   const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
   if (idx >= total) return;
   const int cv = P.c / VEC;
@@ -204,32 +215,33 @@ __global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ F
   const int od0 = (int)(v % dchunks) * S.dch;
   const int64_t n = v / dchunks;
   const int nout = min(S.dch, P.od - od0);
-  float acc[K][WB][VEC];
+  float acc[NACC][WB][VEC];
 #pragma unroll
-  for (int s = 0; s < K; s++)
+  for (int s = 0; s < NACC; s++)
 #pragma unroll
     for (int q = 0; q < WB; q++)
 #pragma unroll
       for (int i = 0; i < VEC; i++) acc[s][q][i] = 0.f;
   T* dst = y + (((n * P.od + od0) * P.oh + oh) * (int64_t)P.ow + ow0) * P.c + c;
   const int64_t dst_plane = (int64_t)P.oh * P.ow * P.c;
-  for (int base = 0; base < nout + K - 1; base += K) {
+  const int nplanes = (nout - 1) * DOWN + K;
+  for (int base = 0; base < nplanes; base += K) {
 #pragma unroll
     for (int s = 0; s < K; s++) {
-      const int r = base + s;                       // plane index relative to the chunk
-      const int jd = od0 + r - P.pad[0];
-      if (r < nout + K - 1 && jd >= 0 && jd < P.id) {
+      const int r = base + s;                       // input plane index relative to the chunk
+      const int jd = od0 * DOWN + r - P.pad[0];
+      if (r < nplanes && jd >= 0 && jd < P.id) {
         // all 4 x 5 row loads of the plane are issued before the first use (predicated, no branches):
         // the kernel runs at 2-3 CTAs per SM, so memory-level parallelism has to come from each thread
-        Vec<T> raw[K][WB + K - 1];
+        Vec<T> raw[K][NCOL];
         const T* plane = x + (n * P.id + jd) * (int64_t)P.ih * P.iw * P.c + c;
 #pragma unroll
         for (int b = 0; b < K; b++) {
-          const int jh = oh + b - P.pad[1];
+          const int jh = oh * DOWN + b - P.pad[1];
           const bool hok = jh >= 0 && jh < P.ih;
 #pragma unroll
-          for (int j = 0; j < WB + K - 1; j++) {
-            const int jw = ow0 + j - P.pad[2];
+          for (int j = 0; j < NCOL; j++) {
+            const int jw = ow0 * DOWN + j - P.pad[2];
             const bool ok = hok && jw >= 0 && jw < P.iw;
             raw[b][j].load(plane + (ok ? ((int64_t)jh * P.iw + jw) * P.c : 0));     // plane[0] is always valid
             if (!ok) raw[b][j].zero();
@@ -242,42 +254,45 @@ __global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ F
           for (int i = 0; i < VEC; i++) p[q][i] = 0.f;
 #pragma unroll
         for (int b = 0; b < K; b++) {
-          float in[WB + K - 1][VEC];
+          float in[NCOL][VEC];
 #pragma unroll
-          for (int j = 0; j < WB + K - 1; j++) raw[b][j].unpack(in[j]);
+          for (int j = 0; j < NCOL; j++) raw[b][j].unpack(in[j]);
           const float hb = S.fh[b];
 #pragma unroll
           for (int q = 0; q < WB; q++)
 #pragma unroll
             for (int i = 0; i < VEC; i++) {
-              float t = S.fw[0] * in[q][i];
-              t = fmaf(S.fw[1], in[q + 1][i], t);
-              t = fmaf(S.fw[2], in[q + 2][i], t);
-              t = fmaf(S.fw[3], in[q + 3][i], t);
+              float t = S.fw[0] * in[q * DOWN][i];
+              t = fmaf(S.fw[1], in[q * DOWN + 1][i], t);
+              t = fmaf(S.fw[2], in[q * DOWN + 2][i], t);
+              t = fmaf(S.fw[3], in[q * DOWN + 3][i], t);
               p[q][i] = fmaf(hb, t, p[q][i]);
             }
         }
-        // plane r feeds outputs o = r - a (a = tap along d); output o lives in slot o % K
+        // plane r feeds outputs o = (r - a) / DOWN for the taps a = r % DOWN + DOWN * j; output o lives in slot o % NACC
 #pragma unroll
-        for (int a = 0; a < K; a++) {
-          const float da = S.fd[a];
+        for (int j = 0; j < NACC; j++) {
+          const float da = S.fd[(s % DOWN) + DOWN * j];
 #pragma unroll
           for (int q = 0; q < WB; q++)
 #pragma unroll
-            for (int i = 0; i < VEC; i++) acc[(s - a + K) % K][q][i] = fmaf(da, p[q][i], acc[(s - a + K) % K][q][i]);
+            for (int i = 0; i < VEC; i++)
+              acc[(s / DOWN - j + NACC) % NACC][q][i] = fmaf(da, p[q][i], acc[(s / DOWN - j + NACC) % NACC][q][i]);
         }
       }
-      // output o = r - (K - 1) is complete: its slot is (s + 1) % K
-      const int o = r - (K - 1);
-      if (o >= 0 && o < nout) {
+      // output o = (r + 1 - K) / DOWN is complete after plane r when DOWN | r + 1: its slot is ((s + 1) / DOWN) % NACC
+      if ((s + 1) % DOWN == 0) {
+        const int o = (r + 1 - K) / DOWN;
+        if (r + 1 >= K && o < nout) {
+#pragma unroll
+          for (int q = 0; q < WB; q++)
+            if (ow0 + q < P.ow) fir_st<T, VEC>(dst + o * dst_plane + (int64_t)q * P.c, acc[((s + 1) / DOWN) % NACC][q]);
+        }
 #pragma unroll
         for (int q = 0; q < WB; q++)
-          if (ow0 + q < P.ow) fir_st<T, VEC>(dst + o * dst_plane + (int64_t)q * P.c, acc[(s + 1) % K][q]);
+#pragma unroll
+          for (int i = 0; i < VEC; i++) acc[((s + 1) / DOWN) % NACC][q][i] = 0.f;
       }
-#pragma unroll
-      for (int q = 0; q < WB; q++)
-#pragma unroll
-        for (int i = 0; i < VEC; i++) acc[(s + 1) % K][q][i] = 0.f;
     }
   }
 }
@@ -308,6 +323,18 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
   const bool vec = P.c % V == 0 && aligned16(a) && aligned16(b);
   const T* ap = static_cast<const T*>(a); T* bp = static_cast<T*>(b);
   const int cvn = P.c / (vec ? V : 1);
+  if (P.up == 1 && P.down == 2 && !bwd && vec && P.kd == 4 && P.kh == 4 && P.kw == 4) {
+    FirSep S;
+    if (factor_rank1(P.f, &S)) {
+      S.dch = 16;
+      const int64_t tot = P.n * ((P.od + S.dch - 1) / S.dch) * P.oh * ((P.ow + 1) / 2) * cvn;
+      if (tot == 0) return B2C_OK;
+      const int64_t blk = cdiv(tot, (int64_t)kThr);
+      if (blk > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+      fir_sep_kernel<T, V, 2><<<(unsigned)blk, kThr, 0, st>>>(P, S, ap, bp, tot);
+      return launched();
+    }
+  }
   if (P.up == 1 && P.down == 1 && P.kw <= 4 && vec) {
     // forward as is; the adjoint of a unit-rate FIR is the FIR with the filter reversed and pad' = K-1-pad
     FirP Q = P;
@@ -324,7 +351,7 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
       if (tot == 0) return B2C_OK;
       const int64_t blk = cdiv(tot, (int64_t)kThr);
       if (blk > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
-      fir_sep_kernel<T, V><<<(unsigned)blk, kThr, 0, st>>>(Q, S, ap, bp, tot);
+      fir_sep_kernel<T, V, 1><<<(unsigned)blk, kThr, 0, st>>>(Q, S, ap, bp, tot);
       return launched();
     }
     const int64_t total = Q.n * Q.od * Q.oh * ((Q.ow + 3) / 4) * cvn;
@@ -338,13 +365,23 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
   if (total == 0) return B2C_OK;
   const int64_t blocks = cdiv(total, (int64_t)kThr);
   if (blocks > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  const unsigned g = (unsigned)blocks;
+  const int rate = P.up == 1 && P.down == 2 ? 12 : (P.up == 2 && P.down == 1 ? 21 : 0);
+#define B2C_FIR_LAUNCH(KERN, U, D)                                                 \
+  do {                                                                             \
+    if (vec) KERN<T, V, U, D><<<g, kThr, 0, st>>>(P, ap, bp, total);               \
+    else KERN<T, 1, U, D><<<g, kThr, 0, st>>>(P, ap, bp, total);                   \
+  } while (0)
   if (!bwd) {
-    if (vec) fir_fwd_kernel<T, V><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
-    else fir_fwd_kernel<T, 1><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
+    if (rate == 12) B2C_FIR_LAUNCH(fir_fwd_kernel, 1, 2);
+    else if (rate == 21) B2C_FIR_LAUNCH(fir_fwd_kernel, 2, 1);
+    else B2C_FIR_LAUNCH(fir_fwd_kernel, 0, 0);
   } else {
-    if (vec) fir_bwd_kernel<T, V><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
-    else fir_bwd_kernel<T, 1><<<(unsigned)blocks, kThr, 0, st>>>(P, ap, bp, total);
+    if (rate == 12) B2C_FIR_LAUNCH(fir_bwd_kernel, 1, 2);
+    else if (rate == 21) B2C_FIR_LAUNCH(fir_bwd_kernel, 2, 1);
+    else B2C_FIR_LAUNCH(fir_bwd_kernel, 0, 0);
   }
+#undef B2C_FIR_LAUNCH
   return launched();
 }
 
