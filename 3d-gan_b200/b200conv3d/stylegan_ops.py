@@ -98,7 +98,8 @@ def demod_coefficients(weight, styles):
     """dcoefs[n, o] = rsqrt(sum_{i,k} (w[o,i,k] * s[n,i])^2 + 1e-8)  (stylegan.py:419-422), as the
     small GEMM  s^2 [N, I] x (sum_k w^2)^T [I, O]  instead of an [N, O, I, k^3] temporary."""
     w2 = weight.float().square().sum(dim=[2, 3, 4])            # [O, I]
-    return (styles.float().square() @ w2.t() + 1e-8).rsqrt()   # [N, O]
+    with torch.autocast(styles.device.type, enabled=False):    # a [N,I] x [I,O] GEMM: keep it out of bf16 autocast
+        return (styles.float().square() @ w2.t() + 1e-8).rsqrt()   # [N, O]
 
 
 def modulated_conv3d(x, weight, styles, noise=None, up=1, down=1, padding=0, resample_filter=None,

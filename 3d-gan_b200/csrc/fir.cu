@@ -196,11 +196,6 @@ __global__ void __launch_bounds__(kThr) fir_fwd_w4_kernel(const __grid_constant_
 // registers once (4 lines x 5 loads, 4 + 4 taps) and scattered into a rolling window of 4 output
 // accumulators along d: 12 multiply-adds per output instead of 64, 10 loads per output instead of 28.
 struct FirSep { float fd[4], fh[4], fw[4]; int dch; };
-constexpr int kSepTW = 8, kSepTH = 4;
-inline int64_t sep_threads(const FirP& P, int dch, int cvn) {
-  return P.n * ((P.od + dch - 1) / dch) * ((P.oh + kSepTH - 1) / kSepTH) * kSepTH * ((P.ow + 2 * kSepTW - 1) / (2 * kSepTW)) *
-         kSepTW * cvn;
-}
 
 // DOWN = 2 (decimating FIR of the discriminator's skip path, stylegan.py:244-247): the same march with input
 // rows / columns / planes at stride 2; a plane feeds K / DOWN = 2 outputs along d.
@@ -213,13 +208,9 @@ __global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ F
   const int cv = P.c / VEC;
   const int c = (int)(idx % cv) * VEC;
   int64_t v = idx / cv;
-  // consecutive threads tile (cvec, kSepTW w-blocks, kSepTH rows): a CTA's warps re-use each other's rows in L1
-  const int wl = (int)(v % kSepTW); v /= kSepTW;
-  const int hl = (int)(v % kSepTH); v /= kSepTH;
-  const int wtiles = (P.ow + WB * kSepTW - 1) / (WB * kSepTW), htiles = (P.oh + kSepTH - 1) / kSepTH;
-  const int ow0 = ((int)(v % wtiles) * kSepTW + wl) * WB; v /= wtiles;
-  const int oh = (int)(v % htiles) * kSepTH + hl; v /= htiles;
-  if (ow0 >= P.ow || oh >= P.oh) return;
+  const int wblocks = (P.ow + WB - 1) / WB;
+  const int ow0 = (int)(v % wblocks) * WB; v /= wblocks;
+  const int oh = (int)(v % P.oh); v /= P.oh;
   const int dchunks = (P.od + S.dch - 1) / S.dch;
   const int od0 = (int)(v % dchunks) * S.dch;
   const int64_t n = v / dchunks;
@@ -336,7 +327,7 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
     FirSep S;
     if (factor_rank1(P.f, &S)) {
       S.dch = 16;
-      const int64_t tot = sep_threads(P, S.dch, cvn);
+      const int64_t tot = P.n * ((P.od + S.dch - 1) / S.dch) * P.oh * ((P.ow + 1) / 2) * cvn;
       if (tot == 0) return B2C_OK;
       const int64_t blk = cdiv(tot, (int64_t)kThr);
       if (blk > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
@@ -356,7 +347,7 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
     FirSep S;
     if (Q.kd == 4 && Q.kh == 4 && Q.kw == 4 && factor_rank1(Q.f, &S)) {
       S.dch = Q.od >= 64 ? 32 : 16;
-      const int64_t tot = sep_threads(Q, S.dch, cvn);
+      const int64_t tot = Q.n * ((Q.od + S.dch - 1) / S.dch) * Q.oh * ((Q.ow + 1) / 2) * cvn;
       if (tot == 0) return B2C_OK;
       const int64_t blk = cdiv(tot, (int64_t)kThr);
       if (blk > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;

@@ -204,9 +204,11 @@ def check_mod_ops(dev, dtype):
                     if dtype == torch.bfloat16 and what == "dy":
                         from abi import kink_robust_err
                         assert kink_robust_err(a.grad, r.grad, tol) < tol, (shape, demod, fn, act, what)
-                    elif dtype == torch.bfloat16 and what == "dstrength":
-                        # a signed sum over every element: its bf16 error scales with the summands, not the sum
-                        assert abs(a.grad.item() - r.grad.item()) < tol * gy.norm().item(), (shape, demod, fn, act)
+                    elif dtype == torch.bfloat16:
+                        # signed sums over all voxels (and, behind lrelu, with a few kink flips): their bf16 error
+                        # scales with the summands, not with the sum
+                        assert (a.grad.float().cpu() - r.grad).abs().max().item() < tol * gy.norm().item(), \
+                            (shape, demod, fn, act, what)
                     else:
                         assert err(a.grad, r.grad) < tol, (shape, demod, fn, act, what, err(a.grad, r.grad))
 
