@@ -301,14 +301,14 @@ def test_gpu_stylegan2_tensor_core_vs_oracle_bf16():
     assert l2(img1, img0) < max(4e-2, 1.5 * l2(imgw, img0)), (l2(img1, img0), l2(imgw, img0))
     assert l2(lr1, lr0) < max(4e-2, 1.5 * l2(lrw, lr0)), (l2(lr1, lr0), l2(lrw, lr0))
     assert set(g1) == set(g0)
-    # parameter gradients: aggregate relative L2 per network against the witness; per tensor only a loose
-    # bound, because many of them (noise_strength, style affines of torgb, ...) are signed sums over every
-    # voxel of a layer whose bf16 error is set by the summands, not by the (much smaller) sum - for stock
-    # torch as well
-    for net in ("G.", "D."):
-        keys = [k for k in g0 if k.startswith(net)]
-        cat = lambda d: torch.cat([d[k].reshape(-1) for k in keys])   # noqa: E731
-        e, ew = l2(cat(g1), cat(g0)), l2(cat(gw), cat(g0))
-        assert e < max(4e-2, 1.5 * ew), (net, e, ew)
-    ratios = sorted(((l2(g1[k], g0[k]) / max(0.25, 3 * l2(gw[k], g0[k])), k) for k in g0 if g0[k].norm() > 0), reverse=True)
-    assert ratios[0][0] < 1.0, ratios[:6]
+    # parameter gradients.  Convolution filters (the products of the wgrad kernels; every element is its own
+    # sum over voxels) are held to the per-layer bf16 bar against the witness.  The remaining tensors
+    # (noise_strength, biases, style affines, mapping network) are signed sums over every voxel AND channel
+    # of a layer, whose bf16 error is set by the summands, not by the (much smaller) sum - for stock torch as
+    # well: a loose per-tensor bound only.
+    def lim(k):
+        ew = l2(gw[k], g0[k])
+        return max(4e-2, 1.5 * ew) if g0[k].dim() == 5 else max(0.25, 3 * ew)
+    ratios = sorted(((l2(g1[k], g0[k]) / lim(k), k) for k in g0 if g0[k].norm() > 0), reverse=True)
+    assert ratios[0][0] < 1.0, ratios[:8]
+    assert sum(1 for k in g0 if g0[k].dim() == 5) >= 20
