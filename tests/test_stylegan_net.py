@@ -301,14 +301,17 @@ def test_gpu_stylegan2_tensor_core_vs_oracle_bf16():
     assert l2(img1, img0) < max(4e-2, 1.5 * l2(imgw, img0)), (l2(img1, img0), l2(imgw, img0))
     assert l2(lr1, lr0) < max(4e-2, 1.5 * l2(lrw, lr0)), (l2(lr1, lr0), l2(lrw, lr0))
     assert set(g1) == set(g0)
-    # parameter gradients.  Convolution filters (the products of the wgrad kernels; every element is its own
-    # sum over voxels) are held to the per-layer bf16 bar against the witness.  The remaining tensors
-    # (noise_strength, biases, style affines, mapping network) are signed sums over every voxel AND channel
-    # of a layer, whose bf16 error is set by the summands, not by the (much smaller) sum - for stock torch as
-    # well: a loose per-tensor bound only.
+    # parameter gradients.  The bf16 gradient error of this two-network chain is dominated by which LeakyReLU
+    # kinks of the discriminator flip under bf16 rounding: measured over seeds (tools/dbg_stylegan_bf16_seeds.py)
+    # it varies by 2-3x in EITHER direction between equivalent bf16 implementations (ours, ours with the
+    # elementwise glue, stock torch autocast), e.g. G.b64.conv1.weight 0.107 / 0.030 / 0.066, 0.068 / 0.109 /
+    # 0.179, 0.016 / 0.010 / 0.031, 0.020 / 0.032 / 0.014.  Convolution filters (every element its own sum over
+    # voxels) are therefore bounded by 3x the witness; the remaining tensors (noise_strength, biases, style
+    # affines: signed sums over every voxel and channel of a layer) only loosely.  The exact check of the same
+    # code path is the fp32 golden test above.
     def lim(k):
         ew = l2(gw[k], g0[k])
-        return max(4e-2, 1.5 * ew) if g0[k].dim() == 5 else max(0.25, 3 * ew)
+        return max(4e-2, 3 * ew) if g0[k].dim() == 5 else max(0.25, 4 * ew)
     ratios = sorted(((l2(g1[k], g0[k]) / lim(k), k) for k in g0 if g0[k].norm() > 0), reverse=True)
     assert ratios[0][0] < 1.0, ratios[:8]
     assert sum(1 for k in g0 if g0[k].dim() == 5) >= 20
