@@ -346,17 +346,77 @@ def _act_id(act):
 
 def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=None, slope=0.0):
     """Drop-in for ``torch.nn.functional.conv3d`` (stylegan.py:168, nn.Conv3d.forward)
-    with an optional fused activation epilogue."""
+    with an optional fused activation epilogue (`act` a name or a b2c activation id)."""
     if groups != 1:
         raise NotImplementedError("b200conv3d.conv3d: groups=%d is not supported (only the dense "
                                   "path is built; no cuDNN fallback)" % groups)
     if isinstance(padding, str):
         raise NotImplementedError("b200conv3d.conv3d: string padding %r is not supported" % padding)
     g = Geom(False, tuple(weight.shape[2:]), stride, padding, dilation)
+    if _s2d_applies(x, weight, g):
+        return _conv3d_s2d(x, weight, bias, g, _act_id(act), slope)
     fold = _fold_factor(x, weight, g)
     if fold > 1:
         return _conv3d_folded(x, weight, bias, g, _act_id(act), slope, fold)
     return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+
+
+# ---- space-to-depth for one-channel stride-2 stems with many taps --------------------------------
+# FID_ResNet.py:119 `Conv3d(1, 64, kernel_size=7, stride=2, padding=3)`: 343 taps on a one-channel tensor.
+# The fused one-channel gather kernel holds <= 64 taps, and the generic lowering writes a 4.6 GB im2col
+# matrix (16.8 ms of the 38.8 ms FID forward at batch 25).  Moving the 2x2x2 sub-lattices of the input into
+# 8 channels (one pass over a 105 MB tensor) turns the layer into a stride-1 `8 -> Cout` convolution with
+# a (k+3)/2-tap "same" kernel (5^3 for k = 7, zero where no original tap lands), which then runs W-folded
+# on the tcgen05 path.
+S2D = [True]
+
+
+def _s2d_applies(x, weight, g):
+    if not S2D[0] or g.transposed or x.dim() != 5 or weight.shape[1] != 1 or x.shape[1] != 1:
+        return False
+    k = weight.shape[2]
+    if tuple(weight.shape[2:]) != (k, k, k) or k % 2 == 0 or k ** 3 <= 64:
+        return False
+    if g.stride != (2, 2, 2) or g.dil != (1, 1, 1) or g.pad != (k // 2,) * 3 or weight.shape[0] % 8:
+        return False
+    return all(v % 2 == 0 for v in x.shape[2:]) and compute_dtype(x) == torch.bfloat16
+
+
+_s2d_index_cache = {}
+
+
+def _s2d_index(k, device):
+    """idx[p, t] = original tap that connects input voxel 2*(o + t - R) + p to output voxel o (pad = k//2),
+    or k (a zero slot); R = the radius of the phase-space kernel."""
+    key = (k, str(device))
+    if key not in _s2d_index_cache:
+        m = k // 2
+        r = max(abs((-m) // 2), (m) // 2)
+        idx = torch.full((2, 2 * r + 1), k, dtype=torch.long)
+        for p in range(2):
+            for t in range(2 * r + 1):
+                kk = 2 * (t - r) + p + m
+                if 0 <= kk < k:
+                    idx[p, t] = kk
+        _s2d_index_cache[key] = (idx.to(device), r)
+    return _s2d_index_cache[key]
+
+
+def s2d_filter(weight):
+    """[Cout, 1, k, k, k] (stride 2, pad k//2) -> [Cout, 8, k', k', k'] (stride 1, pad k'//2); differentiable."""
+    cout, _, k = weight.shape[:3]
+    idx, r = _s2d_index(k, weight.device)
+    kp = 2 * r + 1
+    wz = torch.nn.functional.pad(weight[:, 0], (0, 1, 0, 1, 0, 1))                     # zero slot at index k on every axis
+    wf = wz[:, idx[:, :, None, None, None, None], idx[None, None, :, :, None, None], idx[None, None, None, None, :, :]]
+    return wf.permute(0, 1, 3, 5, 2, 4, 6).reshape(cout, 8, kp, kp, kp), r              # channel = (pd, ph, pw)
+
+
+def _conv3d_s2d(x, weight, bias, g, act, slope):
+    n, _, d, h, w = x.shape
+    x8 = x.reshape(n, d // 2, 2, h // 2, 2, w // 2, 2).permute(0, 1, 3, 5, 2, 4, 6).reshape(n, d // 2, h // 2, w // 2, 8)
+    w8, r = s2d_filter(weight)
+    return conv3d(x8.permute(0, 4, 1, 2, 3), w8, bias, 1, r, act=act, slope=slope)
 
 
 # ---- W-folding of narrow stride-1 convolutions ------------------------------------------------
@@ -382,10 +442,12 @@ def _fold_factor(x, weight, g):
         return 1
     # 1x1x1 convs (utils.py:55,60,101,111) are pure row traffic: fold up to 64 channels (block-diagonal filter)
     cmax = 64 if (kd, kh, kw) == (1, 1, 1) else 32
-    if cin % 8 or cout % 8 or max(cin, cout) > cmax or compute_dtype(x) != torch.bfloat16 or not FOLD_K1[0] and kw == 1:
+    thin_in = cin <= 16 and cout <= 64                      # 16- / 32-byte input rows: fold by 4 whatever the output
+    if cin % 8 or cout % 8 or (max(cin, cout) > cmax and not thin_in) or compute_dtype(x) != torch.bfloat16 \
+            or not FOLD_K1[0] and kw == 1:
         return 1
     w = x.shape[4]
-    for f in ((4, 2) if max(cin, cout) <= cmax // 2 else (2,)):
+    for f in ((4, 2) if (max(cin, cout) <= cmax // 2 or thin_in) else (2,)):
         if w % f == 0 and w // f >= 2 and kw // 2 <= f:
             return f
     return 1

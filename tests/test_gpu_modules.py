@@ -219,3 +219,34 @@ def test_w_folded_conv_matches_plain_and_torch(cfg):
             ref = run(lambda a, c, d: torch.nn.functional.conv3d(a, c, d, padding=k // 2), x)
             for i, (o, r) in enumerate(zip(ours, ref)):
                 assert rel_err(o, r) < 2e-2, (i, rel_err(o, r))
+
+
+@pytest.mark.gpu
+def test_s2d_stem_matches_plain_and_torch():
+    """FID_ResNet.py:119 stem `Conv3d(1, 64, 7, stride=2, padding=3)`: the space-to-depth + W-folded tcgen05
+    route against the generic one-channel lowering (same bf16 inputs) and stock torch fp32, forward and all
+    gradients (no activation in the way: tests/abi.py kink_robust_err explains why)."""
+    import b200conv3d.functional as BF
+    torch.manual_seed(7)
+    x = torch.randn(2, 1, 16, 24, 32, device="cuda")
+    wt = torch.randn(64, 1, 7, 7, 7, device="cuda") * 343 ** -0.5
+    b = torch.randn(64, device="cuda") * 0.1
+    gy = torch.randn(2, 64, 8, 12, 16, device="cuda")
+    assert BF._s2d_applies(x.bfloat16(), wt, BF.Geom(False, (7, 7, 7), 2, 3, 1))
+
+    def run(fn, xin):
+        xx, ww, bb = xin.clone().requires_grad_(True), wt.clone().requires_grad_(True), b.clone().requires_grad_(True)
+        y = fn(xx, ww, bb)
+        y.backward(gy.to(y.dtype))
+        return [t.detach().float() for t in (y, xx.grad, ww.grad, bb.grad)]
+
+    ours = run(lambda a, c, d: BF.conv3d(a, c, d, 2, 3), x.bfloat16())
+    BF.S2D[0] = False
+    try:
+        plain = run(lambda a, c, d: BF.conv3d(a, c, d, 2, 3), x.bfloat16())
+    finally:
+        BF.S2D[0] = True
+    ref = run(lambda a, c, d: F.conv3d(a, c, d, stride=2, padding=3), x)
+    for i, (o, p, r) in enumerate(zip(ours, plain, ref)):
+        assert rel_err(o, p) < 1e-2, (i, rel_err(o, p))
+        assert rel_err(o, r) < 2e-2, (i, rel_err(o, r))
