@@ -153,13 +153,25 @@ chan_reduce_stage1(const T* __restrict__ x, int64_t rows, int C, BnBwdF<T> f, fl
   }
 }
 
-__global__ void chan_reduce_stage2(const float* __restrict__ ws, int nblocks, int C,
-                                   float* __restrict__ out0, float* __restrict__ out1) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// Second stage: out[c] = sum over the stage-1 CTAs of their partial sums.  32 channels x 16 slices per CTA: a
+// slice sums every 16th partial row (128-byte coalesced rows, double accumulators), the slices are combined
+// through shared memory in a fixed order (deterministic).  The one-thread-per-channel version walked all
+// ~1200 partial rows serially: 50-90 us per call, 2-9 % of the FID / BigGAN step.
+constexpr int kS2Chan = 32, kS2Slices = 16;
+__global__ void __launch_bounds__(kS2Chan * kS2Slices)
+chan_reduce_stage2(const float* __restrict__ ws, int nblocks, int C, float* __restrict__ out0, float* __restrict__ out1) {
+  __shared__ double sa[kS2Slices][kS2Chan], sb[kS2Slices][kS2Chan];
+  const int lc = threadIdx.x % kS2Chan, sl = threadIdx.x / kS2Chan;
+  const int c = blockIdx.x * kS2Chan + lc;
   double a = 0.0, b = 0.0;
-  for (int i = 0; i < nblocks; i++) { a += ws[(int64_t)i * 2 * C + c]; b += ws[(int64_t)i * 2 * C + C + c]; }
-  out0[c] = (float)a; out1[c] = (float)b;
+  if (c < C)
+    for (int i = sl; i < nblocks; i += kS2Slices) { a += ws[(int64_t)i * 2 * C + c]; b += ws[(int64_t)i * 2 * C + C + c]; }
+  sa[sl][lc] = a; sb[sl][lc] = b;
+  __syncthreads();
+  if (sl == 0 && c < C) {
+    for (int j = 1; j < kS2Slices; j++) { a += sa[j][lc]; b += sb[j][lc]; }
+    out0[c] = (float)a; out1[c] = (float)b;
+  }
 }
 
 static int reduce_blocks(int64_t rows) {
@@ -185,7 +197,7 @@ static int chan_reduce(const T* x, int64_t rows, int64_t C, BnBwdF<T> f, float* 
     chan_reduce_stage1<T, 1, BWD><<<nb, kThreads, kThreads * 2 * sizeof(float), st>>>(x, rows, (int)C, f, w, rpb);
   int rc = launched();
   if (rc) return rc;
-  chan_reduce_stage2<<<(unsigned)cdiv(C, 256), 256, 0, st>>>(w, nb, (int)C, o0, o1);
+  chan_reduce_stage2<<<(unsigned)cdiv(C, kS2Chan), kS2Chan * kS2Slices, 0, st>>>(w, nb, (int)C, o0, o1);
   return launched();
 }
 
