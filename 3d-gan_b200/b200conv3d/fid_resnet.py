@@ -3,7 +3,7 @@ used by eval_utils.fid_3d, eval_utils.py:41-52) built from the B200 drop-in laye
 epilogues the conv path offers folded in: BN + ReLU in one pass and BN + residual add + ReLU
 in one pass (FID_ResNet.py:97-100).  Parameter names equal the reference's, so the MedicalNet
 checkpoint (`resnet_50.pth`, eval_utils.py:54-63) or a reference state_dict loads unchanged.
-MaxPool3d(3,2,1) after the stem is torch's (resampling kernels are "next").
+MaxPool3d(3,2,1) after the stem is one NDHWC pass (b2c_maxpool3d).
 """
 import torch
 import torch.nn as tnn
@@ -41,7 +41,7 @@ class ResNet(tnn.Module):
         self.conv1 = BN.Conv3d(1, 64, kernel_size=7, stride=(2, 2, 2), padding=(3, 3, 3), bias=False)
         self.bn1 = BN.BatchNorm3d(64)
         self.bn1.fused_act = "relu"
-        self.maxpool = tnn.MaxPool3d(kernel_size=(3, 3, 3), stride=2, padding=1)
+        self.maxpool = BN.MaxPool3d(kernel_size=(3, 3, 3), stride=2, padding=1)
         self.layer1 = self._make_layer(64, layers[0])
         self.layer2 = self._make_layer(128, layers[1], stride=2)
         self.layer3 = self._make_layer(256, layers[2], stride=1, dilation=2)

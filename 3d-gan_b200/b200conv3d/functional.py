@@ -1107,3 +1107,43 @@ def adain(x, s_mean, s_std, eps=1e-5, up=False):
     """Instance-normalise x [N,C,D,H,W] per (n, c) (unbiased variance, as torch.var), scale by s_std [N,C] and
     shift by s_mean [N,C]; with up=True the trilinear x2 interpolation that follows is folded into the pass."""
     return _AdaINFn.apply(x, s_mean, s_std, float(eps), bool(up))
+
+
+# --------------------------------------------------------------- MaxPool3d on NDHWC
+class _MaxPoolFn(Function):
+    """nn.MaxPool3d(k, stride, pad) (FID_ResNet.py:129) in one NDHWC pass (ATen converts to NCDHW and back)."""
+
+    @staticmethod
+    def forward(ctx, x, k, stride, pad):
+        _check_device(x)
+        cd = _keep_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, c = xb.shape
+        od, oh, ow = ((v + 2 * pad - k) // stride + 1 for v in (d, h, w))
+        yl, y = alloc_out(n, od, oh, ow, c, cd, x.device)
+        with _dev(x):
+            check(_lib.lib().b2c_maxpool3d_fwd(_ptr(xb), _ptr(y), n, d, h, w, c, k, stride, pad, _dt(cd), _stream(x)),
+                  "maxpool3d_fwd")
+        ctx.save_for_backward(xb)
+        ctx.meta = (k, stride, pad, cd, x.dtype)
+        return yl
+
+    @staticmethod
+    def backward(ctx, gy):
+        (xb,) = ctx.saved_tensors
+        k, stride, pad, cd, x_dtype = ctx.meta
+        n, d, h, w, c = xb.shape
+        g = to_ndhwc(gy, cd)
+        dxl, dx = alloc_out(n, d, h, w, c, cd, gy.device)
+        with _dev(gy):
+            check(_lib.lib().b2c_maxpool3d_bwd(_ptr(xb), _ptr(g), _ptr(dx), n, d, h, w, c, k, stride, pad, _dt(cd),
+                                               _stream(gy)), "maxpool3d_bwd")
+        return (dxl if x_dtype == cd else dxl.to(x_dtype)), None, None, None
+
+
+def max_pool3d(x, kernel_size, stride=None, padding=0):
+    """Drop-in for F.max_pool3d with one isotropic int per argument (what the reference uses)."""
+    k, s, p = _triple(kernel_size), _triple(stride if stride is not None else kernel_size), _triple(padding)
+    if len(set(k)) != 1 or len(set(s)) != 1 or len(set(p)) != 1:
+        raise NotImplementedError("anisotropic MaxPool3d is not on the reference's path")
+    return _MaxPoolFn.apply(x, k[0], s[0], p[0])

@@ -121,6 +121,18 @@ class AvgPool3d(tnn.AvgPool3d):
         return BF.avg_pool2(x)
 
 
+_TMaxPool3d = tnn.MaxPool3d
+
+
+class MaxPool3d(_TMaxPool3d):
+    """nn.MaxPool3d(kernel_size=3, stride=2, padding=1) after the FID stem (FID_ResNet.py:129) as one NDHWC pass."""
+
+    def forward(self, x):
+        if self.ceil_mode or self.return_indices or BF._triple(self.dilation) != (1, 1, 1):
+            raise ValueError("b200conv3d.nn.MaxPool3d: ceil_mode / return_indices / dilation are not on the reference's path")
+        return BF.max_pool3d(x, self.kernel_size, self.stride, self.padding)
+
+
 class FusedAway(tnn.Identity):
     """Placeholder left where an activation was folded into the previous layer
     by :func:`b200conv3d.patch.fuse`; keeps nn.Sequential indices (and thus

@@ -25,6 +25,7 @@ _CLASS_MAP = {
     "ReLU": (BN._TReLU, BN.ReLU),
     "LeakyReLU": (BN._TLeakyReLU, BN.LeakyReLU),
     "Tanh": (BN._TTanh, BN.Tanh),
+    "MaxPool3d": (BN._TMaxPool3d, BN.MaxPool3d),          # FID_ResNet.py:129
 }
 _stock_functional = {"conv3d": TF.conv3d, "conv_transpose3d": TF.conv_transpose3d}
 _installed = [False]

@@ -173,6 +173,117 @@ int pool2(bool bwd, const void* a, void* b, const RsGeo& g, int di, int hi, int 
   return launched();
 }
 
+// ---- MaxPool3d(k, stride, pad) on NDHWC (FID_ResNet.py:129 `nn.MaxPool3d(kernel_size=3, stride=2, padding=1)`) --
+// ATen has no channels-last 3-D max-pool kernel: it converts to NCDHW and back (2.9 ms for the FID stem at batch
+// 25); here one thread owns (output voxel, 16-byte channel vector) and reads the k^3 window once.  Padding counts
+// as -inf (never materialised).  Ties go to the first element in (d, h, w) scan order, as in ATen.
+struct MpGeo { int64_t n; int id, ih, iw, od, oh, ow, c, k, s, p; };
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThr) maxpool_fwd_kernel(MpGeo g, const T* __restrict__ x, T* __restrict__ y,
+                                                           int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = g.c / VEC;
+  const int c = (int)(idx % cv) * VEC;
+  int64_t v = idx / cv;
+  T* dst = y + v * (int64_t)g.c + c;
+  const int ow = (int)(v % g.ow); v /= g.ow;
+  const int oh = (int)(v % g.oh); v /= g.oh;
+  const int od = (int)(v % g.od);
+  const int64_t n = v / g.od;
+  float m[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; i++) m[i] = -INFINITY;
+  for (int a = 0; a < g.k; a++) {
+    const int jd = od * g.s + a - g.p;
+    if (jd < 0 || jd >= g.id) continue;
+    for (int b = 0; b < g.k; b++) {
+      const int jh = oh * g.s + b - g.p;
+      if (jh < 0 || jh >= g.ih) continue;
+      const T* row = x + ((n * g.id + jd) * g.ih + jh) * (int64_t)g.iw * g.c + c;
+      for (int e = 0; e < g.k; e++) {
+        const int jw = ow * g.s + e - g.p;
+        if (jw < 0 || jw >= g.iw) continue;
+        float t[VEC];
+        rs_ld<T, VEC>(row + (int64_t)jw * g.c, t);
+#pragma unroll
+        for (int i = 0; i < VEC; i++) m[i] = (t[i] > m[i] || t[i] != t[i]) ? t[i] : m[i];
+      }
+    }
+  }
+  rs_st<T, VEC>(dst, m);
+}
+
+// gather form of the backward (deterministic): an input voxel collects dy of every window that covers it and
+// whose FIRST maximum (scan order) it is.  One thread per (input voxel, channel); not on a hot path (the
+// reference only runs the FID network under no_grad, eval_utils.py:41-52).
+template <typename T>
+__global__ void __launch_bounds__(kThr) maxpool_bwd_kernel(MpGeo g, const T* __restrict__ x, const T* __restrict__ dy,
+                                                           T* __restrict__ dx, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int c = (int)(idx % g.c);
+  int64_t v = idx / g.c;
+  const int iw = (int)(v % g.iw); v /= g.iw;
+  const int ih = (int)(v % g.ih); v /= g.ih;
+  const int id = (int)(v % g.id);
+  const int64_t n = v / g.id;
+  const float self = ldf(x, idx);
+  float acc = 0.f;
+  for (int od = max(0, (id + g.p - g.k + g.s) / g.s); od < g.od && od * g.s - g.p <= id; od++)
+    for (int oh = max(0, (ih + g.p - g.k + g.s) / g.s); oh < g.oh && oh * g.s - g.p <= ih; oh++)
+      for (int ow = max(0, (iw + g.p - g.k + g.s) / g.s); ow < g.ow && ow * g.s - g.p <= iw; ow++) {
+        // is (id, ih, iw) the first maximum of window (od, oh, ow)?
+        bool win = true;
+        for (int a = 0; a < g.k && win; a++) {
+          const int jd = od * g.s + a - g.p;
+          if (jd < 0 || jd >= g.id) continue;
+          for (int b = 0; b < g.k && win; b++) {
+            const int jh = oh * g.s + b - g.p;
+            if (jh < 0 || jh >= g.ih) continue;
+            for (int e = 0; e < g.k; e++) {
+              const int jw = ow * g.s + e - g.p;
+              if (jw < 0 || jw >= g.iw) continue;
+              const float t = ldf(x, (((n * g.id + jd) * g.ih + jh) * (int64_t)g.iw + jw) * g.c + c);
+              const bool before = (jd < id) || (jd == id && (jh < ih || (jh == ih && jw < iw)));
+              if (t > self || (before && t == self)) { win = false; break; }
+            }
+          }
+        }
+        if (win) acc += ldf(dy, (((n * g.od + od) * g.oh + oh) * (int64_t)g.ow + ow) * g.c + c);
+      }
+  stf(dx, idx, acc);
+}
+
+template <typename T>
+int maxpool_t(bool bwd, const void* a, const void* b, void* o, const MpGeo& g, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  unsigned blocks;
+  if (!bwd) {
+    const bool vec = g.c % V == 0 && aligned16(a) && aligned16(o);
+    const int64_t total = g.n * g.od * g.oh * g.ow * (g.c / (vec ? V : 1));
+    if (total == 0) return B2C_OK;
+    if (!grid_ok(total, &blocks)) return B2C_ERR_UNSUPPORTED;
+    if (vec) maxpool_fwd_kernel<T, V><<<blocks, kThr, 0, st>>>(g, static_cast<const T*>(a), static_cast<T*>(o), total);
+    else maxpool_fwd_kernel<T, 1><<<blocks, kThr, 0, st>>>(g, static_cast<const T*>(a), static_cast<T*>(o), total);
+    return launched();
+  }
+  const int64_t total = g.n * g.id * g.ih * g.iw * g.c;
+  if (total == 0) return B2C_OK;
+  if (!grid_ok(total, &blocks)) return B2C_ERR_UNSUPPORTED;
+  maxpool_bwd_kernel<T><<<blocks, kThr, 0, st>>>(g, static_cast<const T*>(a), static_cast<const T*>(b), static_cast<T*>(o), total);
+  return launched();
+}
+
+bool mp_geo(int64_t n, int d, int h, int w, int c, int k, int s, int p, MpGeo* g) {
+  if (n < 0 || d <= 0 || h <= 0 || w <= 0 || c <= 0 || k < 1 || s < 1 || p < 0 || 2 * p > k) return false;
+  const int od = (d + 2 * p - k) / s + 1, oh = (h + 2 * p - k) / s + 1, ow = (w + 2 * p - k) / s + 1;
+  if (od <= 0 || oh <= 0 || ow <= 0) return false;
+  *g = MpGeo{n, d, h, w, od, oh, ow, c, k, s, p};
+  return true;
+}
+
 bool up_args_ok(const void* a, const void* b, int64_t n, int d, int h, int w, int cx, int c0, int c, int dt) {
   return a && b && n >= 0 && d > 0 && h > 0 && w > 0 && cx > 0 && c > 0 && c0 >= 0 && c0 + c <= cx && dt_ok(dt);
 }
@@ -210,4 +321,20 @@ extern "C" int b2c_avgpool2_bwd(const void* dy, void* dx, int64_t n, int d, int 
   const RsGeo g{n, d / 2, h / 2, w / 2, c, 0, c};
   cudaStream_t st = static_cast<cudaStream_t>(s);
   return dt == B2C_BF16 ? pool2<__nv_bfloat16>(true, dy, dx, g, d, h, w, st) : pool2<float>(true, dy, dx, g, d, h, w, st);
+}
+
+extern "C" int b2c_maxpool3d_fwd(const void* x, void* y, int64_t n, int d, int h, int w, int c, int k, int stride,
+                                 int pad, int dt, b2c_stream s) {
+  MpGeo g;
+  if (!x || !y || !dt_ok(dt) || !mp_geo(n, d, h, w, c, k, stride, pad, &g)) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? maxpool_t<__nv_bfloat16>(false, x, nullptr, y, g, st) : maxpool_t<float>(false, x, nullptr, y, g, st);
+}
+
+extern "C" int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_t n, int d, int h, int w, int c, int k,
+                                 int stride, int pad, int dt, b2c_stream s) {
+  MpGeo g;
+  if (!x || !dy || !dx || !dt_ok(dt) || !mp_geo(n, d, h, w, c, k, stride, pad, &g)) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? maxpool_t<__nv_bfloat16>(true, x, dy, dx, g, st) : maxpool_t<float>(true, x, dy, dx, g, st);
 }

@@ -283,6 +283,16 @@ int b2c_adain_bwd_apply(const void* x, const void* t, const float* ct,
                         const float* cx, const float* c0, void* dx, int64_t N,
                         int64_t V, int64_t C, int dtype, b2c_stream);
 
+/* ---- nn.MaxPool3d(k, stride, pad) on NDHWC (FID_ResNet.py:129) -------------- *
+ * x [n,d,h,w,c] -> y [n,od,oh,ow,c], o = (i + 2*pad - k) / stride + 1 (floor);   *
+ * padding counts as -inf; ties go to the first element in scan order (ATen).    *
+ * bwd: dx from (x, dy), deterministic gather form (recomputes the arg-max).     */
+int b2c_maxpool3d_fwd(const void* x, void* y, int64_t n, int d, int h, int w,
+                      int c, int k, int stride, int pad, int dtype, b2c_stream);
+int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_t n, int d,
+                      int h, int w, int c, int k, int stride, int pad, int dtype,
+                      b2c_stream);
+
 #ifdef __cplusplus
 }
 #endif

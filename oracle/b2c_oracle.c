@@ -790,3 +790,60 @@ int b2c_adain_bwd_apply(const void* x, const void* t, const float* ct, const flo
       }
   return B2C_OK;
 }
+
+/* ---- nn.MaxPool3d(k, stride, pad) on NDHWC (FID_ResNet.py:129) ------------------------------- */
+static int mp_out(int i, int k, int s, int p) { return (i + 2 * p - k) / s + 1; }
+int b2c_maxpool3d_fwd(const void* x, void* y, int64_t n, int d, int h, int w, int c, int k, int stride, int pad, int dt,
+                      b2c_stream s) {
+  (void)s;
+  if (!x || !y || !dt_ok(dt) || k < 1 || stride < 1 || pad < 0 || 2 * pad > k) return B2C_ERR_INVALID;
+  int od = mp_out(d, k, stride, pad), oh = mp_out(h, k, stride, pad), ow = mp_out(w, k, stride, pad);
+  if (od <= 0 || oh <= 0 || ow <= 0) return B2C_ERR_INVALID;
+  for (int64_t in = 0; in < n; in++)
+    for (int a = 0; a < od; a++)
+      for (int b = 0; b < oh; b++)
+        for (int e = 0; e < ow; e++)
+          for (int ch = 0; ch < c; ch++) {
+            double m = -INFINITY;
+            for (int kd = 0; kd < k; kd++)
+              for (int kh = 0; kh < k; kh++)
+                for (int kw = 0; kw < k; kw++) {
+                  int jd = a * stride + kd - pad, jh = b * stride + kh - pad, jw = e * stride + kw - pad;
+                  if (jd < 0 || jd >= d || jh < 0 || jh >= h || jw < 0 || jw >= w) continue;
+                  double t = ld(x, ((((int64_t)in * d + jd) * h + jh) * w + jw) * c + ch, dt);
+                  if (t > m) m = t;
+                }
+            st(y, ((((int64_t)in * od + a) * oh + b) * ow + e) * c + ch, dt, m);
+          }
+  return B2C_OK;
+}
+int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_t n, int d, int h, int w, int c, int k, int stride,
+                      int pad, int dt, b2c_stream s) {
+  (void)s;
+  if (!x || !dy || !dx || !dt_ok(dt) || k < 1 || stride < 1 || pad < 0 || 2 * pad > k) return B2C_ERR_INVALID;
+  int od = mp_out(d, k, stride, pad), oh = mp_out(h, k, stride, pad), ow = mp_out(w, k, stride, pad);
+  if (od <= 0 || oh <= 0 || ow <= 0) return B2C_ERR_INVALID;
+  int64_t total = n * d * h * w * c;
+  double* acc = (double*)calloc((size_t)total, sizeof(double));
+  if (!acc) return B2C_ERR_INVALID;
+  for (int64_t in = 0; in < n; in++)            /* scatter form: dy goes to the first maximum of its window */
+    for (int a = 0; a < od; a++)
+      for (int b = 0; b < oh; b++)
+        for (int e = 0; e < ow; e++)
+          for (int ch = 0; ch < c; ch++) {
+            double m = -INFINITY; int64_t arg = -1;
+            for (int kd = 0; kd < k; kd++)
+              for (int kh = 0; kh < k; kh++)
+                for (int kw = 0; kw < k; kw++) {
+                  int jd = a * stride + kd - pad, jh = b * stride + kh - pad, jw = e * stride + kw - pad;
+                  if (jd < 0 || jd >= d || jh < 0 || jh >= h || jw < 0 || jw >= w) continue;
+                  int64_t i = ((((int64_t)in * d + jd) * h + jh) * w + jw) * c + ch;
+                  double t = ld(x, i, dt);
+                  if (t > m) { m = t; arg = i; }
+                }
+            if (arg >= 0) acc[arg] += ld(dy, ((((int64_t)in * od + a) * oh + b) * ow + e) * c + ch, dt);
+          }
+  for (int64_t i = 0; i < total; i++) st(dx, i, dt, acc[i]);
+  free(acc);
+  return B2C_OK;
+}

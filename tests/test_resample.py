@@ -92,3 +92,54 @@ def test_gpu_resample_autograd_vs_torch():
     torch.testing.assert_close(xo.grad.cpu(), xr.grad, rtol=1e-6, atol=1e-6)
     with pytest.raises(ValueError):
         B.nn.AvgPool3d(3)(xo)
+
+
+def _maxpool_cases():
+    return [((2, 8, 9, 10, 11), 3, 2, 1), ((1, 16, 8, 8, 8), 3, 2, 1), ((2, 3, 7, 6, 5), 2, 2, 0), ((1, 8, 6, 6, 6), 3, 1, 1)]
+
+
+def check_maxpool(dev, dtype):
+    """b2c_maxpool3d fwd / bwd against F.max_pool3d (FID_ResNet.py:129 uses k3 s2 p1)."""
+    import torch
+    import torch.nn.functional as F
+    import b200conv3d.functional as BF
+    for shape, k, s, p in _maxpool_cases():
+        g = torch.Generator().manual_seed(sum(shape))
+        x = torch.randn(*shape, generator=g).to(dtype).float()
+        x[0, 0, :2, :2, :2] = 1.5                      # ties: the gradient must go to the first maximum only
+        xr = x.clone().requires_grad_(True)
+        yr = F.max_pool3d(xr, k, s, p)
+        gy = torch.randn(*yr.shape, generator=g).to(dtype).float()
+        yr.backward(gy)
+        xg = x.clone().to(dev).to(dtype).requires_grad_(True)
+        y = BF.max_pool3d(xg, k, s, p)
+        y.backward(gy.to(dev).to(dtype))
+        assert y.shape == yr.shape
+        assert torch.equal(y.float().cpu(), yr.detach()), (shape, k, s, p)
+        tol = 1e-6 if dtype == torch.float32 else 1e-2
+        assert (xg.grad.float().cpu() - xr.grad).abs().max().item() <= tol * xr.grad.abs().max().item(), (shape, k, s, p)
+
+
+def test_maxpool_oracle_library_vs_torch(oracle_path):
+    import os
+    import subprocess
+    import sys
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import sys, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+from b200conv3d import _lib
+_lib.use_library(%r, host=True)
+import test_resample as T
+T.check_maxpool("cpu", torch.float32)
+print("HOST-OK")
+''' % (os.path.join(ROOT, "3d-gan_b200"), os.path.join(ROOT, "tests"), oracle_path)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert "HOST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@pytest.mark.gpu
+def test_gpu_maxpool_vs_torch():
+    import torch
+    check_maxpool("cuda", torch.float32)
+    check_maxpool("cuda", torch.bfloat16)

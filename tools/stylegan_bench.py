@@ -129,11 +129,23 @@ def run(kind, a):
         for q in G.parameters():
             q.requires_grad = False
 
+    def fwd_bwd(i):          # "G fwd+bwd alone"
+        for q in G.parameters():
+            q.requires_grad = True
+        G.zero_grad()
+        with amp():
+            img = G(noise())[0]
+            img.float().square().mean().backward()
+        for q in G.parameters():
+            q.requires_grad = False
+
     for q in list(D.parameters()) + list(G.parameters()):
         q.requires_grad = False
     out = {"impl": kind}
     ms = timed(fwd, a.warmup, a.steps)
     out["gen_fwd"] = {"ms": ms, "voxels_per_sec": a.batch * VOX * 1e3 / ms}
+    ms = timed(fwd_bwd, a.warmup, a.steps)
+    out["gen_fwd_bwd"] = {"ms": ms, "voxels_per_sec": a.batch * VOX * 1e3 / ms}
     ms = timed(train, a.warmup, a.steps)
     out["train_step"] = {"ms": ms, "steps_per_sec": 1e3 / ms, "voxels_per_sec": a.batch * VOX * 1e3 / ms}
     out["peak_mem_gb"] = torch.cuda.max_memory_allocated() / 2 ** 30
@@ -211,7 +223,7 @@ def main():
     for kind in ["ours"] + (["witness"] if a.witness else []):
         r = run(kind, a)
         res["runs"].append(r)
-        show("gen_fwd", r), show("train_step", r)
+        show("gen_fwd", r), show("gen_fwd_bwd", r), show("train_step", r)
         print("%-8s peak mem %.1f GB" % (kind, r["peak_mem_gb"]))
         if a.v1:
             r1 = run_v1(kind, a)
