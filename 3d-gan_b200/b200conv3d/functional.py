@@ -432,7 +432,7 @@ def _conv3d_s2d(x, weight, bias, g, act, slope):
 # (index_select) expansion: every original tap is the sum of the blocks it was copied to.
 FOLD = [True]
 FOLD_K1 = [True]
-FOLD_1CH = [True]
+FOLD_1CH = [False]     # measured: the folded 8 <-> 8*C GEMMs leave the tensor-core path (K = 8) - 278 -> 408 ms/step
 
 
 def _fold_factor(x, weight, g):
@@ -441,8 +441,9 @@ def _fold_factor(x, weight, g):
     cout, cin, kd, kh, kw = weight.shape
     if g.stride != (1, 1, 1) or g.dil != (1, 1, 1) or kw % 2 == 0 or g.pad[2] != kw // 2:
         return 1
-    # one-channel 1x1x1 convs (fromrgb / torgb, stylegan.py:542-546,758): an outer / inner product per voxel, pure
-    # HBM traffic.  Folded by 8 they are 8 <-> 8*C block-diagonal GEMMs with 16-byte and 512-byte rows.
+    # experiment knob (off): one-channel 1x1x1 convs (fromrgb / torgb, stylegan.py:542-546,758) folded by 8 into
+    # 8 <-> 8*C block-diagonal GEMMs.  The forward of torgb gains (1.07 -> 0.22 ms) but the K = 8 weight / data
+    # gradients fall to the CUDA-core kernels; the one-channel lowering of csrc/thin.cu stays the default.
     if FOLD_1CH[0] and (kd, kh, kw) == (1, 1, 1) and min(cin, cout) == 1 and max(cin, cout) % 8 == 0 \
             and max(cin, cout) <= 32 and x.shape[4] % 8 == 0 and compute_dtype(x) == torch.bfloat16:
         return 8

@@ -184,9 +184,8 @@ def test_device_prefetcher_order_and_values():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("cfg", [(32, 32, 3, 24, 2), (16, 32, 3, 20, 4), (16, 8, 3, 16, 4), (8, 16, 5, 16, 4),
-                                 (64, 32, 1, 24, 2), (32, 16, 1, 16, 4), (1, 32, 1, 32, 8), (32, 1, 1, 24, 8)],
-                         ids=["32to32", "16to32_f4", "16to8_f4", "8to16_k5_f4", "64to32_k1", "32to16_k1_f4",
-                              "fromrgb_1to32_f8", "torgb_32to1_f8"])
+                                 (64, 32, 1, 24, 2), (32, 16, 1, 16, 4)],
+                         ids=["32to32", "16to32_f4", "16to8_f4", "8to16_k5_f4", "64to32_k1", "32to16_k1_f4"])
 def test_w_folded_conv_matches_plain_and_torch(cfg):
     """Narrow stride-1 convs run W-folded (F voxels along W folded into the channel axis, block-sparse
     expanded filter): same results as the unfolded launch and as stock torch fp32 (bf16 2e-2), forward,
