@@ -180,6 +180,8 @@ def run_ours(a):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL prints its version banner / debug lines to STDOUT by default; the contract is ONE JSON line there
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.lib()                                   # raises if libb2c.so is missing
     torch.manual_seed(1234 + rank)
