@@ -182,7 +182,17 @@ def run_ours(a):
     if world > 1:
         # NCCL prints its version banner / debug lines to STDOUT by default; the contract is ONE JSON line there
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
+        sys.stdout.flush()
+        saved = os.dup(1)                     # belt and braces: fd 1 -> stderr while the communicator comes up
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     lib = _lib.lib()                                   # raises if libb2c.so is missing
     torch.manual_seed(1234 + rank)
     netG, netD = B.dcgan.build(a.z, a.width, a.width, 128, dev)

@@ -33,6 +33,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout for the result line
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(0)
     model = B.fid_resnet.resnet50().to(dev)
