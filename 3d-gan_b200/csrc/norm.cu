@@ -76,7 +76,7 @@ struct BnBwdF {            // g = dy*act'(z);  f0 = g, f1 = g*xhat
 };
 
 template <typename T, int VEC, bool BWD>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, BWD ? 2 : 1)   // BWD: 140 registers left ONE resident CTA per SM (37 % of HBM)
 chan_reduce_stage1(const T* __restrict__ x, int64_t rows, int C, BnBwdF<T> f, float* __restrict__ ws,
                    int64_t rows_per_block) {
   extern __shared__ float sm[];           // [kThreads][2*VEC]
@@ -264,48 +264,58 @@ bn_act_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, const T* __restric
   }
 }
 
+// Four vectors of x and dy per thread are in flight per iteration (128 bytes a thread; at ~128 registers two
+// CTAs are resident, 64 KB per SM: two vectors left the pass at half of HBM).
 template <typename T, int VEC>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 bn_act_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ res,
                   T* __restrict__ dx, T* __restrict__ dres, int64_t nvec, int C, float inv_rows,
                   const float* __restrict__ mean, const float* __restrict__ invstd,
                   const float* __restrict__ scale, const float* __restrict__ shift,
                   const float* __restrict__ s1, const float* __restrict__ s2, int act, float slope) {
+  constexpr int U = 4;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  float sc[VEC], sh[VEC], mu[VEC], is[VEC], k1[VEC], k2[VEC];
+  float sc[VEC], sh[VEC], ka[VEC], kb[VEC];   // dx = sc * (g - k1 - xhat * k2) = sc * g + ka + kb * x
   int cc = -1;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += 2 * stride) {
-    const int64_t i2 = i + stride;
-    const bool two = i2 < nvec;
-    Pk<T, VEC> xa, xb, da, db, ra, rb;
-    xa.load(x, i * VEC); da.load(dy, i * VEC);
-    if (res) ra.load(res, i * VEC);
-    if (two) { xb.load(x, i2 * VEC); db.load(dy, i2 * VEC); if (res) rb.load(res, i2 * VEC); }
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += U * stride) {
+    Pk<T, VEC> xr[U], dr[U], rr[U];
 #pragma unroll
-    for (int u = 0; u < 2; u++) {
-      if (u == 1 && !two) break;
-      const int64_t off = (u ? i2 : i) * VEC;
+    for (int u = 0; u < U; u++) {
+      const int64_t iu = i + u * stride;
+      if (iu < nvec) {
+        xr[u].load(x, iu * VEC); dr[u].load(dy, iu * VEC);
+        if (res) rr[u].load(res, iu * VEC);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t iu = i + u * stride;
+      if (iu >= nvec) break;
+      const int64_t off = iu * VEC;
       const int c0 = (int)(off % C);
       if (c0 != cc) {
+        float mu[VEC], is[VEC], k1[VEC], k2[VEC];
         if (VEC > 1) {
           ldvecf<VEC>(scale, c0, sc, 1.f); ldvecf<VEC>(shift, c0, sh, 0.f); ldvecf<VEC>(mean, c0, mu, 0.f);
           ldvecf<VEC>(invstd, c0, is, 1.f); ldvecf<VEC>(s1, c0, k1, 0.f); ldvecf<VEC>(s2, c0, k2, 0.f);
         } else { sc[0] = scale[c0]; sh[0] = shift[c0]; mu[0] = mean[c0]; is[0] = invstd[c0]; k1[0] = s1[c0]; k2[0] = s2[c0]; }
 #pragma unroll
-        for (int k = 0; k < VEC; k++) { k1[k] *= inv_rows; k2[k] *= inv_rows; }
+        for (int k = 0; k < VEC; k++) {
+          kb[k] = -sc[k] * k2[k] * inv_rows * is[k];
+          ka[k] = -sc[k] * k1[k] * inv_rows - kb[k] * mu[k];
+        }
         cc = c0;
       }
       float xv[VEC], dv[VEC], rv[VEC], gv[VEC];
-      (u ? xb : xa).unpack(xv); (u ? db : da).unpack(dv);
-      if (res) (u ? rb : ra).unpack(rv);
+      xr[u].unpack(xv); dr[u].unpack(dv);
+      if (res) rr[u].unpack(rv);
 #pragma unroll
       for (int k = 0; k < VEC; k++) {
         float z = xv[k] * sc[k] + sh[k];
         if (res) z += rv[k];
         float g = dv[k] * act_dz(z, act, slope);
-        float xh = (xv[k] - mu[k]) * is[k];
         gv[k] = g;
-        xv[k] = sc[k] * (g - k1[k] - xh * k2[k]);
+        xv[k] = fmaf(sc[k], g, fmaf(kb[k], xv[k], ka[k]));
       }
       stvec<T, VEC>(dx, off, xv);
       if (dres) stvec<T, VEC>(dres, off, gv);
