@@ -2,7 +2,7 @@
 # usage: tools/gpurun_retry.sh TIMEOUT 'command'   - retries while the pod answers busy (exit 3)
 T=$1; shift
 for i in $(seq 1 12); do
-  /usr/local/graft/bin/gpurun --timeout "$T" -- "$@"
+  /usr/local/graft/bin/gpurun ${GPUS:+--gpus $GPUS} --timeout "$T" -- "$@"
   rc=$?
   [ $rc -ne 3 ] && exit $rc
   sleep 90
