@@ -1,7 +1,7 @@
 #!/bin/bash
 # usage: tools/gpurun_retry.sh TIMEOUT 'command'   - retries while the pod answers busy (exit 3)
 T=$1; shift
-for i in $(seq 1 12); do
+for i in $(seq 1 ${TRIES:-12}); do
   /usr/local/graft/bin/gpurun ${GPUS:+--gpus $GPUS} --timeout "$T" -- "$@"
   rc=$?
   [ $rc -ne 3 ] && exit $rc
