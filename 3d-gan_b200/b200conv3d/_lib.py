@@ -94,6 +94,7 @@ _SIGNATURES = {
     "b2c_adain_bwd_apply": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp]),
     "b2c_maxpool3d_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_maxpool3d_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b2c_depth_to_space2": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
 EXPORTS = tuple(_SIGNATURES)
 

@@ -315,12 +315,15 @@ class _ConvFn(Function):
             gyb = gz
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            wp = _packed_filter(w, desc, PASS_DGRAD, cd)
-            dxb = torch.empty_like(xb)
-            ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_DGRAD), xb)
-            with _dev(xb), _timed("dgrad", desc, g.fold):
-                check(L.b2c_conv3d_dgrad(C.byref(desc), _ptr(gyb), _ptr(wp), _ptr(dxb), _ptr(ws),
-                                         ws.numel(), _stream(xb)), "conv3d_dgrad")
+            if _dgrad_merge_applies(g, xb, w, cd):
+                dxb = _dgrad_phase_merged(gyb, w, tuple(xb.shape), cd)
+            else:
+                wp = _packed_filter(w, desc, PASS_DGRAD, cd)
+                dxb = torch.empty_like(xb)
+                ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_DGRAD), xb)
+                with _dev(xb), _timed("dgrad", desc, g.fold):
+                    check(L.b2c_conv3d_dgrad(C.byref(desc), _ptr(gyb), _ptr(wp), _ptr(dxb), _ptr(ws),
+                                             ws.numel(), _stream(xb)), "conv3d_dgrad")
             dx = from_ndhwc(dxb)
             if ctx.x_dtype == torch.float32 and cd != torch.float32:
                 dx = from_ndhwc(cast(dxb, torch.float32))
@@ -522,6 +525,113 @@ def conv_transpose3d(x, weight, bias=None, stride=1, padding=0, output_padding=0
         raise NotImplementedError("b200conv3d.conv_transpose3d: groups=%d is not supported" % groups)
     g = Geom(True, tuple(weight.shape[2:]), stride, padding, dilation, output_padding)
     return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+
+
+# ---- phase-merged stride-2 transposed conv for narrow outputs -------------------------------------
+# The up-sampling layers of stylegan.py:262-282 are `conv_transpose3d(k = 3, stride 2)` with 32 / 64 output
+# channels.  In the library's scatter form that is 8 sub-pixel problems of 1 .. 8 taps with N = Cout <= 64
+# columns each: one 128-byte TMA row per 64 x 32 MACs, 77 TFLOP/s on 64 -> 32 at 64^3 -> 129^3.  The 8 phases
+# read the SAME input voxels (offsets 0 / -1 per axis), so they are merged into one stride-1 convolution
+# `Cin -> 8*Cout` with a 2x2x2 kernel (zero where a phase has no tap: 27 of 64 slots are live) on the
+# (in + 1)^3 lattice, followed by ONE depth-to-space pass.  2.4x the MACs, at the tensor pipe's wide-N rate.
+# The result is returned on the even-sized grid 2*(in + 1): its last plane / row / column is exactly zero
+# (odd phase of the last lattice point), so the FIR that follows takes one voxel less of trailing padding
+# instead of a cropped (strided) tensor.
+PHASE_MERGE = [True]
+
+_pm_index_cache = {}
+
+
+def _pm_index(device):
+    """idx[r, u] = tap kd*9 + kh*3 + kw of the 3^3 transposed-conv filter that connects input voxel j + u - 1 to
+    output voxel 2*j + r (per axis: kappa = 2*(1 - u) + r), or 27 (a zero slot)."""
+    key = str(device)
+    if key not in _pm_index_cache:
+        idx = torch.full((8, 8), 27, dtype=torch.long)
+        for r in range(8):
+            for u in range(8):
+                ks = [2 * (1 - ((u >> s) & 1)) + ((r >> s) & 1) for s in (2, 1, 0)]
+                if all(0 <= k < 3 for k in ks):
+                    idx[r, u] = (ks[0] * 3 + ks[1]) * 3 + ks[2]
+        _pm_index_cache[key] = idx.reshape(-1).to(device)
+    return _pm_index_cache[key]
+
+
+def phase_merge_applies(x, weight):
+    """weight: conv_transpose3d layout [Cin, Cout, 3, 3, 3]; stride 2, padding 0."""
+    if not PHASE_MERGE[0] or x.dim() != 5 or tuple(weight.shape[2:]) != (3, 3, 3):
+        return False
+    cin, cout = weight.shape[0], weight.shape[1]
+    return cin % 8 == 0 and cout % 8 == 0 and cin >= 16 and 8 * cout <= 512 and x.is_cuda \
+        and compute_dtype(x) == torch.bfloat16
+
+
+def phase_merged_filter(weight):
+    """[Cin, Cout, 3,3,3] (transposed-conv layout) -> [8*Cout, Cin, 2,2,2] (conv layout), phase-major channels."""
+    cin, cout = weight.shape[0], weight.shape[1]
+    w = weight.permute(1, 0, 2, 3, 4).reshape(cout, cin, 27)
+    w = torch.cat([w, w.new_zeros(cout, cin, 1)], dim=2)
+    w = w.index_select(2, _pm_index(weight.device)).reshape(cout, cin, 8, 8)
+    return w.permute(2, 0, 1, 3).reshape(8 * cout, cin, 2, 2, 2)
+
+
+def _d2s_raw(src, shape_out, c, dt, inverse):
+    """src NDHWC-contiguous; z side [n,jd,jh,jw,8c], y side [n,od,oh,ow,c]; shape_out = the destination's."""
+    dst = torch.empty(shape_out, dtype=src.dtype, device=src.device)
+    zs, ys = (shape_out, src.shape) if inverse else (src.shape, shape_out)
+    with _dev(src):
+        check(_lib.lib().b2c_depth_to_space2(_ptr(src), _ptr(dst), zs[0], zs[1], zs[2], zs[3], c, ys[1], ys[2], ys[3],
+                                             dt, 1 if inverse else 0, _stream(src)), "depth_to_space2")
+    return dst
+
+
+class _D2SFn(Function):
+    """z [N, 8*C, J, J, J] (phase-major channels) -> y [N, C, od, oh, ow], y[2j + r] = z[j, r], cropped to `out`."""
+
+    @staticmethod
+    def forward(ctx, z, out):
+        _check_device(z)
+        cd = _keep_dtype(z)
+        zb = to_ndhwc(z.detach(), cd)
+        n, jd, jh, jw, c8 = zb.shape
+        ctx.meta = (tuple(zb.shape), cd, z.dtype)
+        yb = _d2s_raw(zb, (n, out[0], out[1], out[2], c8 // 8), c8 // 8, _dt(cd), False)
+        return from_ndhwc(yb)
+
+    @staticmethod
+    def backward(ctx, gy):
+        zshape, cd, z_dtype = ctx.meta
+        gz = from_ndhwc(_d2s_raw(to_ndhwc(gy, cd), zshape, zshape[4] // 8, _dt(cd), True))
+        return (gz if z_dtype == cd else gz.to(z_dtype)), None
+
+
+def conv_transpose3d_s2(x, weight, even=False):
+    """`conv_transpose3d(x, weight, stride=2, padding=0)` for a 3^3 filter as ONE stride-1 `Cin -> 8*Cout` conv with
+    a 2x2x2 kernel on the (in + 1)^3 lattice + depth-to-space (b2c_depth_to_space2).  `even`: return the even grid
+    2*(in + 1) per axis, whose last plane / row / column is exactly zero, instead of the 2*in + 1 result."""
+    d, h, w = x.shape[2:]
+    z = conv3d(x, phase_merged_filter(weight), None, 1, 1)                  # [N, 8*Cout, d+1, h+1, w+1]
+    return _D2SFn.apply(z, tuple(2 * v + (2 if even else 1) for v in (d, h, w)))
+
+
+def _dgrad_phase_merged(gyb, w, dshape, cd):
+    """dgrad of `conv3d(k = 3, stride 2, padding 0)` with a narrow input (stylegan.py:257-260 down-sampling convs:
+    32@129^3 -> 64@64^3 ran its sub-pixel scatter form at 77 TFLOP/s): the same merged conv + depth-to-space,
+    written straight into the odd-sized dx.  gyb NDHWC [N, o, o, o, Cout]; w [Cout, Cin, 3,3,3]; returns NDHWC dx."""
+    with torch.no_grad():
+        z = conv3d(from_ndhwc(gyb), phase_merged_filter(w.detach().float()), None, 1, 1)
+        zb = to_ndhwc(z, cd)
+        return _d2s_raw(zb, dshape, dshape[4], _dt(cd), False)
+
+
+def _dgrad_merge_applies(g, xb, w, cd):
+    if not PHASE_MERGE[0] or g.transposed or tuple(w.shape[2:]) != (3, 3, 3) or cd != torch.bfloat16:
+        return False
+    if g.stride != (2, 2, 2) or g.pad != (0, 0, 0) or g.dil != (1, 1, 1):
+        return False
+    cout, cin = w.shape[0], w.shape[1]
+    # every input voxel must lie on the even grid of the (out + 1)^3 lattice: in <= 2 * (out + 1)
+    return cin % 8 == 0 and cout % 8 == 0 and cout >= 16 and 8 * cin <= 512 and xb.is_cuda
 
 
 # -------------------------------------------------------------- batch norm

@@ -87,8 +87,15 @@ def conv3d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight
     # padding (:262-282); the reference's FIR gain is up**2 in 3-D as well - kept
     lo, hi = lo - (k - 1), hi - (k - up)
     trim = max(min(-lo, -hi), 0)
-    y = _conv(x, w.transpose(0, 1), stride=up, padding=trim, transpose=True, flip_weight=not flip_weight)
-    y = fir(y, padding=pads(lo + trim, hi + trim), gain=up ** 2)
+    wt = w.transpose(0, 1)
+    if up == 2 and trim == 0 and hi >= 1 and BF.phase_merge_applies(x, wt):
+        # narrow up-sampling conv: the 8 sub-pixel phases as ONE stride-1 conv + depth-to-space, on the even
+        # grid whose last plane is zero - the FIR takes one voxel less of trailing padding instead
+        y = BF.conv_transpose3d_s2(x, wt.flip([2, 3, 4]) if flip_weight else wt, even=True)
+        y = BF.upfirdn3d(y, f, flip_filter=flip_filter, padding=[lo, hi - 1] * 3, gain=up ** 2)
+    else:
+        y = _conv(x, wt, stride=up, padding=trim, transpose=True, flip_weight=not flip_weight)
+        y = fir(y, padding=pads(lo + trim, hi + trim), gain=up ** 2)
     if down > 1:
         y = fir(y, down=down)
     return bias_act(y, bias, act=act)

@@ -338,3 +338,71 @@ extern "C" int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_
   cudaStream_t st = static_cast<cudaStream_t>(s);
   return dt == B2C_BF16 ? maxpool_t<__nv_bfloat16>(true, x, dy, dx, g, st) : maxpool_t<float>(true, x, dy, dx, g, st);
 }
+
+// ---- depth-to-space by 2 (and its adjoint) on NDHWC ---------------------------------------------------------
+// z [n, jd, jh, jw, 8*c] (phase-major channels: r = rd*4 + rh*2 + rw) <-> y [n, od, oh, ow, c] with
+// y[n, 2*j + r, :] = z[n, j, r, :], od <= 2*jd (cropped).  The second half of the phase-merged transposed
+// convolution of b200conv3d/functional.py.  A thread moves one 16-byte channel vector; the z side is read /
+// written fully contiguously, the y side in runs of 2*c elements (rw = 0, 1 are neighbours along w).
+namespace b2c {
+namespace {
+struct D2sGeo { int64_t n; int jd, jh, jw, c, od, oh, ow; };
+
+template <typename T, int VEC, bool INV>
+__global__ void __launch_bounds__(kThr) d2s_kernel(D2sGeo g, const T* __restrict__ src, T* __restrict__ dst, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = g.c / VEC;
+  const int ci = (int)(idx % cv) * VEC;
+  int64_t v = idx / cv;
+  const int r = (int)(v & 7); v >>= 3;
+  const int jw = (int)(v % g.jw); v /= g.jw;
+  const int jh = (int)(v % g.jh); v /= g.jh;
+  const int jd = (int)(v % g.jd);
+  const int64_t n = v / g.jd;
+  const int od = 2 * jd + (r >> 2), oh = 2 * jh + ((r >> 1) & 1), ow = 2 * jw + (r & 1);
+  const bool in = od < g.od && oh < g.oh && ow < g.ow;
+  const int64_t zo = idx * VEC;
+  const int64_t yo = (((n * g.od + od) * g.oh + oh) * (int64_t)g.ow + ow) * g.c + ci;
+  float t[VEC];
+  if (!INV) {                       // z -> y
+    if (!in) return;
+    rs_ld<T, VEC>(src + zo, t);
+    rs_st<T, VEC>(dst + yo, t);
+  } else {                          // y -> z (zero where the even grid overhangs y)
+    if (in) rs_ld<T, VEC>(src + yo, t);
+    else {
+#pragma unroll
+      for (int i = 0; i < VEC; i++) t[i] = 0.f;
+    }
+    rs_st<T, VEC>(dst + zo, t);
+  }
+}
+
+template <typename T>
+int d2s_t(bool inv, const void* src, void* dst, const D2sGeo& g, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const bool vec = g.c % V == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+  const int64_t total = g.n * g.jd * g.jh * g.jw * 8 * (g.c / (vec ? V : 1));
+  if (total == 0) return B2C_OK;
+  const int64_t b = cdiv(total, (int64_t)kThr);
+  if (b > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  const unsigned blocks = (unsigned)b;
+  const T* sp = static_cast<const T*>(src); T* dp = static_cast<T*>(dst);
+  if (!inv) { if (vec) d2s_kernel<T, V, false><<<blocks, kThr, 0, st>>>(g, sp, dp, total); else d2s_kernel<T, 1, false><<<blocks, kThr, 0, st>>>(g, sp, dp, total); }
+  else      { if (vec) d2s_kernel<T, V, true><<<blocks, kThr, 0, st>>>(g, sp, dp, total); else d2s_kernel<T, 1, true><<<blocks, kThr, 0, st>>>(g, sp, dp, total); }
+  return launched();
+}
+}  // namespace
+}  // namespace b2c
+
+extern "C" int b2c_depth_to_space2(const void* src, void* dst, int64_t n, int jd, int jh, int jw, int c, int od, int oh,
+                                   int ow, int dt, int inverse, b2c_stream s) {
+  using namespace b2c;
+  if (!src || !dst || !dt_ok(dt) || n < 0 || jd <= 0 || jh <= 0 || jw <= 0 || c <= 0 || od <= 0 || oh <= 0 || ow <= 0 ||
+      od > 2 * jd || oh > 2 * jh || ow > 2 * jw)
+    return B2C_ERR_INVALID;
+  D2sGeo g{n, jd, jh, jw, c, od, oh, ow};
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? d2s_t<__nv_bfloat16>(inverse != 0, src, dst, g, st) : d2s_t<float>(inverse != 0, src, dst, g, st);
+}

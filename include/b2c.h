@@ -293,6 +293,17 @@ int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_t n, int d,
                       int h, int w, int c, int k, int stride, int pad, int dtype,
                       b2c_stream);
 
+/* ---- depth-to-space by 2 on NDHWC (second half of the phase-merged stride-2   *
+ * transposed convolution; replaces the sub-pixel scatter of F.conv_transpose3d  *
+ * at stylegan.py:170 for the narrow up-sampling layers of stylegan.py:262-282)  *
+ * z [n,jd,jh,jw,8*c], channel = r*c + ch, r = rd*4 + rh*2 + rw                  *
+ * y [n,od,oh,ow,c],  y[n, 2*j + r] = z[n, j, r];  od <= 2*jd (cropped).         *
+ * inverse == 0: z -> y (elements of y beyond 2*j are not touched: none exist);  *
+ * inverse != 0: y -> z, zero where the even grid overhangs y (the adjoint).     */
+int b2c_depth_to_space2(const void* src, void* dst, int64_t n, int jd, int jh,
+                        int jw, int c, int od, int oh, int ow, int dtype,
+                        int inverse, b2c_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -847,3 +847,27 @@ int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_t n, int d,
   free(acc);
   return B2C_OK;
 }
+
+/* ---- depth-to-space by 2 on NDHWC (include/b2c.h; phase-merged form of F.conv_transpose3d, stylegan.py:170) ---- */
+int b2c_depth_to_space2(const void* src, void* dst, int64_t n, int jd, int jh, int jw, int c, int od, int oh, int ow,
+                        int dt, int inverse, b2c_stream s) {
+  (void)s;
+  if (!src || !dst || !dt_ok(dt) || n < 0 || jd <= 0 || jh <= 0 || jw <= 0 || c <= 0 || od <= 0 || oh <= 0 || ow <= 0 ||
+      od > 2 * jd || oh > 2 * jh || ow > 2 * jw)
+    return B2C_ERR_INVALID;
+  for (int64_t in = 0; in < n; in++)
+    for (int a = 0; a < jd; a++)
+      for (int b = 0; b < jh; b++)
+        for (int e = 0; e < jw; e++)
+          for (int r = 0; r < 8; r++) {
+            int o0 = 2 * a + (r >> 2), o1 = 2 * b + ((r >> 1) & 1), o2 = 2 * e + (r & 1);
+            int inside = o0 < od && o1 < oh && o2 < ow;
+            for (int ch = 0; ch < c; ch++) {
+              int64_t zi = (((((int64_t)in * jd + a) * jh + b) * jw + e) * 8 + r) * c + ch;
+              int64_t yi = ((((int64_t)in * od + o0) * oh + o1) * ow + o2) * c + ch;
+              if (!inverse) { if (inside) st(dst, yi, dt, ld(src, zi, dt)); }
+              else st(dst, zi, dt, inside ? ld(src, yi, dt) : 0.0);
+            }
+          }
+  return B2C_OK;
+}

@@ -143,3 +143,50 @@ def test_gpu_maxpool_vs_torch():
     import torch
     check_maxpool("cuda", torch.float32)
     check_maxpool("cuda", torch.bfloat16)
+
+
+def check_d2s(dev, dtype):
+    """b2c_depth_to_space2 (both directions, cropped and even grids) against the view / permute formulation."""
+    import torch
+    import b200conv3d.functional as BF
+    for n, c, j, crop in ((2, 8, (3, 4, 5), (1, 1, 1)), (1, 16, (2, 2, 3), (0, 0, 0)), (2, 3, (2, 3, 2), (1, 0, 1)),
+                          (1, 32, (4, 1, 2), (0, 1, 0))):
+        g = torch.Generator().manual_seed(n + c + sum(j))
+        out = tuple(2 * a - b for a, b in zip(j, crop))
+        z = torch.randn(n, 8 * c, *j, generator=g).to(dtype).float()
+        zr = z.clone().requires_grad_(True)
+        yr = zr.reshape(n, 2, 2, 2, c, *j).permute(0, 4, 5, 1, 6, 2, 7, 3).reshape(n, c, 2 * j[0], 2 * j[1], 2 * j[2])
+        yr = yr[:, :, :out[0], :out[1], :out[2]]
+        gy = torch.randn(*yr.shape, generator=g).to(dtype).float()
+        yr.backward(gy)
+        zg = z.clone().to(dev).to(dtype).requires_grad_(True)
+        y = BF._D2SFn.apply(zg, out)
+        y.backward(gy.to(dev).to(dtype))
+        assert y.shape == yr.shape
+        assert torch.equal(y.float().cpu(), yr.detach()), (n, c, j, crop)
+        assert torch.equal(zg.grad.float().cpu(), zr.grad), (n, c, j, crop)
+
+
+def test_d2s_oracle_library_vs_torch(oracle_path):
+    import os
+    import subprocess
+    import sys
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import sys, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+from b200conv3d import _lib
+_lib.use_library(%r, host=True)
+import test_resample as T
+T.check_d2s("cpu", torch.float32)
+print("HOST-OK")
+''' % (os.path.join(ROOT, "3d-gan_b200"), os.path.join(ROOT, "tests"), oracle_path)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert "HOST-OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@pytest.mark.gpu
+def test_gpu_d2s_vs_torch():
+    import torch
+    check_d2s("cuda", torch.float32)
+    check_d2s("cuda", torch.bfloat16)

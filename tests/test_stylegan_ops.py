@@ -286,3 +286,78 @@ print("HOST-OK")
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_gpu_adain_vs_torch(dtype):
     check_adain("cuda", dtype)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cin,cout,res", [(64, 32, 12), (32, 16, 9), (128, 64, 6)])
+def test_gpu_phase_merged_up_conv_matches_scatter_form_and_oracle(cin, cout, res):
+    """The narrow up-sampling layers (stylegan.py:262-282: conv_transpose3d k3 s2 + FIR) run as ONE stride-1
+    `Cin -> 8*Cout` 2x2x2 conv + depth-to-space on the even grid (functional.conv_transpose3d_s2_even).  Result
+    and both gradients against the library's sub-pixel scatter form on the same bf16 inputs, and against the
+    fp32 formulation of oracle/ref_stylegan_ops.py."""
+    sys.path.insert(0, os.path.join(ROOT, "3d-gan_b200"))
+    import b200conv3d.functional as BF
+    import b200conv3d.stylegan_ops as P
+    g = torch.Generator().manual_seed(cin + cout + res)
+    x = torch.randn(2, cin, res, res, res, generator=g)
+    w = torch.randn(cout, cin, 3, 3, 3, generator=g) / (cin * 27) ** 0.5
+    gy = torch.randn(2, cout, 2 * res, 2 * res, 2 * res, generator=g)
+    f = P.make_resample_filter()
+
+    def run(merge):
+        BF.PHASE_MERGE[0] = merge
+        try:
+            xs = x.cuda().requires_grad_(True)
+            ws = w.cuda().requires_grad_(True)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                y = P.conv3d_resample(xs, ws, f=f.cuda(), up=2, padding=1, flip_weight=False)
+            y.backward(gy.cuda().to(y.dtype))
+            return y.float().cpu(), xs.grad.float().cpu(), ws.grad.float().cpu()
+        finally:
+            BF.PHASE_MERGE[0] = True
+
+    assert BF.phase_merge_applies(x.cuda().bfloat16(), w.transpose(0, 1).cuda())
+    got, ref = run(True), run(False)
+    xr, wr = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    yo = O.conv3d_resample(xr, wr, f=f, up=2, padding=1, flip_weight=False)
+    yo.backward(gy)
+    gold = (yo.detach(), xr.grad, wr.grad)
+    assert got[0].shape == ref[0].shape == gold[0].shape
+    l2 = lambda a, b: ((a - b).norm() / b.norm().clamp_min(1e-30)).item()   # noqa: E731
+    for a, b, o, name in zip(got, ref, gold, ("y", "dx", "dw")):
+        # bf16 tolerance: both forms round the conv result to bf16 once before the FIR
+        assert l2(a, o) < max(1.2e-2, 1.5 * l2(b, o)), (name, l2(a, o), l2(b, o))
+        assert l2(a, b) < 1.5e-2, (name, l2(a, b))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cin,cout,res", [(32, 64, 13), (64, 128, 12), (8, 16, 7)])
+def test_gpu_phase_merged_dgrad_of_down_conv(cin, cout, res):
+    """dgrad of the narrow stride-2 3^3 convs (stylegan.py:257-260) = the same merged conv + depth-to-space,
+    written into the (odd or even) input grid: against the sub-pixel scatter form and fp32 torch."""
+    sys.path.insert(0, os.path.join(ROOT, "3d-gan_b200"))
+    import b200conv3d.functional as BF
+    g = torch.Generator().manual_seed(cin + cout + res)
+    x = torch.randn(2, cin, res, res, res, generator=g)
+    w = torch.randn(cout, cin, 3, 3, 3, generator=g) / (cin * 27) ** 0.5
+    xr = x.clone().requires_grad_(True)
+    yr = torch.nn.functional.conv3d(xr, w, stride=2)
+    gy = torch.randn(*yr.shape, generator=g)
+    yr.backward(gy)
+
+    def run(merge):
+        BF.PHASE_MERGE[0] = merge
+        try:
+            xs = x.cuda().bfloat16().requires_grad_(True)
+            ws = w.cuda().requires_grad_(True)
+            y = BF.conv3d(xs, ws, None, 2, 0)
+            y.backward(gy.cuda().bfloat16())
+            return xs.grad.float().cpu(), ws.grad.float().cpu()
+        finally:
+            BF.PHASE_MERGE[0] = True
+
+    (dx1, dw1), (dx0, dw0) = run(True), run(False)
+    l2 = lambda a, b: ((a - b).norm() / b.norm().clamp_min(1e-30)).item()   # noqa: E731
+    assert dx1.shape == xr.grad.shape
+    assert l2(dx1, xr.grad) < max(8e-3, 1.5 * l2(dx0, xr.grad)), (l2(dx1, xr.grad), l2(dx0, xr.grad))
+    assert l2(dx1, dx0) < 8e-3 and l2(dw1, dw0) < 1e-5     # (8 channels: the catch-all direct wgrad accumulates with atomics)
