@@ -268,8 +268,15 @@ static Geo gemm_geo(int64_t rows, int nout, int kin) {
   return p;
 }
 
+static bool is_pointwise(const Geo& g);
+static int pw_wgrad_blocks(int64_t rows);
+
 size_t thin_workspace(const Geo& g, int kind) {
   size_t b = col_bytes(g);
+  if (kind == 2 && is_pointwise(g)) {          // partial column sums of the pointwise weight gradient
+    const size_t pw = align256((size_t)pw_wgrad_blocks(rows_of(g)) * g.sc * sizeof(float));
+    if (pw > b) b = pw;
+  }
   if (kind == 2) {
     b += align256((size_t)g.sc * thin_kp(g) * sizeof(float));
     b += tc_wgrad_workspace(gemm_geo(rows_of(g), g.sc, thin_kp(g)));
@@ -294,8 +301,123 @@ static int im2col_launch(const Geo& g, const void* big, void* col, cudaStream_t 
   return launched();
 }
 
+// ---------------------------------------------------------------------------
+// 1x1x1 filters on a one-channel tensor (fromrgb / torgb, stylegan.py:542-546,758; their gradients):
+// no reduction over taps is left, the three passes are an outer product, a row dot product and a
+// weighted column sum - pure HBM streams.  Through the K = 16 GEMM lowering they ran at 1 TB/s.
+static bool is_pointwise(const Geo& g) {
+  for (int i = 0; i < 3; i++) if (g.k[i] != 1 || g.s[i] != 1 || g.p[i] != 0) return false;
+  return g.sd == g.bd && g.sh == g.bh && g.sw == g.bw && g.sc % 8 == 0 && g.sc <= 512;
+}
+
+// out[v][a] = act(big[v] * w[a] + bias[a]); w[a] = wp[a * wstride]
+__global__ void __launch_bounds__(256)
+pw_outer_kernel(const bf16* __restrict__ big, const bf16* __restrict__ wp, int wstride, const float* __restrict__ bias,
+                bf16* __restrict__ out, int sc, int act, float slope, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = sc >> 3;
+  const int c0 = (int)(idx % cv) * 8;
+  const int64_t v = idx / cv;
+  const float x = __bfloat162float(big[v]);
+  float o[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++)
+    o[i] = act_f(fmaf(x, __bfloat162float(wp[(int64_t)(c0 + i) * wstride]), bias ? bias[c0 + i] : 0.f), act, slope);
+  Vec<bf16> pk; pk.pack(o); pk.store(out + v * sc + c0);
+}
+
+// out[v] = act(bias[0] + sum_a small[v][a] * w[a]); LPR lanes share a row (power of two <= 32)
+__global__ void __launch_bounds__(256)
+pw_rowdot_kernel(const bf16* __restrict__ small, const bf16* __restrict__ wp, int wstride, const float* __restrict__ bias,
+                 bf16* __restrict__ out, int sc, int lpr, int act, float slope, int64_t rows) {
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t v = gid / lpr;
+  const int l = (int)(gid % lpr);
+  float acc = 0.f;
+  if (v < rows)
+    for (int c0 = l * 8; c0 < sc; c0 += lpr * 8) {
+      Vec<bf16> pk; pk.load(small + v * sc + c0);
+      float x[8]; pk.unpack(x);
+#pragma unroll
+      for (int i = 0; i < 8; i++) acc = fmaf(x[i], __bfloat162float(wp[(int64_t)(c0 + i) * wstride]), acc);
+    }
+  for (int o = lpr >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (v < rows && l == 0) out[v] = __float2bfloat16_rn(act_f(acc + (bias ? bias[0] : 0.f), act, slope));
+}
+
+// part[b][a] = sum over the rows of slab b of small[v][a] * big[v]   (deterministic two-stage column sum)
+__global__ void __launch_bounds__(256)
+pw_wgrad_stage1(const bf16* __restrict__ small, const bf16* __restrict__ big, float* __restrict__ part, int sc,
+                int64_t rows, int64_t rows_per_block) {
+  extern __shared__ float pw_sm[];           // [256][8]
+  const int cv = sc >> 3;
+  const int lanes = cv < 256 ? cv : 256, rstep = 256 / lanes;
+  const int lane = threadIdx.x % lanes, rl = threadIdx.x / lanes;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+  for (int g0 = 0; g0 < cv; g0 += lanes) {
+    const int c0 = (g0 + lane) * 8;
+    float a[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = 0.f;
+    if (g0 + lane < cv && rl < rstep)
+      for (int64_t rb = r0 + rl; rb < r1; rb += 4 * (int64_t)rstep) {
+        Vec<bf16> pk[4]; float xs[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int64_t r = rb + (int64_t)u * rstep;
+          if (r < r1) { pk[u].load(small + r * sc + c0); xs[u] = __bfloat162float(big[r]); }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          if (rb + (int64_t)u * rstep >= r1) break;
+          float y[8]; pk[u].unpack(y);
+#pragma unroll
+          for (int i = 0; i < 8; i++) a[i] = fmaf(y[i], xs[u], a[i]);
+        }
+      }
+    float* my = pw_sm + threadIdx.x * 8;
+#pragma unroll
+    for (int i = 0; i < 8; i++) my[i] = a[i];
+    __syncthreads();
+    if (rl == 0 && g0 + lane < cv) {
+      for (int j = 1; j < rstep; j++) {
+        const float* o = pw_sm + (j * lanes + lane) * 8;
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[i] += o[i];
+      }
+#pragma unroll
+      for (int i = 0; i < 8; i++) part[(int64_t)blockIdx.x * sc + c0 + i] = a[i];
+    }
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(256)
+pw_wgrad_stage2(const float* __restrict__ part, int nblocks, int sc, float* __restrict__ dw) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= sc) return;
+  double acc = 0.0;
+  for (int b = 0; b < nblocks; b++) acc += part[(int64_t)b * sc + a];
+  dw[a] = (float)acc;
+}
+static int pw_wgrad_blocks(int64_t rows) {
+  int64_t nb = (int64_t)num_sms() * 4;
+  if (nb > rows) nb = rows;
+  return (int)(nb < 1 ? 1 : nb);
+}
+
 int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, const float* bias, int act,
                 float slope, void* ws, size_t wsb, cudaStream_t st) {
+  if (is_pointwise(g)) {
+    const int64_t total = rows_of(g) * (g.sc / 8);
+    if (total == 0) return B2C_OK;
+    if (cdiv(total, 256) > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+    pw_outer_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(static_cast<const bf16*>(big), static_cast<const bf16*>(wp),
+                                                                thin_kp(g), bias, static_cast<bf16*>(out_small), g.sc, act,
+                                                                slope, total);
+    return launched();
+  }
   if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
     const int rc = tc_thin_gather_launch(g, big, wp, thin_kp(g), out_small, bias, act, slope, st);
     if (rc != B2C_ERR_UNSUPPORTED) return rc;
@@ -311,6 +433,18 @@ int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, 
 
 int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big, const float* bias, int act,
                  float slope, void* ws, size_t wsb, cudaStream_t st) {
+  if (is_pointwise(g)) {
+    const int64_t rows = rows_of(g);
+    if (rows == 0) return B2C_OK;
+    int lpr = 1;
+    while (lpr < g.sc / 8 && lpr < 32) lpr <<= 1;
+    if (cdiv(rows * lpr, 256) > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+    // scatter packing: wp[t][a], one tap -> w[a] = wp[a]
+    pw_rowdot_kernel<<<(unsigned)cdiv(rows * lpr, 256), 256, 0, st>>>(static_cast<const bf16*>(small),
+                                                                     static_cast<const bf16*>(wp), 1, bias,
+                                                                     static_cast<bf16*>(out_big), g.sc, lpr, act, slope, rows);
+    return launched();
+  }
   if (!ws || wsb < thin_workspace(g, 1)) return B2C_ERR_WORKSPACE;
   const int Kp = thin_kp(g);
   ConvPlan plan;
@@ -334,6 +468,20 @@ int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big,
 int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void* ws, size_t wsb, cudaStream_t st,
                bool flip) {
   if (!ws || wsb < thin_workspace(g, 2)) return B2C_ERR_WORKSPACE;
+  if (is_pointwise(g)) {
+    const int64_t rows = rows_of(g);
+    const int nb = pw_wgrad_blocks(rows);
+    if ((size_t)nb * g.sc * sizeof(float) > wsb) return B2C_ERR_WORKSPACE;
+    float* part = static_cast<float*>(ws);
+    if (rows > 0)
+      pw_wgrad_stage1<<<nb, 256, 256 * 8 * sizeof(float), st>>>(static_cast<const bf16*>(small),
+                                                               static_cast<const bf16*>(big), part, g.sc, rows,
+                                                               cdiv(rows, (int64_t)nb));
+    int rc = launched();
+    if (rc) return rc;
+    pw_wgrad_stage2<<<(unsigned)cdiv(g.sc, 256), 256, 0, st>>>(part, rows > 0 ? nb : 0, g.sc, dw);
+    return launched();
+  }
   const int Kp = thin_kp(g), T = g.taps();
   if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
     const int frc = tc_thin_wgrad_launch(g, small, big, dw, flip ? 1 : 0, ws, wsb, st);

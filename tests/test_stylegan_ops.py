@@ -361,3 +361,37 @@ def test_gpu_phase_merged_dgrad_of_down_conv(cin, cout, res):
     assert dx1.shape == xr.grad.shape
     assert l2(dx1, xr.grad) < max(8e-3, 1.5 * l2(dx0, xr.grad)), (l2(dx1, xr.grad), l2(dx0, xr.grad))
     assert l2(dx1, dx0) < 8e-3 and l2(dw1, dw0) < 1e-5     # (8 channels: the catch-all direct wgrad accumulates with atomics)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("c,shape", [(32, (2, 5, 6, 7)), (16, (1, 9, 4, 3)), (96, (3, 4, 4, 5)), (64, (1, 16, 16, 16))])
+def test_gpu_pointwise_one_channel_convs(c, shape):
+    """fromrgb (1 -> C) and torgb (C -> 1) 1x1x1 convs (stylegan.py:542-546,758) take the pointwise kernels of
+    csrc/thin.cu (outer product / row dot / weighted column sum): forward with the fused bias + activation and
+    all three gradients against fp32 torch on the same bf16-rounded operands."""
+    sys.path.insert(0, os.path.join(ROOT, "3d-gan_b200"))
+    import b200conv3d.functional as BF
+    n, d, h, w = shape
+    g = torch.Generator().manual_seed(c + sum(shape))
+    bf = lambda t: t.bfloat16().float()   # noqa: E731
+    l2 = lambda a, b: ((a.float().cpu() - b).norm() / b.norm().clamp_min(1e-30)).item()   # noqa: E731
+    for cin, cout, act in ((1, c, "lrelu"), (c, 1, None)):
+        x = bf(torch.randn(n, cin, d, h, w, generator=g))
+        wt = bf(torch.randn(cout, cin, 1, 1, 1, generator=g) / cin ** 0.5)
+        b = torch.randn(cout, generator=g) * 0.1
+        gy = bf(torch.randn(n, cout, d, h, w, generator=g))
+        xr, wr, br = (t.clone().requires_grad_(True) for t in (x, wt, b))
+        yr = torch.nn.functional.conv3d(xr, wr, br)
+        if act:
+            yr = torch.nn.functional.leaky_relu(yr, 0.2)
+        yr.backward(gy)
+        xs = x.cuda().bfloat16().requires_grad_(True)
+        ws, bs = wt.cuda().requires_grad_(True), b.cuda().requires_grad_(True)
+        y = BF.conv3d(xs, ws, bs, 1, 0, act=act, slope=0.2)
+        y.backward(gy.cuda().bfloat16())
+        assert y.dtype == torch.bfloat16 and y.shape == yr.shape
+        assert l2(y, yr.detach()) < 4e-3, (cin, cout, l2(y, yr.detach()))
+        # lrelu': taken from the rounded output; elements within rounding of the kink may flip -> L2 criteria
+        assert l2(xs.grad, xr.grad) < 8e-3, (cin, cout, "dx", l2(xs.grad, xr.grad))
+        assert l2(ws.grad, wr.grad) < 8e-3, (cin, cout, "dw", l2(ws.grad, wr.grad))
+        assert l2(bs.grad, br.grad) < 8e-3, (cin, cout, "db", l2(bs.grad, br.grad))
