@@ -10,9 +10,11 @@ demodulation).  What runs where:
   * dense convolutions / transposed convolutions -> b2c_conv3d_* (tcgen05 path in bf16);
   * pad + depthwise 4x4x4 FIR + decimation / zero-insertion (`_upfirdn3d_ref`,
     stylegan.py:172-200) -> ONE b2c_fir3d pass (no materialised padding, no groups=C conv);
-  * style scaling of the input, demodulation coefficients, noise / bias / activation -> ATen
-    elementwise ops on NDHWC tensors for now (fusing them into the conv prologue / epilogue is
-    the `in_scale` / `out_scale` / `addend` extension sketched in SURVEY §8(b)).
+  * style scaling of the input -> ONE b2c_modulate pass; demodulation, noise, bias and activation ->
+    ONE b2c_mod_epilogue pass (`synthesis_conv`); the demodulation coefficients are a small fp32 GEMM;
+  * narrow stride-2 up-sampling convs (and the data gradient of the down-sampling convs) -> the
+    phase-merged form of functional.conv_transpose3d_s2: one stride-1 `Cin -> 8*Cout` conv +
+    b2c_depth_to_space2;  `fromrgb` / `torgb` 1x1x1 convs -> the pointwise kernels of csrc/thin.cu.
 
 With `b200conv3d.install()` the reference's own stylegan.py reaches the same kernels through
 `F.conv3d` / `F.conv_transpose3d`, except its `groups=C` FIR call, which this module replaces.

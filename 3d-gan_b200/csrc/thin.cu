@@ -310,40 +310,86 @@ static bool is_pointwise(const Geo& g) {
   return g.sd == g.bd && g.sh == g.bh && g.sw == g.bw && g.sc % 8 == 0 && g.sc <= 512;
 }
 
-// out[v][a] = act(big[v] * w[a] + bias[a]); w[a] = wp[a * wstride]
+// out[v][a] = act(big[v] * w[a] + bias[a]); w[a] = wp[a * wstride].  A thread owns one 8-channel group (its
+// weights and bias stay in registers) and walks the rows of its block's slab, 256 / (sc/8) rows per pass.
 __global__ void __launch_bounds__(256)
 pw_outer_kernel(const bf16* __restrict__ big, const bf16* __restrict__ wp, int wstride, const float* __restrict__ bias,
-                bf16* __restrict__ out, int sc, int act, float slope, int64_t total) {
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
+                bf16* __restrict__ out, int sc, int act, float slope, int64_t rows, int64_t rows_per_block) {
   const int cv = sc >> 3;
-  const int c0 = (int)(idx % cv) * 8;
-  const int64_t v = idx / cv;
-  const float x = __bfloat162float(big[v]);
-  float o[8];
+  const int lanes = cv < 256 ? cv : 256, rstep = 256 / lanes;
+  const int lane = threadIdx.x % lanes, rl = threadIdx.x / lanes;
+  if (rl >= rstep) return;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+  for (int c0 = lane * 8; c0 < sc; c0 += lanes * 8) {
+    float w[8], bb[8];
 #pragma unroll
-  for (int i = 0; i < 8; i++)
-    o[i] = act_f(fmaf(x, __bfloat162float(wp[(int64_t)(c0 + i) * wstride]), bias ? bias[c0 + i] : 0.f), act, slope);
-  Vec<bf16> pk; pk.pack(o); pk.store(out + v * sc + c0);
+    for (int i = 0; i < 8; i++) {
+      w[i] = __bfloat162float(wp[(int64_t)(c0 + i) * wstride]);
+      bb[i] = bias ? bias[c0 + i] : 0.f;
+    }
+    for (int64_t rb = r0 + rl; rb < r1; rb += 4 * (int64_t)rstep) {
+      float x[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int64_t r = rb + (int64_t)u * rstep;
+        x[u] = r < r1 ? __bfloat162float(big[r]) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int64_t r = rb + (int64_t)u * rstep;
+        if (r >= r1) break;
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) o[i] = act_f(fmaf(x[u], w[i], bb[i]), act, slope);
+        Vec<bf16> pk; pk.pack(o); pk.store(out + r * sc + c0);
+      }
+    }
+  }
 }
 
-// out[v] = act(bias[0] + sum_a small[v][a] * w[a]); LPR lanes share a row (power of two <= 32)
+// out[v] = act(bias[0] + sum_a small[v][a] * w[a]); LPR lanes share a row (power of two <= 32, sc <= 512: at most
+// two 8-channel groups per lane, weights in registers); a thread has four rows in flight.
 __global__ void __launch_bounds__(256)
 pw_rowdot_kernel(const bf16* __restrict__ small, const bf16* __restrict__ wp, int wstride, const float* __restrict__ bias,
-                 bf16* __restrict__ out, int sc, int lpr, int act, float slope, int64_t rows) {
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t v = gid / lpr;
-  const int l = (int)(gid % lpr);
-  float acc = 0.f;
-  if (v < rows)
-    for (int c0 = l * 8; c0 < sc; c0 += lpr * 8) {
-      Vec<bf16> pk; pk.load(small + v * sc + c0);
-      float x[8]; pk.unpack(x);
+                 bf16* __restrict__ out, int sc, int lpr, int act, float slope, int64_t rows, int64_t rows_per_block) {
+  const int l = threadIdx.x % lpr, rl = threadIdx.x / lpr, rstep = 256 / lpr;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+  const int ca = l * 8, cb = ca + lpr * 8;
+  const bool ha = ca < sc, hb = cb < sc;
+  float wa[8], wb[8];
 #pragma unroll
-      for (int i = 0; i < 8; i++) acc = fmaf(x[i], __bfloat162float(wp[(int64_t)(c0 + i) * wstride]), acc);
+  for (int i = 0; i < 8; i++) {
+    wa[i] = ha ? __bfloat162float(wp[(int64_t)(ca + i) * wstride]) : 0.f;
+    wb[i] = hb ? __bfloat162float(wp[(int64_t)(cb + i) * wstride]) : 0.f;
+  }
+  const float b0 = bias ? bias[0] : 0.f;
+  // block-uniform trip count (the row offset rl is added inside): every lane reaches the full-mask shuffles
+  for (int64_t base = r0; base < r1; base += 4 * (int64_t)rstep) {
+    const int64_t rb = base + rl;
+    Vec<bf16> pa[4], pb[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int64_t r = rb + (int64_t)u * rstep;
+      pa[u].zero(); pb[u].zero();
+      if (r < r1) {
+        if (ha) pa[u].load(small + r * sc + ca);
+        if (hb) pb[u].load(small + r * sc + cb);
+      }
     }
-  for (int o = lpr >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  if (v < rows && l == 0) out[v] = __float2bfloat16_rn(act_f(acc + (bias ? bias[0] : 0.f), act, slope));
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int64_t r = rb + (int64_t)u * rstep;
+      float xa[8], xb[8];
+      pa[u].unpack(xa); pb[u].unpack(xb);
+      float acc = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; i++) acc = fmaf(xa[i], wa[i], fmaf(xb[i], wb[i], acc));
+      for (int o = lpr >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (r < r1 && l == 0) out[r] = __float2bfloat16_rn(act_f(acc + b0, act, slope));
+    }
+  }
 }
 
 // part[b][a] = sum over the rows of slab b of small[v][a] * big[v]   (deterministic two-stage column sum)
@@ -362,15 +408,15 @@ pw_wgrad_stage1(const bf16* __restrict__ small, const bf16* __restrict__ big, fl
 #pragma unroll
     for (int i = 0; i < 8; i++) a[i] = 0.f;
     if (g0 + lane < cv && rl < rstep)
-      for (int64_t rb = r0 + rl; rb < r1; rb += 4 * (int64_t)rstep) {
-        Vec<bf16> pk[4]; float xs[4];
+      for (int64_t rb = r0 + rl; rb < r1; rb += 8 * (int64_t)rstep) {
+        Vec<bf16> pk[8]; float xs[8];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < 8; u++) {
           const int64_t r = rb + (int64_t)u * rstep;
           if (r < r1) { pk[u].load(small + r * sc + c0); xs[u] = __bfloat162float(big[r]); }
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < 8; u++) {
           if (rb + (int64_t)u * rstep >= r1) break;
           float y[8]; pk[u].unpack(y);
 #pragma unroll
@@ -410,12 +456,11 @@ static int pw_wgrad_blocks(int64_t rows) {
 int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, const float* bias, int act,
                 float slope, void* ws, size_t wsb, cudaStream_t st) {
   if (is_pointwise(g)) {
-    const int64_t total = rows_of(g) * (g.sc / 8);
-    if (total == 0) return B2C_OK;
-    if (cdiv(total, 256) > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
-    pw_outer_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(static_cast<const bf16*>(big), static_cast<const bf16*>(wp),
-                                                                thin_kp(g), bias, static_cast<bf16*>(out_small), g.sc, act,
-                                                                slope, total);
+    const int64_t rows = rows_of(g);
+    if (rows == 0) return B2C_OK;
+    const int nb = pw_wgrad_blocks(rows) * 2;
+    pw_outer_kernel<<<nb, 256, 0, st>>>(static_cast<const bf16*>(big), static_cast<const bf16*>(wp), thin_kp(g), bias,
+                                        static_cast<bf16*>(out_small), g.sc, act, slope, rows, cdiv(rows, (int64_t)nb));
     return launched();
   }
   if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
@@ -437,12 +482,11 @@ int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big,
     const int64_t rows = rows_of(g);
     if (rows == 0) return B2C_OK;
     int lpr = 1;
-    while (lpr < g.sc / 8 && lpr < 32) lpr <<= 1;
-    if (cdiv(rows * lpr, 256) > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+    while (2 * lpr < g.sc / 8 && lpr < 32) lpr <<= 1;        // one or two 8-channel groups per lane (sc <= 512)
+    const int nb = pw_wgrad_blocks(rows) * 2;
     // scatter packing: wp[t][a], one tap -> w[a] = wp[a]
-    pw_rowdot_kernel<<<(unsigned)cdiv(rows * lpr, 256), 256, 0, st>>>(static_cast<const bf16*>(small),
-                                                                     static_cast<const bf16*>(wp), 1, bias,
-                                                                     static_cast<bf16*>(out_big), g.sc, lpr, act, slope, rows);
+    pw_rowdot_kernel<<<nb, 256, 0, st>>>(static_cast<const bf16*>(small), static_cast<const bf16*>(wp), 1, bias,
+                                         static_cast<bf16*>(out_big), g.sc, lpr, act, slope, rows, cdiv(rows, (int64_t)nb));
     return launched();
   }
   if (!ws || wsb < thin_workspace(g, 1)) return B2C_ERR_WORKSPACE;
