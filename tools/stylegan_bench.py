@@ -78,6 +78,17 @@ def kernel_table(fn, top=30):
     return {"total_ms": sum(r[1] for r in rows), "rows": rows[:top]}
 
 
+def op_table(fn, top=25):
+    """ATen ops (not b2c launches) by device time, with input shapes: which glue op owns the generic kernels."""
+    from torch.profiler import ProfilerActivity, profile
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof:
+        fn(0)
+        torch.cuda.synchronize()
+    tab = prof.key_averages(group_by_input_shape=True).table(sort_by="self_cuda_time_total", row_limit=top,
+                                                             max_name_column_width=40, max_shapes_column_width=70)
+    return tab
+
+
 def build(kind, a, dev="cuda"):
     p = argparse.Namespace(z_size=a.z, filterG=a.cb, filterD=a.cb, device=dev, stylegan2=True, stylegan=False)
     torch.manual_seed(1234)
@@ -155,6 +166,8 @@ def run(kind, a):
     if a.kernels:
         out["gen_fwd"]["kernels"] = kernel_table(fwd)
         out["train_step"]["kernels"] = kernel_table(train)
+    if a.ops:
+        print(op_table(train), file=sys.stderr)
     del G, D, optD, optG, reals
     torch.cuda.empty_cache()
     return out
@@ -214,6 +227,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--witness", action="store_true", help="also time stock torch layers (cuDNN) under bf16 autocast")
+    ap.add_argument("--ops", action="store_true", help="ATen op table of one train step (stderr)")
     ap.add_argument("--kernels", action="store_true", help="per-kernel time table of one call (torch.profiler)")
     ap.add_argument("--v1", action="store_true", help="also the v1-like generator styleGAN_gen")
     ap.add_argument("--json", default="")
