@@ -282,7 +282,10 @@ class _ConvFn(Function):
         desc = _desc(g, tuple(xb.shape), cout, cd, _force_algo[0])
         L = _lib.lib()
         wp = _packed_filter(w, desc, PASS_FWD, cd)
-        yl, y = alloc_out(desc.y.n, desc.y.d, desc.y.h, desc.y.w, desc.y.c, cd, x.device)
+        # a W-folded launch (g.fold > 1) writes [N,D,H,W/F,F*C] = the same bytes as [N,D,H,W,C]: the result is
+        # allocated in the UNFOLDED logical shape, so the caller gets a fresh tensor, not a view of one (an in-place
+        # op on a view - nn.ReLU(True), `y.add_(x)` - makes autograd rebase it: a clone and two strided copies)
+        yl, y = alloc_out(desc.y.n, desc.y.d, desc.y.h, desc.y.w * g.fold, desc.y.c // g.fold, cd, x.device)
         bf = None
         if bias is not None:
             bf = bias.detach()
@@ -513,7 +516,7 @@ def _conv3d_folded(x, weight, bias, g, act, slope, f):
     b2 = None if bias is None else bias.repeat(f)
     g2 = Geom(False, tuple(w2.shape[2:]), 1, (g.pad[0], g.pad[1], 1 if w2.shape[4] == 3 else 0), 1)
     g2.fold = f
-    return _unfold_w(_ConvFn.apply(_fold_w(x, f), w2, b2, g2, act, slope), f)
+    return _ConvFn.apply(_fold_w(x, f), w2, b2, g2, act, slope)       # unfolded by _ConvFn (same storage)
 
 
 def conv_transpose3d(x, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1,

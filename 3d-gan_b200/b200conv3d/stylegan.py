@@ -227,7 +227,9 @@ class SynthesisBlock(tnn.Module):
             y = self.skip(x)
             x = self.conv0(x, next(w_iter), **kw())
             x = self.conv1(x, next(w_iter), **kw())
-            x = y.add_(x)
+            # (stylegan.py: `y.add_(x)`) out of place when y is a view - the W-folded skip conv returns one, and an
+            # in-place op on a view makes autograd rebase it (CopySlices: a clone and two strided copies per pass)
+            x = y + x if y._is_view() else y.add_(x)
         else:
             x = self.conv0(x, next(w_iter), **kw())
             x = self.conv1(x, next(w_iter), **kw())
@@ -334,7 +336,9 @@ class DiscriminatorBlock(tnn.Module):
             y = self.skip(x)
             x = self.conv0(x)
             x = self.conv1(x)
-            x = y.add_(x)
+            # (stylegan.py: `y.add_(x)`) out of place when y is a view - the W-folded skip conv returns one, and an
+            # in-place op on a view makes autograd rebase it (CopySlices: a clone and two strided copies per pass)
+            x = y + x if y._is_view() else y.add_(x)
         else:
             x = self.conv0(x)
             x = self.conv1(x)
