@@ -16,6 +16,7 @@ import stylegan_bench as SB  # noqa: E402
 
 SEEN = collections.Counter()
 ANY = False
+THRESH = 1 << 26
 
 
 class Spy(TorchDispatchMode):
@@ -25,7 +26,7 @@ class Spy(TorchDispatchMode):
                  "transpose", "unsqueeze", "squeeze", "aten.t.", "unbind", "split", "narrow", "zeros", "ones")
         if (ANY and not any(v in name for v in views)) or any(k in name for k in ("copy_", "clone", "_to_copy",
                                                                                    "contiguous", "add", "mul")):
-            big = [a for a in args if isinstance(a, torch.Tensor) and a.numel() >= (1 << 26)]
+            big = [a for a in args if isinstance(a, torch.Tensor) and a.numel() >= THRESH]
             if big:
                 fr = [f for f in traceback.extract_stack()[:-1] if "b200conv3d" in f.filename or "stylegan" in f.filename]
                 key = (name, tuple(big[0].shape), tuple(big[0].stride()), big[0].dtype,
@@ -57,9 +58,31 @@ def main_biggan():
         print("%6.2f Gelem  x%d  %s" % (b / 1e9, SEEN[k], k))
 
 
+def main_dcgan():
+    import b200conv3d as B
+    from b200conv3d.train import GanStep
+    torch.manual_seed(1234)
+    g, d = B.dcgan.build(512, 128, 128, 128, "cuda")
+    step = GanStep(g, d, 512, iterD=2, autocast_dtype=torch.bfloat16, seed=99)
+    reals = [torch.rand(32, 1, 128, 128, 128, device="cuda") * 2 - 1 for _ in range(2)]
+    for _ in range(2):
+        step.step(iter(reals))
+    torch.cuda.synchronize()
+    global THRESH
+    THRESH = 1 << 22
+    with Spy():
+        step.step(iter(reals))
+    torch.cuda.synchronize()
+    for k, n in sorted(SEEN.items(), key=lambda kv: -kv[1])[:40]:
+        print("x%d  %s" % (n, k))
+
+
 def main():
+    global ANY
+    if len(sys.argv) > 1 and sys.argv[1] == "dcgan":
+        ANY = True
+        return main_dcgan()
     if len(sys.argv) > 1 and sys.argv[1] == "biggan":
-        global ANY
         ANY = True
         return main_biggan()
     a = argparse.Namespace(batch=8, cb=4096, z=512, iterD=2, steps=1, warmup=1, witness=False, kernels=False, v1=False,
