@@ -14,12 +14,13 @@ import contextlib
 
 import torch
 import torch.nn as tnn
+import torch.nn.utils.parametrize  # noqa: F401  (tnn.utils.parametrize.is_parametrized)
 import torch.optim as optim
 
 
 class GanStep:
     def __init__(self, netG, netD, z_size=512, lrG=5e-5, lrD=1e-4, hinge=False, iterD=2,
-                 autocast_dtype=torch.bfloat16, reducer_g=None, reducer_d=None, seed=None):
+                 autocast_dtype=torch.bfloat16, reducer_g=None, reducer_d=None, seed=None, batch_real_fake=True):
         from . import functional as BF
         BF.watch_optimizers()          # fused Adam does not bump Tensor._version (packed-filter cache)
         self.netG, self.netD = netG, netD
@@ -30,6 +31,14 @@ class GanStep:
         self.optimizerG = optim.Adam(netG.parameters(), lr=lrG, betas=(0.0, 0.9), fused=fused)
         self.autocast_dtype = autocast_dtype
         self.reducer_g, self.reducer_d = reducer_g, reducer_d
+        # one D pass over cat(real, fake) is the same arithmetic as two passes only when no layer couples the
+        # samples of a batch (BatchNorm, minibatch-std) or changes state per call (spectral norm runs one power
+        # iteration per forward: the reference's second pass sees the updated u)
+        coupled = (tnn.modules.batchnorm._BatchNorm,)
+        stateful = any(isinstance(m, coupled) or "MinibatchStd" in type(m).__name__ or
+                       tnn.utils.parametrize.is_parametrized(m) or hasattr(m, "weight_u") or hasattr(m, "weight_orig")
+                       for m in netD.modules())
+        self.batch_real_fake = bool(batch_real_fake) and self.device.type == "cuda" and not stateful
         self.gen = None
         if seed is not None:
             self.gen = torch.Generator(device=self.device)
@@ -55,13 +64,22 @@ class GanStep:
             self.reducer_d.begin()
         with self._amp():
             fake = self.netG(self.noise(real.shape[0]))
+            if self.batch_real_fake:
+                # netD has no batch-coupled layer (LayerNorm / spectral norm only): D(real) and D(fake) of
+                # trainer.py:222-241 as ONE pass over the concatenated batch - the same per-sample arithmetic, half
+                # the launches, one weight-gradient GEMM per layer with twice the reduction and no accumulate pass
+                n = real.shape[0]
+                out = self.netD(torch.cat([real.to(fake.dtype), fake]))
+                o_real, o_fake = out[:n], out[n:]
+            else:
+                o_real, o_fake = self.netD(real), self.netD(fake)
             if self.hinge:
-                errD_real = tnn.functional.relu(1.0 - self.netD(real)).mean()
-                errD_fake = tnn.functional.relu(1.0 + self.netD(fake)).mean()
+                errD_real = tnn.functional.relu(1.0 - o_real).mean()
+                errD_fake = tnn.functional.relu(1.0 + o_fake).mean()
                 errD = errD_fake + errD_real
             else:
-                errD_real = self.netD(real).mean()
-                errD_fake = self.netD(fake).mean()
+                errD_real = o_real.mean()
+                errD_fake = o_fake.mean()
                 errD = errD_fake - errD_real
             errD.backward()
         if self.reducer_d is not None:

@@ -45,6 +45,7 @@ def test_reference_golden_fp32():
     assert rel_err(dreal.reshape(-1), torch.from_numpy(gold["dreal0"])) < 1e-4
     # trainer.py:208-283, one D_step + G_step with the reference's noise draws
     step = B.train.GanStep(g, d, z, autocast_dtype=None)
+    assert step.batch_real_fake        # LayerNorm D: D(real), D(fake) run as ONE batched pass - checked against the golden
     step.noise = lambda n: torch.randn(n, z, 1, 1, 1).cuda()
     torch.manual_seed(77)
     er, ef = step.D_step(real.cuda())
@@ -143,6 +144,7 @@ def test_biggan_reference_golden_fp32():
     assert rel_err(fake[:, 0, ::8, ::8, ::8], torch.from_numpy(gold["fake0_sample"])) < 1e-4
     assert rel_err(dreal.reshape(-1), torch.from_numpy(gold["dreal0"])) < 1e-4
     step = B.train.GanStep(g, d, z, hinge=True, autocast_dtype=None)
+    assert not step.batch_real_fake    # spectral norm: one power iteration per forward, the two passes must stay two
     step.noise = lambda n: torch.randn(n, z, 1, 1, 1).cuda()
     torch.manual_seed(77)
     er, ef = step.D_step(real.cuda())
