@@ -62,6 +62,7 @@ _SIGNATURES = {
     "b2c_cast": (_i32, [_vp, _vp, _i64, _i32, _i32, _vp]),
     "b2c_stats_workspace": (_sz, [_i64, _i64]),
     "b2c_channel_stats": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "b2c_channel_stats_static": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp]),
     "b2c_bn_finalize": (_i32, [_vp, _vp, _i64, _i64, _f32, _f32, _vp, _vp, _vp, _vp,
                                _vp, _vp, _vp, _vp, _vp]),
     "b2c_bn_act_fwd": (_i32, [_vp, _vp, _vp, _i64, _i64, _i32, _vp, _vp, _i32, _f32, _vp]),

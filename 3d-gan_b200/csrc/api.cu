@@ -67,6 +67,7 @@ extern "C" const char* b2c_strerror(int c) {
     case B2C_ERR_WORKSPACE: return "workspace too small";
     case B2C_ERR_CUDA: return "CUDA error";
     case B2C_ERR_NO_DEVICE: return "no sm_100 device";
+    case B2C_ERR_STATIC_LIMIT: return "problem exceeds the static scratch limit (B2C_STATIC_SCRATCH_BYTES)";
     default: return "unknown error";
   }
 }

@@ -3,6 +3,8 @@
 // whole-sample LayerNorm (+activation) and backward, pointwise activations.
 // Every kernel moves 16-byte vectors, grids are sized in multiples of the SM
 // count, and all reductions are deterministic two-stage trees (no atomics).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b2c {
@@ -697,6 +699,54 @@ extern "C" int b2c_channel_stats(const void* x, int64_t rows, int64_t C, int dt,
   }
   BnBwdF<float> f{};
   return chan_reduce<float, false>(static_cast<const float*>(x), rows, C, f, sum, sq, ws, wsb, st);
+}
+
+// ---- allocation-free variant of b2c_channel_stats -------------------------------------------
+// The stage-1 partial sums live in a file-scope device array instead of a caller workspace, for
+// callers that cannot allocate (CUDA graph capture, serving loops).  Every device that loads the
+// library holds the array until exit.  In host code `g_stats_static` is only a stand-in for the
+// symbol: its device address is looked up once per device (cudaGetSymbolAddress with that device
+// current) and that pointer is what the kernels get.
+namespace b2c {
+static __device__ __align__(256) float g_stats_static[B2C_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+static int stats_static_ptr(float** out) {
+  static std::mutex mu;
+  static float* ptrs[64] = {};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return B2C_ERR_CUDA;
+  if (dev < 0 || dev >= 64) return B2C_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    if (cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_stats_static) != cudaSuccess || !p) {
+      (void)cudaGetLastError();
+      return B2C_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return B2C_OK;
+}
+}  // namespace b2c
+
+extern "C" int b2c_channel_stats_static(const void* x, int64_t rows, int64_t C, int dt, float* sum, float* sq,
+                                        b2c_stream s) {
+  if (!x || !sum || !sq || !dt_ok(dt) || rows <= 0 || C <= 0 || C > 0x7fffffff) return B2C_ERR_INVALID;
+  if (b2c_stats_workspace(rows, C) > (size_t)B2C_STATIC_SCRATCH_BYTES) return B2C_ERR_STATIC_LIMIT;
+  float* scratch = nullptr;
+  const int rc = stats_static_ptr(&scratch);
+  if (rc) return rc;
+  // Stage 1 overwrites every partial that stage 2 reads: nothing in the array has to start at zero.
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (dt == B2C_BF16) {
+    BnBwdF<__nv_bfloat16> f{};
+    return chan_reduce<__nv_bfloat16, false>(static_cast<const __nv_bfloat16*>(x), rows, C, f, sum, sq, scratch,
+                                             B2C_STATIC_SCRATCH_BYTES, st);
+  }
+  BnBwdF<float> f{};
+  return chan_reduce<float, false>(static_cast<const float*>(x), rows, C, f, sum, sq, scratch,
+                                   B2C_STATIC_SCRATCH_BYTES, st);
 }
 
 extern "C" int b2c_bn_finalize(const float* sum, const float* sq, int64_t count, int64_t C, float eps, float momentum,

@@ -40,6 +40,7 @@ typedef void* b2c_stream;
 #define B2C_ERR_WORKSPACE     -3   /* workspace too small                    */
 #define B2C_ERR_CUDA          -4   /* a CUDA runtime / driver call failed    */
 #define B2C_ERR_NO_DEVICE     -5   /* no sm_100 device / driver available    */
+#define B2C_ERR_STATIC_LIMIT  -6   /* problem larger than the static scratch */
 
 /* ---- dtypes --------------------------------------------------------- */
 #define B2C_BF16 0
@@ -142,6 +143,24 @@ size_t b2c_stats_workspace(int64_t rows, int64_t C);
 int b2c_channel_stats(const void* x, int64_t rows, int64_t C, int dtype,
                       float* sum, float* sqsum, void* ws, size_t ws_bytes,
                       b2c_stream);
+/* Allocation-free variant of b2c_channel_stats.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and arithmetic (bit-identical results) as
+ * b2c_channel_stats, but the stage-1 partial sums go to a file-scope
+ * `static __device__` array of B2C_STATIC_SCRATCH_BYTES (4 MiB) inside the
+ * library instead of a caller workspace; every GPU that loads the library holds
+ * that array until exit.  Calls no cudaMalloc / cudaFree / allocating routine.
+ * Limit: b2c_stats_workspace(rows, C) <= B2C_STATIC_SCRATCH_BYTES (C <= 885 at
+ * 148 SMs), otherwise B2C_ERR_STATIC_LIMIT.  All calls on a device share the
+ * array (it keeps the last call's partials; nothing needs clearing because
+ * stage 1 overwrites every slot stage 2 reads): calls that overlap on the GPU
+ * (different streams, or concurrent graph launches) RACE - serialise them.
+ * The first call on each device looks the array's address up
+ * (cudaGetSymbolAddress); make that call once before starting a capture.      */
+#define B2C_STATIC_SCRATCH_BYTES (4u << 20)
+int b2c_channel_stats_static(const void* x, int64_t rows, int64_t C, int dtype,
+                             float* sum, float* sqsum, b2c_stream);
 /* BatchNorm3d training-mode finalize (momentum update exactly like torch:
  * running = (1-m)*running + m*batch, unbiased var for running, biased for
  * normalisation).  Writes mean[C], invstd[C], scale[C]=gamma*invstd,

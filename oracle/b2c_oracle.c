@@ -93,6 +93,7 @@ const char* b2c_strerror(int c) {
     case B2C_ERR_WORKSPACE: return "workspace too small";
     case B2C_ERR_CUDA: return "CUDA error";
     case B2C_ERR_NO_DEVICE: return "no sm_100 device";
+    case B2C_ERR_STATIC_LIMIT: return "problem exceeds the static scratch limit (B2C_STATIC_SCRATCH_BYTES)";
     default: return "unknown error";
   }
 }
@@ -337,6 +338,12 @@ int b2c_channel_stats(const void* x, int64_t rows, int64_t C, int dt, float* sum
     sum[c] = (float)a; sq[c] = (float)b;
   }
   return B2C_OK;
+}
+/* Host stand-in of the allocation-free variant (no reference counterpart; the product
+ * version keeps its partials in a static device array - the oracle needs no scratch). */
+int b2c_channel_stats_static(const void* x, int64_t rows, int64_t C, int dt, float* sum, float* sq,
+                             b2c_stream s) {
+  return b2c_channel_stats(x, rows, C, dt, sum, sq, NULL, 0, s);
 }
 int b2c_bn_finalize(const float* sum, const float* sq, int64_t count, int64_t C, float eps,
                     float momentum, const float* gamma, const float* beta, float* mean,
