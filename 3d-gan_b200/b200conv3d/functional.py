@@ -134,6 +134,12 @@ def to_ndhwc(x, dtype):
         return p if x.dtype == dtype else cast(p, dtype)
     if x.dtype not in (torch.bfloat16, torch.float32):
         x = x.float()
+        p = x.permute(0, 2, 3, 4, 1)
+    if p.stride(4) == 1 and x.shape[1] > 1 and not x.is_contiguous():
+        # a channel slice / crop of NDHWC storage (`x[:, :Cout]`, utils.py:74): one strided copy of whole channel
+        # runs instead of the NCDHW round trip
+        pc = p.contiguous()
+        return pc if pc.dtype == dtype else cast(pc, dtype)
     xs = x if x.is_contiguous() else x.contiguous()
     n, c, d, h, w = xs.shape
     out = torch.empty((n, d, h, w, c), dtype=dtype, device=x.device)
@@ -209,7 +215,11 @@ _hook_installed = [False]
 
 
 def invalidate_packs(optimizer=None, *_a, **_k):
-    """Drop the cached packed filters of the parameters an optimizer just stepped (called from
+    """REQUIRED after any in-place write to a parameter that does not go through an optimizer step or bump
+    ``Tensor._version`` - ``p.data.clamp_()`` weight clipping, a hand-written EMA, ``dist.broadcast(p.data)`` -
+    call it without arguments.  (``PACK_DEBUG[0] = True`` re-packs on every cache hit and raises on a stale pack.)
+
+    Drop the cached packed filters of the parameters an optimizer just stepped (called from
     a global optimizer post-step hook: fused / foreach optimizers update parameters in place
     WITHOUT bumping ``Tensor._version``, so the version counter alone cannot be trusted).
     Parameters of other optimizers keep their packs (G's filters stay packed across the
@@ -239,8 +249,15 @@ def _packed_filter(w, desc, pas, dtype):
     spectral-norm weights are fresh tensors every forward, utils.py:13)."""
     state = (w.data_ptr(), w._version, _weights_epoch[0])
     cache = getattr(w, "_b2c_pack", None)
-    if cache is not None and cache[0] == state and (pas, dtype) in cache[1]:
-        return cache[1][(pas, dtype)]
+    # the packed layout depends on the whole descriptor (one-channel layers switch layout on stride / pad / algo,
+    # csrc/thin.cu thin_mode), not only on the pass: the same weight used through F.conv3d with another geometry
+    # gets its own pack
+    sub = (pas, dtype, int(desc.transposed), tuple(desc.k), tuple(desc.stride), tuple(desc.pad), tuple(desc.dil),
+           int(desc.algo))
+    if cache is not None and cache[0] == state and sub in cache[1]:
+        if PACK_DEBUG[0]:
+            _check_pack(w, desc, pas, cache[1][sub])
+        return cache[1][sub]
     wf = w.detach()
     if wf.dtype != torch.float32:
         wf = wf.float()
@@ -255,10 +272,24 @@ def _packed_filter(w, desc, pas, dtype):
         if cache is None or cache[0] != state:
             cache = (state, {})
             w._b2c_pack = cache
-        cache[1][(pas, dtype)] = out
+        cache[1][sub] = out
     except AttributeError:
         pass
     return out
+
+
+PACK_DEBUG = [False]     # set PACK_DEBUG[0] = True: every cache hit is re-packed and compared (finds stale packs)
+
+
+def _check_pack(w, desc, pas, cached):
+    L = _lib.lib()
+    wf = w.detach().float().contiguous()
+    fresh = torch.empty_like(cached)
+    with _dev(w):
+        check(L.b2c_filter_pack(C.byref(desc), pas, _ptr(wf), _ptr(fresh), _stream(w)), "filter_pack")
+    if not torch.equal(fresh, cached):
+        raise RuntimeError("b200conv3d: stale packed filter - the parameter was written through `.data` (weight "
+                           "clipping, EMA, broadcast) without b200conv3d.functional.invalidate_packs()")
 
 
 # ------------------------------------------------------------------- conv
@@ -353,11 +384,13 @@ def _act_id(act):
 def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=None, slope=0.0):
     """Drop-in for ``torch.nn.functional.conv3d`` (stylegan.py:168, nn.Conv3d.forward)
     with an optional fused activation epilogue (`act` a name or a b2c activation id)."""
-    if groups != 1:
-        raise NotImplementedError("b200conv3d.conv3d: groups=%d is not supported (only the dense "
-                                  "path is built; no cuDNN fallback)" % groups)
     if isinstance(padding, str):
         raise NotImplementedError("b200conv3d.conv3d: string padding %r is not supported" % padding)
+    if groups != 1:
+        if groups == x.shape[1] and tuple(weight.shape[:2]) == (groups, 1) and bias is None and act is None:
+            return _depthwise_fir(x, weight, stride, padding, dilation)
+        raise NotImplementedError("b200conv3d.conv3d: groups=%d is not supported (dense convs and the depthwise "
+                                  "one-filter FIR of stylegan.py:197 are built; no cuDNN fallback)" % groups)
     g = Geom(False, tuple(weight.shape[2:]), stride, padding, dilation)
     if _s2d_applies(x, weight, g):
         return _conv3d_s2d(x, weight, bias, g, _act_id(act), slope)
@@ -365,6 +398,30 @@ def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=
     if fold > 1:
         return _conv3d_folded(x, weight, bias, g, _act_id(act), slope, fold)
     return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+
+
+def _depthwise_fir(x, weight, stride, padding, dilation):
+    """``F.conv3d(x, f.repeat([C,1,1,1,1]), groups=C)`` of stylegan.py:195-197: every channel is filtered with the SAME
+    constant filter, which is what b2c_fir3d computes in one NDHWC pass (its taps are a host array).  One device ->
+    host read fetches the taps together with the proof that all channels share them; per-channel filters raise."""
+    s, p, d = _triple(stride), _triple(padding), _triple(dilation)
+    if len(set(s)) != 1 or d != (1, 1, 1):
+        raise NotImplementedError("depthwise conv3d: isotropic stride and dilation 1 only (stylegan.py:197)")
+    if weight.requires_grad:
+        raise NotImplementedError("depthwise conv3d: the filter is a constant buffer on the reference's path "
+                                  "(stylegan.py:462-465); a trainable depthwise filter is not supported")
+    k = tuple(weight.shape[2:])
+    if k[0] * k[1] * k[2] > 64:
+        raise NotImplementedError("depthwise conv3d: at most 64 taps")
+    w0 = weight[0, 0].detach().float()
+    same = (weight[:, 0].detach().float() == w0).all().float().reshape(1)
+    host = torch.cat([w0.reshape(-1), same]).cpu().tolist()
+    if host[-1] != 1.0:
+        raise NotImplementedError("depthwise conv3d with per-channel filters is not on the reference's path")
+    out_sp = tuple((a + 2 * pp - kk) // s[0] + 1 for a, pp, kk in zip(x.shape[2:], p, k))
+    if min(out_sp) <= 0:
+        raise RuntimeError("conv3d: computed output size is too small")
+    return _FirFn.apply(x, host[:-1], k, 1, s[0], p, out_sp)
 
 
 # ---- space-to-depth for one-channel stride-2 stems with many taps --------------------------------
@@ -894,7 +951,11 @@ def activation(x, act, slope=0.0, inplace=False):
 
 # --------------------------------------------------------------- x2 resampling (NDHWC)
 def _keep_dtype(x):
-    return x.dtype if x.dtype in (torch.bfloat16, torch.float32) else torch.float32
+    """bf16 / fp32 tensors keep their dtype; fp16 (the reference's autocast dtype, trainer.py:213) maps to bf16 like
+    compute_dtype does, so the resampling passes between two convs stay 2-byte; anything else is plumbing -> fp32."""
+    if x.dtype in (torch.bfloat16, torch.float32):
+        return x.dtype
+    return torch.bfloat16 if x.dtype == torch.float16 else torch.float32
 
 
 class _Up2Fn(Function):

@@ -110,7 +110,10 @@ class Tanh(_TTanh):
         return BF.activation(x, "tanh", 0.0, False)
 
 
-class AvgPool3d(tnn.AvgPool3d):
+_TAvgPool3d = tnn.AvgPool3d
+
+
+class AvgPool3d(_TAvgPool3d):
     """nn.AvgPool3d(2) of the BigGAN discriminator blocks (utils.py:113-116, biggan.py:86,92) as
     one NDHWC pass.  Other pooling configurations are not on the reference's path: they raise."""
 

@@ -15,6 +15,10 @@ backward pass:
 * :meth:`finish` (called before ``optimizer.step()``) joins the side stream and
   scatters the averaged gradients back.
 
+Several ``backward()`` calls between :meth:`begin` and :meth:`finish` are allowed (StyleGAN2Loss): a bucket whose
+gradients change after its reduce was launched is reduced again in :meth:`finish`.  Every rank must produce
+gradients for the same set of parameters in a pass (a bucket reduced on some ranks only would hang the collective).
+
 With the ``gloo`` backend (CPU tests) the same code runs synchronously.
 """
 import torch
@@ -41,7 +45,8 @@ class GradReducer:
             for p in b:
                 self.bucket_of[p] = bi
         self.pending = [0] * len(self.buckets)
-        self.inflight = []          # (bucket index, flat tensor, work handle)
+        self.inflight = {}          # bucket index -> (grads, flat tensor, work handle)
+        self.dirty = set()          # buckets whose gradients changed after their reduce was launched
         dev = self.params[0].device if self.params else torch.device("cpu")
         self.cuda = dev.type == "cuda"
         self.stream = torch.cuda.Stream(device=dev) if self.cuda else None
@@ -55,7 +60,8 @@ class GradReducer:
     def begin(self):
         """Call after the parameters' requires_grad flags are set for this pass
         (trainer.py:209-210,255-256) and before backward."""
-        self.inflight = []
+        self.inflight = {}
+        self.dirty = set()
         self._reset()
 
     def _hook(self, p):
@@ -65,6 +71,11 @@ class GradReducer:
         self.pending[bi] -= 1
         if self.pending[bi] == 0:
             self._launch(bi)
+        elif self.pending[bi] < 0:
+            # a further backward() between begin() and finish() (StyleGAN2Loss.step_D / step_G call it two or
+            # three times per optimizer step, stylegan.py:39-99) accumulated into p.grad AFTER this bucket's
+            # reduce was launched: the in-flight result is stale, finish() reduces the bucket again
+            self.dirty.add(bi)
 
     def _launch(self, bi):
         grads = [p.grad for p in self.buckets[bi] if p.requires_grad and p.grad is not None]
@@ -81,7 +92,7 @@ class GradReducer:
         else:
             flat = torch.cat([g.reshape(-1).float() for g in grads])
             work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-        self.inflight.append((grads, flat, work))
+        self.inflight[bi] = (grads, flat, work)
 
     def finish(self):
         """Join all bucket reductions, write back the rank-averaged gradients."""
@@ -91,15 +102,22 @@ class GradReducer:
             for bi in range(len(self.buckets)):
                 if 0 < self.pending[bi] < sum(1 for p in self.buckets[bi] if p.requires_grad):
                     self._launch(bi)
+            for bi in sorted(self.dirty):        # same order on every rank: the collectives stay matched
+                stale = self.inflight.pop(bi, None)
+                if stale is not None:
+                    stale[2].wait()
+                self._launch(bi)
             inv = 1.0 / self.world
-            for grads, flat, work in self.inflight:
+            for bi in sorted(self.inflight):
+                grads, flat, work = self.inflight[bi]
                 work.wait()                       # CUDA: the current stream waits for NCCL
                 if self.cuda:
                     flat.record_stream(torch.cuda.current_stream())
                 flat.mul_(inv)
                 for g, o in zip(grads, flat.split([g.numel() for g in grads])):
                     g.copy_(o.view_as(g))
-            self.inflight = []
+            self.inflight = {}
+            self.dirty = set()
         self._reset()
 
     def remove(self):

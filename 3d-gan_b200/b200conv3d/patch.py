@@ -26,8 +26,9 @@ _CLASS_MAP = {
     "LeakyReLU": (BN._TLeakyReLU, BN.LeakyReLU),
     "Tanh": (BN._TTanh, BN.Tanh),
     "MaxPool3d": (BN._TMaxPool3d, BN.MaxPool3d),          # FID_ResNet.py:129
+    "AvgPool3d": (BN._TAvgPool3d, BN.AvgPool3d),          # biggan.py:86,92
 }
-_stock_functional = {"conv3d": TF.conv3d, "conv_transpose3d": TF.conv_transpose3d}
+_stock_functional = {"conv3d": TF.conv3d, "conv_transpose3d": TF.conv_transpose3d, "interpolate": TF.interpolate}
 _installed = [False]
 
 
@@ -41,13 +42,31 @@ def _f_conv_transpose3d(input, weight, bias=None, stride=1, padding=0, output_pa
                                dilation)
 
 
+def _f_interpolate(input, size=None, scale_factor=None, mode="nearest", align_corners=None,
+                   recompute_scale_factor=None, antialias=False):
+    """``F.interpolate(x, scale_factor=2)`` on a 5-D tensor (nearest; biggan.py:26,31 through utils.py:78-80) is one
+    NDHWC pass of the library.  Every other use of F.interpolate keeps torch's implementation: it is not a
+    convolution and not on the path this package replaces (trilinear x2 of stylegan.py:1081 is SURVEY 8(f) n1)."""
+    sf = scale_factor
+    if isinstance(sf, (list, tuple)) and len(set(sf)) == 1:
+        sf = sf[0]
+    if (input.dim() == 5 and mode == "nearest" and size is None and sf is not None and not isinstance(sf, (list, tuple))
+            and float(sf) == 2.0 and (input.is_cuda or BF._lib.is_host())):
+        return BF.upsample_nearest2x(input)
+    return _stock_functional["interpolate"](input, size=size, scale_factor=scale_factor, mode=mode,
+                                            align_corners=align_corners,
+                                            recompute_scale_factor=recompute_scale_factor, antialias=antialias)
+
+
 def install():
     """Rebind the torch layer names the reference uses.  Idempotent."""
     for name, (_, ours) in _CLASS_MAP.items():
         setattr(tnn, name, ours)
     TF.conv3d = _f_conv3d
     TF.conv_transpose3d = _f_conv_transpose3d
+    TF.interpolate = _f_interpolate
     BF.watch_optimizers()
+    BF.invalidate_packs()
     _installed[0] = True
 
 
@@ -56,6 +75,7 @@ def uninstall():
         setattr(tnn, name, stock)
     TF.conv3d = _stock_functional["conv3d"]
     TF.conv_transpose3d = _stock_functional["conv_transpose3d"]
+    TF.interpolate = _stock_functional["interpolate"]
     _installed[0] = False
 
 
@@ -81,6 +101,7 @@ def convert(model):
     n = 0
     for m in model.modules():
         n += bool(_swap_class(m))
+    BF.invalidate_packs()          # parameters may have been loaded / broadcast through `.data` before the swap
     return n
 
 

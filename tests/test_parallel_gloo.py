@@ -78,3 +78,46 @@ def test_grad_reducer_world2_matches_global_batch():
             torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-6)   # D differs by one Adam step only through fp noise
     for a, b in zip(res[0][3], res[1][3]):
         torch.testing.assert_close(a, b, rtol=0, atol=0)             # replicas stay bit-identical
+
+
+def _worker_multi_backward(rank, world, port, q):
+    """Three backward() calls between begin() and finish(), as StyleGAN2Loss.step_D / step_G do
+    (stylegan.py:39-99): the rank-averaged gradient must be the average of the SUM of all three."""
+    sys.path.insert(0, os.path.join(ROOT, "3d-gan_b200"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from b200conv3d.parallel import GradReducer
+    _, d = _nets()
+    red = GradReducer(d, bucket_mb=0)
+    torch.manual_seed(7)
+    x = torch.rand(4, 1, 8, 8, 8)[rank * 2:rank * 2 + 2]
+    red.begin()
+    d(x).mean().backward()
+    (d(x * 0.5) ** 2).mean().backward()
+    (3.0 * d(-x)).mean().backward()
+    red.finish()
+    q.put((rank, [p.grad.detach().numpy().copy() for p in d.parameters()]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_grad_reducer_world2_several_backward_calls_per_step():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker_multi_backward, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(2)], key=lambda t: t[0])
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    _, d = _nets()
+    torch.manual_seed(7)
+    x = torch.rand(4, 1, 8, 8, 8)
+    d(x).mean().backward()
+    (d(x * 0.5) ** 2).mean().backward()
+    (3.0 * d(-x)).mean().backward()
+    for _, grads in res:
+        for a, p in zip(grads, d.parameters()):
+            torch.testing.assert_close(torch.from_numpy(a), p.grad, rtol=1e-4, atol=1e-6)
