@@ -41,8 +41,13 @@ class FirDesc(C.Structure):
                 ("dtype", C.c_int32)]
 
 
+STAT_NONE, STAT_CHANNEL, STAT_SAMPLE = 0, 1, 2
+
+
 class Fusion(C.Structure):
-    _fields_ = [("bias", C.c_void_p), ("act", C.c_int32), ("slope", C.c_float)]
+    """b2c_fusion (include/b2c.h); the three trailing fields default to "no statistics"."""
+    _fields_ = [("bias", C.c_void_p), ("act", C.c_int32), ("slope", C.c_float), ("stat_kind", C.c_int32),
+                ("stat_sum", C.c_void_p), ("stat_sqsum", C.c_void_p)]
 
 
 _vp, _i64, _i32, _f32, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_size_t
@@ -55,6 +60,7 @@ _SIGNATURES = {
     "b2c_filter_packed_bytes": (_sz, [_D, _i32]),
     "b2c_filter_pack": (_i32, [_D, _i32, _vp, _vp, _vp]),
     "b2c_conv3d_workspace": (_sz, [_D, _i32]),
+    "b2c_conv3d_stats_workspace": (_sz, [_D, _i32]),
     "b2c_conv3d_fwd": (_i32, [_D, _vp, _vp, _vp, C.POINTER(Fusion), _vp, _sz, _vp]),
     "b2c_conv3d_dgrad": (_i32, [_D, _vp, _vp, _vp, _vp, _sz, _vp]),
     "b2c_conv3d_wgrad": (_i32, [_D, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
@@ -73,6 +79,7 @@ _SIGNATURES = {
     "b2c_ln_workspace": (_sz, [_i64, _i64]),
     "b2c_ln_act_fwd": (_i32, [_vp, _vp, _i64, _i64, _i32, _vp, _vp, _f32, _i32, _f32,
                               _vp, _vp, _vp, _sz, _vp]),
+    "b2c_ln_act_fwd_stats": (_i32, [_vp, _vp, _i64, _i64, _i32, _vp, _vp, _f32, _i32, _f32, _vp, _vp, _vp, _vp, _vp]),
     "b2c_ln_act_bwd": (_i32, [_vp, _vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp,
                               _i32, _f32, _vp, _vp, _vp, _sz, _vp]),
     "b2c_act_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _f32, _vp]),
@@ -95,6 +102,7 @@ _SIGNATURES = {
     "b2c_adain_bwd_apply": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _vp]),
     "b2c_maxpool3d_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_maxpool3d_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b2c_window_w": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_depth_to_space2": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
 EXPORTS = tuple(_SIGNATURES)

@@ -87,6 +87,10 @@ class GBlockDeep(tnn.Module):
         self.bn1, self.bn2, self.bn3, self.bn4 = _bn_relu(in_channels), _bn_relu(hid), _bn_relu(hid), _bn_relu(hid)
         self.upsample = upsample
         self.activation = BN.FusedAway(tnn.ReLU(inplace=True))     # folded into the four BN passes
+        # conv1 -> bn2 (utils.py:74-75, before the up-sampling), conv2 -> bn3, conv3 -> bn4 (utils.py:81-84) are
+        # adjacent: their BatchNorm statistics ride in the conv's GEMM epilogue
+        for conv in (self.conv1, self.conv2, self.conv3):
+            conv.fused_stats = "channel"
 
     def forward(self, x):
         h = self.conv1(self.bn1(x))

@@ -26,6 +26,8 @@ class Bottleneck(tnn.Module):
         self.downsample = downsample
         for bn in (self.bn1, self.bn2, self.bn3):
             bn.fused_act, bn.fused_slope = "relu", 0.0
+        for conv in (self.conv1, self.conv2, self.conv3):      # each feeds a BatchNorm3d: statistics in the GEMM epilogue
+            conv.fused_stats = "channel"
 
     def forward(self, x):
         out = self.bn1(self.conv1(x))                      # BN + ReLU, one pass
@@ -41,6 +43,7 @@ class ResNet(tnn.Module):
         self.conv1 = BN.Conv3d(1, 64, kernel_size=7, stride=(2, 2, 2), padding=(3, 3, 3), bias=False)
         self.bn1 = BN.BatchNorm3d(64)
         self.bn1.fused_act = "relu"
+        self.conv1.fused_stats = "channel"
         self.maxpool = BN.MaxPool3d(kernel_size=(3, 3, 3), stride=2, padding=1)
         self.layer1 = self._make_layer(64, layers[0])
         self.layer2 = self._make_layer(128, layers[1], stride=2)
@@ -59,6 +62,7 @@ class ResNet(tnn.Module):
             downsample = tnn.Sequential(
                 BN.Conv3d(self.inplanes, planes * 4, kernel_size=1, stride=stride, bias=False),
                 BN.BatchNorm3d(planes * 4))
+            downsample[0].fused_stats = "channel"
         layers = [Bottleneck(self.inplanes, planes, stride=stride, dilation=dilation, downsample=downsample)]
         self.inplanes = planes * 4
         for _ in range(1, blocks):

@@ -17,7 +17,7 @@ from torch.autograd import Function
 
 from . import _lib
 from ._lib import (ACT_IDS, ACT_NONE, ALGO_AUTO, BF16, F32, PASS_DGRAD,
-                   PASS_FWD, PASS_WGRAD, ConvDesc, Fusion, check)
+                   PASS_FWD, PASS_WGRAD, STAT_CHANNEL, STAT_SAMPLE, ConvDesc, Fusion, check)
 
 _force_algo = [ALGO_AUTO]     # tests / profiling: force DIRECT or TC
 PROFILE = None                # bench.py: list collecting (pass, desc tuple, start event, end event)
@@ -210,6 +210,11 @@ def _desc(g, xshape, cout, dtype, algo):
     return d
 
 
+def _grad_slot(p):
+    from . import parallel
+    return parallel.grad_slot(p) if parallel._SLOTS else None
+
+
 _weights_epoch = [0]
 _hook_installed = [False]
 
@@ -301,7 +306,9 @@ class _ConvFn(Function):
     of trainer.py:209-210,249-250,255-256 decides which passes run."""
 
     @staticmethod
-    def forward(ctx, x, w, bias, g, act, slope):
+    def forward(ctx, x, w, bias, g, act, slope, stats=None):
+        """`stats`: None, or a dict {"kind": STAT_CHANNEL | STAT_SAMPLE} that receives "sum" / "sqsum" (fp32) of the
+        stored output, accumulated in the GEMM epilogue for the BatchNorm3d / LayerNorm that follows."""
         _check_device(x)
         cd = compute_dtype(x)
         xb = to_ndhwc(x.detach(), cd)
@@ -321,8 +328,15 @@ class _ConvFn(Function):
         if bias is not None:
             bf = bias.detach()
             bf = bf if bf.dtype == torch.float32 else bf.float()
-        fu = Fusion(_ptr(bf), int(act), float(slope))
-        ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_FWD), x)
+        fu = Fusion(_ptr(bf), int(act), float(slope), 0, None, None)
+        nws = L.b2c_conv3d_workspace(C.byref(desc), PASS_FWD)
+        if stats is not None:
+            n_st = desc.y.c if stats["kind"] == STAT_CHANNEL else desc.y.n
+            st_buf = torch.empty((2, n_st), dtype=torch.float32, device=x.device)
+            fu.stat_kind, fu.stat_sum, fu.stat_sqsum = stats["kind"], st_buf[0].data_ptr(), st_buf[1].data_ptr()
+            nws = ((nws + 255) & ~255) + L.b2c_conv3d_stats_workspace(C.byref(desc), stats["kind"])
+            stats["sum"], stats["sqsum"] = st_buf[0], st_buf[1]
+        ws = _ws(nws, x)
         with _dev(x), _timed("fwd", desc, g.fold):
             check(L.b2c_conv3d_fwd(C.byref(desc), _ptr(xb), _ptr(wp), _ptr(y), C.byref(fu),
                                    _ptr(ws), ws.numel(), _stream(x)), "conv3d_fwd")
@@ -364,7 +378,9 @@ class _ConvFn(Function):
         need_w = ctx.needs_input_grad[1]
         need_b = ctx.has_bias and ctx.needs_input_grad[2]
         if need_w or need_b:
-            dw = torch.empty(w.shape, dtype=torch.float32, device=w.device) if need_w else None
+            # data-parallel runs: the gradient is written straight into the parameter's slot of its all-reduce bucket
+            slot = _grad_slot(w) if (need_w and w.dtype == torch.float32) else None
+            dw = slot if slot is not None else (torch.empty(w.shape, dtype=torch.float32, device=w.device) if need_w else None)
             db = torch.empty(cout, dtype=torch.float32, device=w.device) if need_b else None
             ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_WGRAD), xb)
             with _dev(xb), _timed("wgrad", desc, g.fold):
@@ -372,7 +388,7 @@ class _ConvFn(Function):
                                          _ptr(ws), ws.numel(), _stream(xb)), "conv3d_wgrad")
             if dw is not None and w.dtype != torch.float32:
                 dw = dw.to(w.dtype)
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
 def _act_id(act):
@@ -381,9 +397,37 @@ def _act_id(act):
     return ACT_IDS[act]
 
 
-def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=None, slope=0.0):
+STATS = [True]      # False: never ask the conv epilogue for statistics (the norm layers run their own pass)
+_STAT_IDS = {"channel": STAT_CHANNEL, "sample": STAT_SAMPLE}
+
+
+def _with_stats(fn_apply, y_args, stats, fold=1):
+    """Run a conv Function; attach the statistics its epilogue accumulated to the output tensor (consumed by
+    batch_norm_act / layer_norm_act when the tensor reaches them unmodified)."""
+    if stats is None or not STATS[0]:
+        return fn_apply(*y_args)
+    holder = {"kind": _STAT_IDS[stats]}
+    y = fn_apply(*y_args, holder)
+    if "sum" in holder:
+        sm, sq = holder["sum"], holder["sqsum"]
+        if fold > 1 and holder["kind"] == STAT_CHANNEL:      # folded channels are (f, c): sum the f copies of c
+            sm, sq = sm.view(fold, -1).sum(0), sq.view(fold, -1).sum(0)
+        y._b2c_stats = (holder["kind"], sm, sq, y._version)
+    return y
+
+
+def take_stats(x, kind, n):
+    """The (sum, sqsum) a producing conv attached to `x`, if they describe its CURRENT contents; else None."""
+    st = getattr(x, "_b2c_stats", None)
+    if st is None or st[0] != kind or st[3] != x._version or st[1].numel() != n:
+        return None
+    return st[1], st[2]
+
+
+def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=None, slope=0.0, stats=None):
     """Drop-in for ``torch.nn.functional.conv3d`` (stylegan.py:168, nn.Conv3d.forward)
-    with an optional fused activation epilogue (`act` a name or a b2c activation id)."""
+    with an optional fused activation epilogue (`act` a name or a b2c activation id) and, with
+    ``stats="channel" | "sample"``, the statistics of the output for the BatchNorm3d / LayerNorm that follows."""
     if isinstance(padding, str):
         raise NotImplementedError("b200conv3d.conv3d: string padding %r is not supported" % padding)
     if groups != 1:
@@ -393,11 +437,11 @@ def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=
                                   "one-filter FIR of stylegan.py:197 are built; no cuDNN fallback)" % groups)
     g = Geom(False, tuple(weight.shape[2:]), stride, padding, dilation)
     if _s2d_applies(x, weight, g):
-        return _conv3d_s2d(x, weight, bias, g, _act_id(act), slope)
+        return _conv3d_s2d(x, weight, bias, g, _act_id(act), slope, stats)
     fold = _fold_factor(x, weight, g)
     if fold > 1:
-        return _conv3d_folded(x, weight, bias, g, _act_id(act), slope, fold)
-    return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+        return _conv3d_folded(x, weight, bias, g, _act_id(act), slope, fold, stats)
+    return _with_stats(_ConvFn.apply, (x, weight, bias, g, _act_id(act), slope), stats)
 
 
 def _depthwise_fir(x, weight, stride, padding, dilation):
@@ -475,11 +519,11 @@ def s2d_filter(weight):
     return wf.permute(0, 1, 3, 5, 2, 4, 6).reshape(cout, 8, kp, kp, kp), r              # channel = (pd, ph, pw)
 
 
-def _conv3d_s2d(x, weight, bias, g, act, slope):
+def _conv3d_s2d(x, weight, bias, g, act, slope, stats=None):
     n, _, d, h, w = x.shape
     x8 = x.reshape(n, d // 2, 2, h // 2, 2, w // 2, 2).permute(0, 1, 3, 5, 2, 4, 6).reshape(n, d // 2, h // 2, w // 2, 8)
     w8, r = s2d_filter(weight)
-    return conv3d(x8.permute(0, 4, 1, 2, 3), w8, bias, 1, r, act=act, slope=slope)
+    return conv3d(x8.permute(0, 4, 1, 2, 3), w8, bias, 1, r, act=act, slope=slope, stats=stats)
 
 
 # ---- W-folding of narrow stride-1 convolutions ------------------------------------------------
@@ -568,23 +612,23 @@ def _unfold_w(y, f):
     return y.permute(0, 2, 3, 4, 1).reshape(n, d, h, wf * f, fc // f).permute(0, 4, 1, 2, 3)
 
 
-def _conv3d_folded(x, weight, bias, g, act, slope, f):
+def _conv3d_folded(x, weight, bias, g, act, slope, f, stats=None):
     w2 = fold_filter(weight, f)
     b2 = None if bias is None else bias.repeat(f)
     g2 = Geom(False, tuple(w2.shape[2:]), 1, (g.pad[0], g.pad[1], 1 if w2.shape[4] == 3 else 0), 1)
     g2.fold = f
-    return _ConvFn.apply(_fold_w(x, f), w2, b2, g2, act, slope)       # unfolded by _ConvFn (same storage)
+    return _with_stats(_ConvFn.apply, (_fold_w(x, f), w2, b2, g2, act, slope), stats, f)   # unfolded by _ConvFn
 
 
 def conv_transpose3d(x, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1,
-                     dilation=1, act=None, slope=0.0):
+                     dilation=1, act=None, slope=0.0, stats=None):
     """Drop-in for ``torch.nn.functional.conv_transpose3d`` (stylegan.py:170,
     nn.ConvTranspose3d.forward).  Computed as a stride-decomposed sub-pixel
     convolution inside the library, never by zero insertion."""
     if groups != 1:
         raise NotImplementedError("b200conv3d.conv_transpose3d: groups=%d is not supported" % groups)
     g = Geom(True, tuple(weight.shape[2:]), stride, padding, dilation, output_padding)
-    return _ConvFn.apply(x, weight, bias, g, _act_id(act), slope)
+    return _with_stats(_ConvFn.apply, (x, weight, bias, g, _act_id(act), slope), stats)
 
 
 # ---- phase-merged stride-2 transposed conv for narrow outputs -------------------------------------
@@ -707,7 +751,8 @@ class _BNActFn(Function):
     dcgan.py:48-64, utils.py:62-86, biggan.py:40-41, FID_ResNet.py:71-100."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, rmean, rvar, training, momentum, eps, act, slope):
+    def forward(ctx, x, gamma, beta, residual, rmean, rvar, training, momentum, eps, act, slope, pre=None):
+        """`pre`: (sum, sqsum) per channel delivered by the producing conv's epilogue, or None."""
         _check_device(x)
         cd = compute_dtype(x)
         xb = to_ndhwc(x.detach(), cd)
@@ -722,9 +767,12 @@ class _BNActFn(Function):
         with _dev(x):
             st = _stream(x)
             if training:
-                ws = _ws(L.b2c_stats_workspace(rows, c), x)
-                check(L.b2c_channel_stats(_ptr(xb), rows, c, _dt(cd), _ptr(s_sum), _ptr(s_sq),
-                                          _ptr(ws), ws.numel(), st), "channel_stats")
+                if pre is not None:
+                    s_sum, s_sq = pre[0], pre[1]
+                else:
+                    ws = _ws(L.b2c_stats_workspace(rows, c), x)
+                    check(L.b2c_channel_stats(_ptr(xb), rows, c, _dt(cd), _ptr(s_sum), _ptr(s_sq),
+                                              _ptr(ws), ws.numel(), st), "channel_stats")
                 check(L.b2c_bn_finalize(_ptr(s_sum), _ptr(s_sq), rows, c, float(eps),
                                         float(momentum), _ptr(gf), _ptr(bf), _ptr(mean),
                                         _ptr(invstd), _ptr(scale), _ptr(shift),
@@ -783,26 +831,27 @@ class _BNActFn(Function):
                     dres = from_ndhwc(cast(drb, torch.float32) if ctx.res_dtype == torch.float32 else drb)
         dgamma = s2.clone() if (ctx.affine[0] and ctx.needs_input_grad[1]) else None
         dbeta = s1.clone() if (ctx.affine[1] and ctx.needs_input_grad[2]) else None
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None
 
 
 def batch_norm_act(x, gamma, beta, running_mean, running_var, training, momentum, eps,
                    act=None, slope=0.0, residual=None):
     use_batch = training or running_mean is None
+    pre = take_stats(x, STAT_CHANNEL, x.shape[1]) if (use_batch and x.dim() == 5) else None
     return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, use_batch,
-                          0.0 if momentum is None else momentum, eps, _act_id(act), slope)
+                          0.0 if momentum is None else momentum, eps, _act_id(act), slope, pre)
 
 
 # -------------------------------------------------------------- layer norm
-def _perm_affine(p, c, s, to_ndhwc_order):
+def _perm_affine(p, c, s, to_ndhwc_order, out=None):
     """[C,D,H,W] fp32 <-> [D,H,W,C] fp32 through b2c_transpose.  The parameter -> NDHWC copy is
-    cached on the parameter like a packed filter (same invalidation rules)."""
+    cached on the parameter like a packed filter (same invalidation rules).  `out`: destination (flat view)."""
     state = (p.data_ptr(), p._version, _weights_epoch[0])
     cache = getattr(p, "_b2c_pack", None) if to_ndhwc_order else None
     if cache is not None and cache[0] == state and ("ln", c, s) in cache[1]:
         return cache[1][("ln", c, s)]
     pf = _f32(p).reshape(-1)
-    out = torch.empty_like(pf)
+    out = torch.empty_like(pf) if out is None else out.view(-1)
     rows, cols = (c, s) if to_ndhwc_order else (s, c)
     with _dev(pf):
         check(_lib.lib().b2c_transpose(_ptr(pf), _ptr(out), 1, rows, cols, F32, F32, _stream(pf)),
@@ -824,7 +873,8 @@ class _LNActFn(Function):
     elementwise affine."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, eps, act, slope):
+    def forward(ctx, x, gamma, beta, eps, act, slope, pre=None):
+        """`pre`: (sum, sqsum) per sample delivered by the producing conv's epilogue, or None."""
         _check_device(x)
         cd = compute_dtype(x)
         xb = to_ndhwc(x.detach(), cd)
@@ -835,14 +885,21 @@ class _LNActFn(Function):
         bp = _perm_affine(beta, c, d * h * w, True) if beta is not None else None
         mr = torch.empty((2, n), dtype=torch.float32, device=x.device)
         yl, y = alloc_out(n, d, h, w, c, cd, x.device)
-        ws = _ws(L.b2c_ln_workspace(n, Lh), x)
-        with _dev(x):
-            check(L.b2c_ln_act_fwd(_ptr(xb), _ptr(y), n, Lh, _dt(cd), _ptr(gp), _ptr(bp),
-                                   float(eps), int(act), float(slope), _ptr(mr[0]), _ptr(mr[1]),
-                                   _ptr(ws), ws.numel(), _stream(x)), "ln_act_fwd")
+        if pre is not None:
+            with _dev(x):
+                check(L.b2c_ln_act_fwd_stats(_ptr(xb), _ptr(y), n, Lh, _dt(cd), _ptr(gp), _ptr(bp), float(eps),
+                                             int(act), float(slope), _ptr(pre[0]), _ptr(pre[1]), _ptr(mr[0]),
+                                             _ptr(mr[1]), _stream(x)), "ln_act_fwd_stats")
+        else:
+            ws = _ws(L.b2c_ln_workspace(n, Lh), x)
+            with _dev(x):
+                check(L.b2c_ln_act_fwd(_ptr(xb), _ptr(y), n, Lh, _dt(cd), _ptr(gp), _ptr(bp),
+                                       float(eps), int(act), float(slope), _ptr(mr[0]), _ptr(mr[1]),
+                                       _ptr(ws), ws.numel(), _stream(x)), "ln_act_fwd")
         ctx.save_for_backward(xb, gp, bp, mr)
         ctx.act, ctx.slope, ctx.cd, ctx.x_dtype = int(act), float(slope), cd, x.dtype
         ctx.pshape = tuple(gamma.shape) if gamma is not None else None
+        ctx.affine = (gamma, beta)
         return yl
 
     @staticmethod
@@ -868,13 +925,18 @@ class _LNActFn(Function):
         dx = None
         if need_x:
             dx = from_ndhwc(cast(dxb, torch.float32) if ctx.x_dtype == torch.float32 else dxb)
-        dgamma = _perm_affine(dg, c, d * h * w, False).reshape(ctx.pshape) if need_g else None
-        dbeta = _perm_affine(db, c, d * h * w, False).reshape(ctx.pshape) if need_b else None
-        return dx, dgamma, dbeta, None, None, None
+        def unperm(grad, param):          # NDHWC order -> the parameter's [C,D,H,W], into its all-reduce slot if any
+            slot = _grad_slot(param) if param.dtype == torch.float32 else None
+            return _perm_affine(grad, c, d * h * w, False, out=slot).reshape(ctx.pshape) if slot is None else \
+                (_perm_affine(grad, c, d * h * w, False, out=slot), slot)[1]
+        dgamma = unperm(dg, ctx.affine[0]) if need_g else None
+        dbeta = unperm(db, ctx.affine[1]) if need_b else None
+        return dx, dgamma, dbeta, None, None, None, None
 
 
 def layer_norm_act(x, gamma, beta, eps, act=None, slope=0.0):
-    return _LNActFn.apply(x, gamma, beta, eps, _act_id(act), slope)
+    pre = take_stats(x, STAT_SAMPLE, x.shape[0]) if x.dim() == 5 else None
+    return _LNActFn.apply(x, gamma, beta, eps, _act_id(act), slope, pre)
 
 
 # --------------------------------------------------------------- pointwise

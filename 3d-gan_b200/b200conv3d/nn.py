@@ -31,19 +31,21 @@ class Conv3d(_TConv3d):
     FID_ResNet.py:9-16,70-75,119-125,157-162, stylegan.py:998-1038)."""
     fused_act = None
     fused_slope = 0.0
+    fused_stats = None        # "channel" / "sample": the next layer is a BatchNorm3d / whole-sample LayerNorm
 
     def forward(self, x):
         if self.padding_mode != "zeros":
             raise NotImplementedError("b200conv3d.Conv3d: padding_mode=%r is not supported"
                                       % self.padding_mode)
         return BF.conv3d(x, self.weight, self.bias, self.stride, self.padding, self.dilation,
-                         self.groups, act=self.fused_act, slope=self.fused_slope)
+                         self.groups, act=self.fused_act, slope=self.fused_slope, stats=self.fused_stats)
 
 
 class ConvTranspose3d(_TConvTranspose3d):
     """nn.ConvTranspose3d replacement (dcgan.py:19-40,47-67)."""
     fused_act = None
     fused_slope = 0.0
+    fused_stats = None
 
     def forward(self, x, output_size=None):
         if self.padding_mode != "zeros":
@@ -54,7 +56,7 @@ class ConvTranspose3d(_TConvTranspose3d):
                                            self.kernel_size, 3, self.dilation)
         return BF.conv_transpose3d(x, self.weight, self.bias, self.stride, self.padding, out_pad,
                                    self.groups, self.dilation, act=self.fused_act,
-                                   slope=self.fused_slope)
+                                   slope=self.fused_slope, stats=self.fused_stats)
 
 
 class BatchNorm3d(_TBatchNorm3d):

@@ -9,117 +9,151 @@ averaged with a bucketed all-reduce over NCCL / NVLink that overlaps the rest of
 backward pass:
 
 * parameters are bucketed in reverse registration order (the order backward produces
-  their gradients), ~``bucket_mb`` MB of fp32 per bucket;
-* a post-accumulate-grad hook marks a parameter ready; when a bucket is complete it is
-  flattened and all-reduced on a side stream while backward keeps running;
-* :meth:`finish` (called before ``optimizer.step()``) joins the side stream and
-  scatters the averaged gradients back.
+  their gradients), ~``bucket_mb`` MB of fp32 per bucket; a parameter larger than a
+  bucket (the 134 M-element filter of dcgan.py:51) is its own bucket;
+* every bucket is ONE persistent flat fp32 buffer and every parameter owns a *slot*
+  (a view) in it.  The weight-gradient kernels write straight into the slot
+  (``b200conv3d.functional`` asks :func:`grad_slot`), autograd adopts that tensor as
+  ``.grad`` without a copy, so a bucket is complete - in place, no ``torch.cat`` - the
+  moment its last gradient is written; gradients produced any other way are copied into
+  their slot by the post-accumulate hook (and ``.grad`` re-pointed at it);
+* a complete bucket is all-reduced IN PLACE with ``ReduceOp.AVG`` on a side stream while
+  backward keeps running: no scaling pass and no copy back - ``.grad`` already is the
+  reduced buffer;
+* :meth:`finish` (before ``optimizer.step()``) joins the side stream.
 
-Several ``backward()`` calls between :meth:`begin` and :meth:`finish` are allowed (StyleGAN2Loss): a bucket whose
-gradients change after its reduce was launched is reduced again in :meth:`finish`.  Every rank must produce
-gradients for the same set of parameters in a pass (a bucket reduced on some ranks only would hang the collective).
+Several ``backward()`` calls between :meth:`begin` and :meth:`finish` are allowed (StyleGAN2Loss calls it two or three
+times per optimizer step, stylegan.py:39-99): the reductions are then deferred to :meth:`finish`, because a bucket that
+was averaged once must not be accumulated into again.  Every rank must produce gradients for the same set of
+parameters in a pass (a bucket reduced on some ranks only would hang the collective).
 
-With the ``gloo`` backend (CPU tests) the same code runs synchronously.
+With the ``gloo`` backend (CPU tests) the same code runs synchronously (sum, then divide).
 """
 import torch
 import torch.distributed as dist
 
+_SLOTS = {}          # id(param) -> (reducer, index): consulted by b200conv3d.functional through grad_slot()
+
+
+def grad_slot(p):
+    """The fp32 tensor (shaped like ``p``) a gradient kernel should write ``p``'s gradient into during the current
+    backward pass, or None.  Handed out ONCE per pass per parameter: a second gradient of the same parameter in one
+    pass (two discriminator passes) must be accumulated by autograd, not overwrite the first."""
+    ent = _SLOTS.get(id(p))
+    if ent is None:
+        return None
+    red, i = ent
+    if not red.armed or red.taken[i] or not p.requires_grad or p.grad is not None:
+        return None
+    red.taken[i] = True
+    return red.slots[i]
+
 
 class GradReducer:
-    def __init__(self, module, bucket_mb=32, group=None):
+    def __init__(self, module, bucket_mb=32, group=None, overlap=True):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.params = [p for p in module.parameters()]
-        self.buckets = []          # list of lists of params (reverse order)
-        cur, size, cap = [], 0, bucket_mb * (1 << 20)
-        for p in reversed(self.params):
-            cur.append(p)
-            size += p.numel() * 4
-            if size >= cap:
-                self.buckets.append(cur)
-                cur, size = [], 0
-        if cur:
-            self.buckets.append(cur)
-        self.bucket_of = {}
-        for bi, b in enumerate(self.buckets):
-            for p in b:
-                self.bucket_of[p] = bi
-        self.pending = [0] * len(self.buckets)
-        self.inflight = {}          # bucket index -> (grads, flat tensor, work handle)
-        self.dirty = set()          # buckets whose gradients changed after their reduce was launched
         dev = self.params[0].device if self.params else torch.device("cpu")
         self.cuda = dev.type == "cuda"
+        self.avg = self.cuda                    # NCCL has ReduceOp.AVG; gloo does not
+        self.overlap = overlap
+        cap = bucket_mb * (1 << 20)
+        buckets, cur, size = [], [], 0
+        for i in reversed(range(len(self.params))):
+            n = self.params[i].numel() * 4
+            if cur and size + n > cap:
+                buckets.append(cur)
+                cur, size = [], 0
+            cur.append(i)
+            size += n
+        if cur:
+            buckets.append(cur)
+        self.buckets = buckets                  # lists of parameter indices (reverse order)
+        self.flat, self.slots, self.bucket_of = [], [None] * len(self.params), {}
+        for bi, b in enumerate(buckets):
+            total = sum((self.params[i].numel() + 63) // 64 * 64 for i in b)      # 256-byte aligned slots
+            flat = torch.zeros(total, dtype=torch.float32, device=dev)
+            off = 0
+            for i in b:
+                n = self.params[i].numel()
+                self.slots[i] = flat[off:off + n].view(self.params[i].shape)
+                off += (n + 63) // 64 * 64
+                self.bucket_of[i] = bi
+            self.flat.append(flat)
+        self.index = {id(p): i for i, p in enumerate(self.params)}
+        self.taken = [False] * len(self.params)
+        self.pending = [0] * len(buckets)
+        self.inflight = {}                      # bucket index -> work handle
+        self.deferred = False                   # a second backward() was seen: reduce everything in finish()
+        self.armed = False
         self.stream = torch.cuda.Stream(device=dev) if self.cuda else None
         self.handles = [p.register_post_accumulate_grad_hook(self._hook) for p in self.params]
-        self._reset()
+        for i, p in enumerate(self.params):
+            _SLOTS[id(p)] = (self, i)
 
-    def _reset(self):
-        for bi, b in enumerate(self.buckets):
-            self.pending[bi] = sum(1 for p in b if p.requires_grad)
-
-    def begin(self):
-        """Call after the parameters' requires_grad flags are set for this pass
-        (trainer.py:209-210,255-256) and before backward."""
-        self.inflight = {}
-        self.dirty = set()
-        self._reset()
+    # ------------------------------------------------------------------ pass life cycle
+    def begin(self, backwards=1):
+        """Call after the parameters' requires_grad flags are set for this pass and ``zero_grad()``
+        (trainer.py:209-211,255-258), before backward.  `backwards`: how many ``backward()`` calls of this pass reach
+        every trainable parameter (StyleGAN2Loss.step_D: 2) - a bucket is reduced when the last one has written it."""
+        self.inflight, self.deferred = {}, False
+        self.taken = [False] * len(self.params)
+        self.active = [[i for i in b if self.params[i].requires_grad] for b in self.buckets]
+        self.pending = [len(a) * int(backwards) for a in self.active]
+        self.armed = self.world > 1
 
     def _hook(self, p):
-        if self.world == 1:
+        if not self.armed:
             return
-        bi = self.bucket_of[p]
+        i = self.index[id(p)]
+        slot = self.slots[i]
+        if p.grad is not None and p.grad.data_ptr() != slot.data_ptr():
+            # a gradient that was not written into its slot (dtype / layout / produced by a stock torch op)
+            slot.copy_(p.grad)
+            p.grad = slot
+        bi = self.bucket_of[i]
         self.pending[bi] -= 1
-        if self.pending[bi] == 0:
+        if self.pending[bi] == 0 and not self.deferred and self.overlap:
             self._launch(bi)
-        elif self.pending[bi] < 0:
-            # a further backward() between begin() and finish() (StyleGAN2Loss.step_D / step_G call it two or
-            # three times per optimizer step, stylegan.py:39-99) accumulated into p.grad AFTER this bucket's
-            # reduce was launched: the in-flight result is stale, finish() reduces the bucket again
-            self.dirty.add(bi)
+        elif self.pending[bi] < 0 and not self.deferred:
+            # a further backward() in this pass: buckets already averaged cannot take more gradients -
+            # undo nothing, but from now on everything waits for finish()
+            self.deferred = True
+            if self.inflight:
+                raise RuntimeError(
+                    "GradReducer: backward() was called again after gradient buckets of this pass were already "
+                    "all-reduced; say begin(backwards=k), or construct the reducer with overlap=False, for losses that "
+                    "call backward() several times per optimizer step (StyleGAN2Loss)")
 
     def _launch(self, bi):
-        grads = [p.grad for p in self.buckets[bi] if p.requires_grad and p.grad is not None]
-        if not grads:
+        if not self.active[bi]:
             return
+        flat = self.flat[bi]
         if self.cuda:
             ev = torch.cuda.current_stream().record_event()
             with torch.cuda.stream(self.stream):
                 self.stream.wait_event(ev)
-                flat = torch.cat([g.reshape(-1).float() for g in grads])
-                for g in grads:
-                    g.record_stream(self.stream)
-                work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                work = dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True)
         else:
-            flat = torch.cat([g.reshape(-1).float() for g in grads])
             work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-        self.inflight[bi] = (grads, flat, work)
+            work.wait()
+            flat.div_(self.world)
+        self.inflight[bi] = work
 
     def finish(self):
-        """Join all bucket reductions, write back the rank-averaged gradients."""
-        if self.world > 1:
-            # buckets whose parameters never produced a gradient this pass are skipped;
-            # buckets with missing hooks (unused params) are flushed here
-            for bi in range(len(self.buckets)):
-                if 0 < self.pending[bi] < sum(1 for p in self.buckets[bi] if p.requires_grad):
+        """Join all bucket reductions; afterwards every ``p.grad`` holds the rank-averaged gradient."""
+        if self.armed:
+            for bi in range(len(self.buckets)):       # same order on every rank: the collectives stay matched
+                if bi not in self.inflight and any(self.params[i].grad is not None for i in self.active[bi]):
                     self._launch(bi)
-            for bi in sorted(self.dirty):        # same order on every rank: the collectives stay matched
-                stale = self.inflight.pop(bi, None)
-                if stale is not None:
-                    stale[2].wait()
-                self._launch(bi)
-            inv = 1.0 / self.world
             for bi in sorted(self.inflight):
-                grads, flat, work = self.inflight[bi]
-                work.wait()                       # CUDA: the current stream waits for NCCL
-                if self.cuda:
-                    flat.record_stream(torch.cuda.current_stream())
-                flat.mul_(inv)
-                for g, o in zip(grads, flat.split([g.numel() for g in grads])):
-                    g.copy_(o.view_as(g))
+                self.inflight[bi].wait()              # CUDA: the current stream waits for NCCL
             self.inflight = {}
-            self.dirty = set()
-        self._reset()
+        self.armed = False
 
     def remove(self):
         for h in self.handles:
             h.remove()
+        for p in self.params:
+            _SLOTS.pop(id(p), None)

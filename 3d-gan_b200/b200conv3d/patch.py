@@ -139,6 +139,12 @@ def fuse(model):
                 a.fused_act, a.fused_slope = act
                 seq[i + 1] = BN.FusedAway(b)
                 n += 1
+            # conv -> BatchNorm3d / whole-sample LayerNorm: the statistics ride in the conv's GEMM epilogue
+            if isinstance(a, (BN.Conv3d, BN.ConvTranspose3d)) and a.fused_act is None:
+                if isinstance(b, BN.BatchNorm3d):
+                    a.fused_stats = "channel"
+                elif isinstance(b, BN.LayerNorm) and len(b.normalized_shape) == 4:
+                    a.fused_stats = "sample"
     return n
 
 

@@ -23,14 +23,19 @@ bool is_point_convT(const b2c_conv_desc* c) {
          c->y.w == c->dil[2] * (c->k[2] - 1) + 1 && c->dil[0] == 1 && c->dil[1] == 1 && c->dil[2] == 1;
 }
 
+// `stats` (forward only): filled by the kernel that can accumulate them in its epilogue (nblocks > 0 afterwards);
+// left untouched (nblocks == 0) by the others - the caller then falls back to one pass over the output.
 int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w, void* out, const float* bias,
-             int act, float slope, void* ws, size_t wsb, cudaStream_t st) {
+             int act, float slope, void* ws, size_t wsb, cudaStream_t st, const TcStats* stats = nullptr) {
   const Geo g = make_geo(c);
   Geo tg;
   if (const int tm = thin_mode(c, g, &tg)) {
     t_last_algo = B2C_ALGO_TC;
+    // the fused one-channel gather kernel accumulates per-sample sums (dcgan.py:161-162 Conv(1 -> ndf) -> LayerNorm)
+    const bool st_ok = stats && stats->kind == 2 && tm == 1 && !scatter && tg.n == c->y.n &&
+                       (int64_t)tg.sd * tg.sh * tg.sw >= 4;
     return scatter != (tm == 2) ? thin_scatter(tg, in, w, out, bias, act, slope, ws, wsb, st)
-                                : thin_gather(tg, in, w, out, bias, act, slope, ws, wsb, st);
+                                : thin_gather(tg, in, w, out, bias, act, slope, ws, wsb, st, st_ok ? stats : nullptr);
   }
   if (tc_allowed(c)) {
     ConvPlan plan;
@@ -49,7 +54,8 @@ int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w
     }
     if (rc == B2C_OK) {
       t_last_algo = B2C_ALGO_TC;
-      return tc_conv_launch(plan, in, w, out, bias, bias_mod, act, slope, st);
+      const bool st_ok = stats && stats->kind && tc_conv_stats_supported(plan, stats->kind, bias_mod);
+      return tc_conv_launch(plan, in, w, out, bias, bias_mod, act, slope, st, st_ok ? stats : nullptr);
     }
     if (c->algo == B2C_ALGO_TC) return B2C_ERR_UNSUPPORTED;
   } else if (c->algo == B2C_ALGO_TC) {
@@ -60,7 +66,18 @@ int fwd_like(const b2c_conv_desc* c, bool scatter, const void* in, const void* w
                  : direct_gather(g, c->io_dtype, in, w, out, bias, act, slope, st);
 }
 
+int stat_len_of(const b2c_conv_desc* c, int kind) { return kind == B2C_STAT_CHANNEL ? c->y.c : c->y.n; }
+
 }  // namespace
+
+extern "C" size_t b2c_conv3d_stats_workspace(const b2c_conv_desc* c, int kind) {
+  if (check_desc(c) || (kind != B2C_STAT_CHANNEL && kind != B2C_STAT_SAMPLE)) return 0;
+  const int64_t rows = (int64_t)c->y.n * c->y.d * c->y.h * c->y.w;
+  size_t fused = 2 * tc_conv_stats_bytes(stat_len_of(c, kind));        // one partial row per CTA (<= 2 per SM)
+  size_t unfused = kind == B2C_STAT_CHANNEL ? channel_stats2_workspace(rows, c->y.c)
+                                            : sample_stats_workspace(c->y.n, rows / c->y.n * c->y.c);
+  return fused > unfused ? fused : unfused;
+}
 
 namespace {
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -94,7 +111,25 @@ extern "C" int b2c_conv3d_fwd(const b2c_conv_desc* c, const void* x, const void*
   const int act = f ? f->act : B2C_ACT_NONE;
   const float slope = f ? f->slope : 0.f;
   if (act < B2C_ACT_NONE || act > B2C_ACT_TANH) return B2C_ERR_INVALID;
-  return fwd_like(c, c->transposed != 0, x, wp, y, bias, act, slope, ws, wsb, static_cast<cudaStream_t>(s));
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  const int kind = f ? f->stat_kind : B2C_STAT_NONE;
+  if (kind == B2C_STAT_NONE) return fwd_like(c, c->transposed != 0, x, wp, y, bias, act, slope, ws, wsb, st);
+  // statistics of the stored output for the BatchNorm3d / LayerNorm that follows: the tail of the workspace holds
+  // the per-CTA partial rows (or the scratch of the one-pass fall-back)
+  if ((kind != B2C_STAT_CHANNEL && kind != B2C_STAT_SAMPLE) || !f->stat_sum || !f->stat_sqsum) return B2C_ERR_INVALID;
+  if (kind == B2C_STAT_SAMPLE && c->y.n > 65535) return B2C_ERR_UNSUPPORTED;
+  const size_t core = align256(b2c_conv3d_workspace(c, B2C_PASS_FWD)), extra = b2c_conv3d_stats_workspace(c, kind);
+  if (!ws || wsb < core + extra) return B2C_ERR_WORKSPACE;
+  float* part = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + core);
+  const int len = stat_len_of(c, kind);
+  TcStats ts{kind, len, part, extra, 0};
+  rc = fwd_like(c, c->transposed != 0, x, wp, y, bias, act, slope, ws, core, st, &ts);
+  if (rc) return rc;
+  if (ts.nblocks > 0) return stat_finalize(part, ts.nblocks, len, f->stat_sum, f->stat_sqsum, st);
+  const int64_t rows = (int64_t)c->y.n * c->y.d * c->y.h * c->y.w;
+  return kind == B2C_STAT_CHANNEL
+             ? channel_stats2(y, rows, c->y.c, c->io_dtype, f->stat_sum, f->stat_sqsum, part, extra, st)
+             : sample_stats(y, c->y.n, rows / c->y.n * c->y.c, c->io_dtype, f->stat_sum, f->stat_sqsum, part, extra, st);
 }
 
 extern "C" int b2c_conv3d_dgrad(const b2c_conv_desc* c, const void* dy, const void* wp, void* dx, void* ws,

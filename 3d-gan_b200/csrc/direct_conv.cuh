@@ -17,4 +17,10 @@ int direct_wgrad(const Geo& g, int dt, const void* small, const void* big, float
 // norm.cu: deterministic per-channel sum (dbias)
 size_t channel_sum_workspace(int64_t rows, int64_t C);
 int channel_sum(const void* x, int64_t rows, int C, int dt, float* out, void* ws, size_t wsb, cudaStream_t st);
+// statistics handed from a conv epilogue to the following normalisation layer (norm.cu)
+int stat_finalize(const float* part, int nblocks, int len, float* sum, float* sq, cudaStream_t st);
+size_t sample_stats_workspace(int64_t N, int64_t L);
+int sample_stats(const void* y, int64_t N, int64_t L, int dt, float* sum, float* sq, void* ws, size_t wsb, cudaStream_t st);
+size_t channel_stats2_workspace(int64_t rows, int64_t C);
+int channel_stats2(const void* y, int64_t rows, int64_t C, int dt, float* sum, float* sq, void* ws, size_t wsb, cudaStream_t st);
 }  // namespace b2c

@@ -684,6 +684,97 @@ int channel_sum(const void* x, int64_t rows, int C, int dt, float* out, void* ws
 }
 }  // namespace b2c
 
+// ---- statistics handed from a conv epilogue to the normalisation layer that follows -------------------
+namespace b2c {
+// second stage of the fused conv statistics: out[i] = sum over the CTAs' partial rows part[b][2][len]
+int stat_finalize(const float* part, int nblocks, int len, float* sum, float* sq, cudaStream_t st) {
+  if (!part || !sum || !sq || nblocks <= 0 || len <= 0) return B2C_ERR_INVALID;
+  chan_reduce_stage2<<<(unsigned)cdiv(len, kS2Chan), kS2Chan * kS2Slices, 0, st>>>(part, nblocks, len, sum, sq);
+  return launched();
+}
+
+// [N][chunks][2] partial sums -> sum[N], sq[N]  (per-sample statistics computed by a separate pass)
+__global__ void ln_sums_kernel(const float* part, int chunks, int N, float* sum, float* sq) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  double a = 0, b = 0;
+  for (int i = 0; i < chunks; i++) { a += part[((int64_t)n * chunks + i) * 2]; b += part[((int64_t)n * chunks + i) * 2 + 1]; }
+  sum[n] = (float)a; sq[n] = (float)b;
+}
+__global__ void ln_from_sums_kernel(const float* sum, const float* sq, int N, double invL, float eps, float* mean,
+                                    float* rstd) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const double m = (double)sum[n] * invL;
+  double var = (double)sq[n] * invL - m * m;
+  if (var < 0) var = 0;
+  mean[n] = (float)m; rstd[n] = (float)rsqrt(var + (double)eps);
+}
+
+// Unfused fall-backs of the same contract (paths whose epilogue does not accumulate): one read of y.
+size_t sample_stats_workspace(int64_t N, int64_t L) {
+  if (N <= 0 || L <= 0) return 0;
+  return (size_t)N * ln_chunks(N, L) * 2 * sizeof(float);
+}
+int sample_stats(const void* y, int64_t N, int64_t L, int dt, float* sum, float* sq, void* ws, size_t wsb,
+                 cudaStream_t st) {
+  if (!y || !sum || !sq || !ws || N <= 0 || L <= 0 || N > 65535) return B2C_ERR_INVALID;
+  if (wsb < sample_stats_workspace(N, L)) return B2C_ERR_WORKSPACE;
+  const int chunks = ln_chunks(N, L);
+  float* part = static_cast<float*>(ws);
+  dim3 grid(chunks, (unsigned)N);
+  if (dt == B2C_BF16) {
+    const __nv_bfloat16* yp = static_cast<const __nv_bfloat16*>(y);
+    if (L % 8 == 0 && aligned16(y)) ln_partial_kernel<__nv_bfloat16, 8><<<grid, kThreads, 0, st>>>(yp, L, part);
+    else ln_partial_kernel<__nv_bfloat16, 1><<<grid, kThreads, 0, st>>>(yp, L, part);
+  } else {
+    const float* yp = static_cast<const float*>(y);
+    if (L % 4 == 0 && aligned16(y)) ln_partial_kernel<float, 4><<<grid, kThreads, 0, st>>>(yp, L, part);
+    else ln_partial_kernel<float, 1><<<grid, kThreads, 0, st>>>(yp, L, part);
+  }
+  int rc = launched();
+  if (rc) return rc;
+  ln_sums_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(part, chunks, (int)N, sum, sq);
+  return launched();
+}
+size_t channel_stats2_workspace(int64_t rows, int64_t C) { return (size_t)reduce_blocks(rows) * 2 * C * sizeof(float); }
+int channel_stats2(const void* y, int64_t rows, int64_t C, int dt, float* sum, float* sq, void* ws, size_t wsb,
+                   cudaStream_t st) {
+  if (dt == B2C_BF16) {
+    BnBwdF<__nv_bfloat16> f{};
+    return chan_reduce<__nv_bfloat16, false>(static_cast<const __nv_bfloat16*>(y), rows, C, f, sum, sq, ws, wsb, st);
+  }
+  BnBwdF<float> f{};
+  return chan_reduce<float, false>(static_cast<const float*>(y), rows, C, f, sum, sq, ws, wsb, st);
+}
+}  // namespace b2c
+
+// LayerNorm forward from statistics the producing convolution already accumulated (b2c_fusion.stat_*): no pass
+// over x for mean / variance - finalize [N] values, then the apply pass.
+extern "C" int b2c_ln_act_fwd_stats(const void* x, void* y, int64_t N, int64_t L, int dt, const float* gamma,
+                                    const float* beta, float eps, int act, float slope, const float* sum,
+                                    const float* sqsum, float* mean, float* rstd, b2c_stream s) {
+  if (!x || !y || !sum || !sqsum || !mean || !rstd || !dt_ok(dt) || N <= 0 || L <= 0 || N > 65535) return B2C_ERR_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  ln_from_sums_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(sum, sqsum, (int)N, 1.0 / (double)L, eps, mean, rstd);
+  int rc = launched();
+  if (rc) return rc;
+  if (dt == B2C_BF16) {
+    const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x); __nv_bfloat16* yp = static_cast<__nv_bfloat16*>(y);
+    if (L % 8 == 0 && aligned16(x) && aligned16(y))
+      ln_apply_fwd_kernel<__nv_bfloat16, 8><<<ln_apply_grid(N, L / 8), kThreads, 0, st>>>(xp, yp, (int)N, L, gamma, beta, mean, rstd, act, slope);
+    else
+      ln_apply_fwd_kernel<__nv_bfloat16, 1><<<ln_apply_grid(N, L), kThreads, 0, st>>>(xp, yp, (int)N, L, gamma, beta, mean, rstd, act, slope);
+  } else {
+    const float* xp = static_cast<const float*>(x); float* yp = static_cast<float*>(y);
+    if (L % 4 == 0 && aligned16(x) && aligned16(y))
+      ln_apply_fwd_kernel<float, 4><<<ln_apply_grid(N, L / 4), kThreads, 0, st>>>(xp, yp, (int)N, L, gamma, beta, mean, rstd, act, slope);
+    else
+      ln_apply_fwd_kernel<float, 1><<<ln_apply_grid(N, L), kThreads, 0, st>>>(xp, yp, (int)N, L, gamma, beta, mean, rstd, act, slope);
+  }
+  return launched();
+}
+
 extern "C" size_t b2c_stats_workspace(int64_t rows, int64_t C) {
   if (rows <= 0 || C <= 0) return 0;
   return (size_t)reduce_blocks(rows) * 2 * C * sizeof(float);

@@ -396,6 +396,83 @@ int d2s_t(bool inv, const void* src, void* dst, const D2sGeo& g, cudaStream_t st
 }  // namespace
 }  // namespace b2c
 
+// ---- W-window gather (second generation of the W-folding of narrow stride-1 convolutions) ----------------
+// x [rows, W, C] -> y [rows, W/F, (F + 2*pad) * C],  y[r, j, v*C + c] = x[r, F*j + v - pad, c]  (0 outside [0, W))
+// turns a C -> Cout conv with 2*pad+1 taps along W into a (F+2*pad)*C -> F*Cout conv with ONE tap along W whose
+// output [rows, W/F, F*Cout] IS the unfolded [rows, W, Cout] tensor; its block-Toeplitz filter has
+// (2*pad+1) / (F + 2*pad) non-zero blocks (3/6 for F = 4 against 1/4 for the 3-tap folding).
+// Adjoint (inverse != 0): x[r, w, c] = sum over the windows that contain w of y[r, j, (w - F*j + pad)*C + c].
+namespace b2c {
+namespace {
+struct WinGeo { int64_t rows; int w, c, f, pad; };
+
+template <typename T, int VEC, bool ADJ>
+__global__ void __launch_bounds__(kThr) window_w_kernel(WinGeo g, const T* __restrict__ src, T* __restrict__ dst, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = g.c / VEC, win = g.f + 2 * g.pad, groups = g.w / g.f;
+  const int ci = (int)(idx % cv) * VEC;
+  int64_t t = idx / cv;
+  float o[VEC];
+  if (!ADJ) {                                  // one thread per 16-byte vector of y
+    const int v = (int)(t % win); t /= win;
+    const int j = (int)(t % groups);
+    const int64_t r = t / groups;
+    const int w = g.f * j + v - g.pad;
+    if (w >= 0 && w < g.w) rs_ld<T, VEC>(src + (r * g.w + w) * (int64_t)g.c + ci, o);
+    else {
+#pragma unroll
+      for (int i = 0; i < VEC; i++) o[i] = 0.f;
+    }
+    rs_st<T, VEC>(dst + idx * VEC, o);
+  } else {                                     // one thread per 16-byte vector of x: gather form, no atomics
+    const int w = (int)(t % g.w);
+    const int64_t r = t / g.w;
+#pragma unroll
+    for (int i = 0; i < VEC; i++) o[i] = 0.f;
+    // windows j with 0 <= w - F*j + pad < win
+    int j0 = (w + g.pad - win + g.f) / g.f;    // ceil((w + pad - win + 1) / F)
+    if (j0 < 0) j0 = 0;
+    int j1 = (w + g.pad) / g.f;
+    if (j1 > groups - 1) j1 = groups - 1;
+    for (int j = j0; j <= j1; j++) {
+      const int v = w - g.f * j + g.pad;
+      float a[VEC];
+      rs_ld<T, VEC>(src + ((r * groups + j) * (int64_t)win + v) * g.c + ci, a);
+#pragma unroll
+      for (int i = 0; i < VEC; i++) o[i] += a[i];
+    }
+    rs_st<T, VEC>(dst + idx * VEC, o);
+  }
+}
+
+template <typename T>
+int window_w_t(bool adj, const void* src, void* dst, const WinGeo& g, cudaStream_t st) {
+  constexpr int V = Vec<T>::N;
+  const bool vec = g.c % V == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+  const int cv = g.c / (vec ? V : 1);
+  const int64_t total = adj ? g.rows * g.w * cv : g.rows * (g.w / g.f) * (g.f + 2 * g.pad) * cv;
+  if (total == 0) return B2C_OK;
+  const int64_t b = cdiv(total, (int64_t)kThr);
+  if (b > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  const unsigned blocks = (unsigned)b;
+  const T* sp = static_cast<const T*>(src); T* dp = static_cast<T*>(dst);
+  if (!adj) { if (vec) window_w_kernel<T, V, false><<<blocks, kThr, 0, st>>>(g, sp, dp, total); else window_w_kernel<T, 1, false><<<blocks, kThr, 0, st>>>(g, sp, dp, total); }
+  else      { if (vec) window_w_kernel<T, V, true><<<blocks, kThr, 0, st>>>(g, sp, dp, total); else window_w_kernel<T, 1, true><<<blocks, kThr, 0, st>>>(g, sp, dp, total); }
+  return launched();
+}
+}  // namespace
+}  // namespace b2c
+
+extern "C" int b2c_window_w(const void* src, void* dst, int64_t rows, int w, int c, int f, int pad, int dt, int inverse,
+                            b2c_stream s) {
+  using namespace b2c;
+  if (!src || !dst || !dt_ok(dt) || rows < 0 || w <= 0 || c <= 0 || f <= 0 || pad < 0 || w % f != 0) return B2C_ERR_INVALID;
+  WinGeo g{rows, w, c, f, pad};
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dt == B2C_BF16 ? window_w_t<__nv_bfloat16>(inverse != 0, src, dst, g, st) : window_w_t<float>(inverse != 0, src, dst, g, st);
+}
+
 extern "C" int b2c_depth_to_space2(const void* src, void* dst, int64_t n, int jd, int jh, int jw, int c, int od, int oh,
                                    int ow, int dt, int inverse, b2c_stream s) {
   using namespace b2c;

@@ -47,6 +47,13 @@ struct alignas(64) TcConvParams {
   int32_t w_rows;        // filter rows staged per stage
   int32_t nacc;          // TMEM accumulator sets: 2 (epilogue of tile i overlaps tile i+1) or 1 (256 x 256 tiles)
   int32_t dbg;           // B2C_DBG env (diagnostics only): 1 no TMA store, 2 no tcgen05.ld, 4 no st.shared
+  // statistics of the STORED output (after bias / activation / bf16 rounding) for the normalisation layer that
+  // follows (dcgan.py:47-65 ConvT -> BatchNorm3d, dcgan.py:161-179 Conv -> LayerNorm): every CTA accumulates its
+  // tiles in shared memory in a fixed order and writes ONE partial row; a second stage sums the rows (deterministic)
+  int32_t stat_kind;     // 0 none, 1 per output channel (sum over voxels), 2 per sample (sum over voxels x channels)
+  int32_t stat_len;      // channels (kind 1; = bias_mod for the point GEMM) or samples (kind 2)
+  int32_t sb_log[3];     // log2 of the sub-tile box extents {w, h, d} (powers of two)
+  float* stat_part;      // [gridDim.x][2][stat_len]
 };
 
 // hardware tanh (abs error ~5e-4 of full scale): far inside bf16 output resolution near +-1
@@ -81,6 +88,26 @@ __device__ __forceinline__ void st_shared_b16(uint32_t addr, uint16_t v) {
   asm volatile("st.shared.b16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
 }
 
+__device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+
+// Which rows of a 128-row sub-tile lie inside the output lattice (the TMA store clips the others).
+struct RowClip {
+  int lim[4];            // valid extent of the sub-tile box per lattice dim {n, d, h, w}
+  int l3, l2, l1;        // log2 of the box extents {w, h, d}
+  bool full;
+  __device__ __forceinline__ bool ok(int r) const {
+    if (full) return true;
+    const int iw = r & ((1 << l3) - 1), ih = (r >> l3) & ((1 << l2) - 1), id = (r >> (l3 + l2)) & ((1 << l1) - 1);
+    const int in = r >> (l3 + l2 + l1);
+    return iw < lim[3] && ih < lim[2] && id < lim[1] && in < lim[0];
+  }
+};
+
 struct TileCoord { int si, nt, q[4], iters; };
 
 // NCTA == 2: `tile` indexes PAIR tiles; the two CTAs of a pair take M tiles 2j and 2j+1 of
@@ -114,6 +141,21 @@ __device__ __forceinline__ TileCoord decode_tile(const TcConvParams& P, int tile
   return c;
 }
 
+// validity of the rows of the 128-row sub-tile whose origin is q (lattice coordinates {n, d, h, w})
+__device__ __forceinline__ RowClip make_clip(const TcConvParams& P, const TileCoord& c, const int* q) {
+  RowClip k;
+  const SubDesc& sub = P.subs[c.si];
+  k.l3 = P.sb_log[0]; k.l2 = P.sb_log[1]; k.l1 = P.sb_log[2];
+  const int sb[4] = {kBlockM >> (k.l3 + k.l2 + k.l1), 1 << k.l1, 1 << k.l2, 1 << k.l3};
+  k.full = true;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    k.lim[i] = sub.ext[i] - q[i];
+    if (k.lim[i] < sb[i]) k.full = false;
+  }
+  return k;
+}
+
 constexpr uint32_t kStagingBytes = 2 * kABytes;      // two 128-row x 64-column bf16 slabs (ring)
 constexpr int kEpiThreads = 128;
 
@@ -123,7 +165,9 @@ constexpr int kEpiThreads = 128;
 //               tile i overlaps the main loop of tile i+1
 //   warps 2..5  epilogue: TMEM -> registers -> bias/activation -> bf16 -> swizzled smem
 //               slab -> TMA store (coalesced, clipped at the tensor edge)
-template <int NCTA>
+// STATS: the epilogue also accumulates the statistics of P.stat_kind (a separate instantiation, so that launches
+// without them keep the register allocation of the plain kernel).
+template <int NCTA, bool STATS>
 __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_constant__ TcConvParams P) {
   extern __shared__ uint8_t smem_raw[];
   const int rank = NCTA == 2 ? (int)cluster_ctarank() : 0;     // rank 0 = leader: issues every MMA of the pair
@@ -261,6 +305,33 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
     const int et = threadIdx.x - 64;             // 0..127
     const uint32_t lane_off = (uint32_t)(grp * 32) << 16;
     uint32_t tcount = 0, slab_count = 0;
+    // fused statistics, in shared memory behind the barriers.  kind 2 (per sample): the CTA's sums [2][stat_len] and a
+    // [128][2] scratch.  kind 1 (per channel): the sums of the CTA's CURRENT N tile [2][256] and a [4 warps][64][2]
+    // scratch (the 256 x 256 tiles leave < 6 KB of shared memory); they are added to the CTA's row of the partial
+    // buffer in global memory whenever the N tile changes (never, when the grid is a multiple of tiles_n).
+    float* sacc = reinterpret_cast<float*>(sgen + stages * stage_bytes + kStagingBytes + 256);
+    float* sscr = sacc + (P.stat_kind == 1 ? 512 : ((2 * P.stat_len + 3) & ~3));
+    float* gpart = P.stat_part + (size_t)blockIdx.x * 2 * P.stat_len;
+    float ks = 0.f, kq = 0.f;                    // swap mode: this thread's channel, over every tile of the CTA
+    int cur_nt = -1;
+    auto flush_nt = [&]() {                      // all 128 epilogue threads; entry e is always handled by thread e % 128
+      named_bar_sync(2, kEpiThreads);
+      if (cur_nt >= 0)
+        for (int e = et; e < 2 * P.block_n; e += kEpiThreads) {
+          const int which = e >= P.block_n ? 1 : 0, col = cur_nt * P.block_n + (e - which * P.block_n);
+          if (col < P.nout) gpart[which * P.stat_len + (P.bias_mod < P.nout ? col % P.bias_mod : col)] += sacc[e];
+        }
+      for (int e = et; e < 512; e += kEpiThreads) sacc[e] = 0.f;
+      named_bar_sync(2, kEpiThreads);
+    };
+    if (STATS && !P.swap) {
+      if (P.stat_kind == 1) {
+        for (int i = et; i < 2 * P.stat_len; i += kEpiThreads) gpart[i] = 0.f;
+      } else {
+        for (int i = et; i < 2 * P.stat_len; i += kEpiThreads) sacc[i] = 0.f;
+      }
+      named_bar_sync(1, kEpiThreads);
+    }
     // A failed (timed-out) wait only raises g_tc_error: the loop is never left early, so the
     // named barriers of the 128 epilogue threads stay matched and the kernel drains.
     for (int tile = first_tile; tile < P.num_tiles; tile += tile_step, tcount++) {
@@ -286,9 +357,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
         for (int m = 0; m < P.mt; m++) {
           int q[4] = {c.q[0], c.q[1], c.q[2], c.q[3]};
           q[P.split_dim] += m * P.sub_ext;
+          const RowClip clip = make_clip(P, c, q);
           if (et == 0) tma_store_wait_read<0>();
           named_bar_sync(1, kEpiThreads);
           if (warp_live) {
+            float ts = 0.f, tq = 0.f;              // two-level sum: 128 voxels here, then the CTA's running sums
             for (int h = 0; h < 2; h++) {
               uint32_t v[64];
               const uint32_t tcol = tmem_base + lane_off + acc * acc_cols + m * 128 + h * 64;
@@ -308,8 +381,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
                 const __nv_bfloat16 hv = __float2bfloat16_rn(__uint_as_float(v[j]));
                 st_shared_b16(sdst + (uint32_t)(h * 64 + j) * 128u + ((chunk ^ (uint32_t)(j & 7)) << 4),
                               *reinterpret_cast<const uint16_t*>(&hv));
+                if (STATS && P.stat_kind == 1 && clip.ok(h * 64 + j)) {   // column = voxel h*64 + j of sub-tile m
+                  const float r = __bfloat162float(hv);
+                  ts += r; tq += r * r;
+                }
               }
             }
+            ks += ts; kq += tq;
           }
           fence_proxy_async();
           named_bar_sync(1, kEpiThreads);
@@ -319,10 +397,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
             tma_store_commit();
           }
         }
-      } else
+      } else {
+      if (STATS && P.stat_kind == 1 && c.nt != cur_nt) { flush_nt(); cur_nt = c.nt; }
       for (int m = 0; m < P.mt; m++) {
         int q[4] = {c.q[0], c.q[1], c.q[2], c.q[3]};
         q[P.split_dim] += m * P.sub_ext;
+        const RowClip clip = make_clip(P, c, q);
+        float rs = 0.f, rq = 0.f;                // kind 2: this thread's row (voxel), over the channels of the tile
         for (int j = 0; j < nslab; j++, slab_count++) {
           const uint32_t sbuf = staging + (slab_count & 1u) * kABytes;
           // the TMA store that last read this slab buffer (2 slabs ago) must be done with it
@@ -374,12 +455,21 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
           apply_act64(v, P.act, P.slope);
 #pragma unroll
           for (int ch = 0; ch < 8; ch++) {
-            if (ch * 8 < ncol)
-              st_shared_v4(sbuf + row * 128 + ((ch ^ (row & 7)) << 4),
-                           pack_bf16x2(__uint_as_float(v[ch * 8 + 0]), __uint_as_float(v[ch * 8 + 1])),
-                           pack_bf16x2(__uint_as_float(v[ch * 8 + 2]), __uint_as_float(v[ch * 8 + 3])),
-                           pack_bf16x2(__uint_as_float(v[ch * 8 + 4]), __uint_as_float(v[ch * 8 + 5])),
-                           pack_bf16x2(__uint_as_float(v[ch * 8 + 6]), __uint_as_float(v[ch * 8 + 7])));
+            if (ch * 8 < ncol) {
+              const uint32_t p0 = pack_bf16x2(__uint_as_float(v[ch * 8 + 0]), __uint_as_float(v[ch * 8 + 1])),
+                             p1 = pack_bf16x2(__uint_as_float(v[ch * 8 + 2]), __uint_as_float(v[ch * 8 + 3])),
+                             p2 = pack_bf16x2(__uint_as_float(v[ch * 8 + 4]), __uint_as_float(v[ch * 8 + 5])),
+                             p3 = pack_bf16x2(__uint_as_float(v[ch * 8 + 6]), __uint_as_float(v[ch * 8 + 7]));
+              st_shared_v4(sbuf + row * 128 + ((ch ^ (row & 7)) << 4), p0, p1, p2, p3);
+              if (STATS && P.stat_kind == 2 && col0 + ch * 8 < P.nout) {      // the stored (rounded) values; nout % 8 == 0
+                const uint32_t pk[4] = {p0, p1, p2, p3};
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                  const float lo = __uint_as_float(pk[i] << 16), hi = __uint_as_float(pk[i] & 0xffff0000u);
+                  rs += lo + hi; rq += lo * lo + hi * hi;
+                }
+              }
+            }
           }
           fence_proxy_async();                   // make the generic-proxy smem writes visible to TMA
           named_bar_sync(1, kEpiThreads);
@@ -387,7 +477,81 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
             tma_store_5d(om, sbuf, col0, q[3], q[2], q[1], q[0]);
             tma_store_commit();
           }
+          if (STATS && P.stat_kind == 1) {
+            // per-channel sums of the slab just staged (its bf16 values, as stored).  A warp owns 32 rows: lane =
+            // (8 rows, 8 channels); the four row groups of a warp are combined with shuffles, the four warps through
+            // the scratch in a fixed order, then ONE thread adds to the sums of this N tile.
+            const int ch8 = lane & 7, rg = (et >> 5) * 4 + (lane >> 3);
+            float s8[8], q8[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) s8[k] = q8[k] = 0.f;
+            if (ch8 * 8 < ncol) {
+#pragma unroll
+              for (int i = 0; i < 8; i++) {
+                const int r = rg * 8 + i;
+                if (clip.ok(r)) {
+                  const uint4 raw = ld_shared_v4(sbuf + r * 128 + ((ch8 ^ (r & 7)) << 4));
+                  const uint32_t pk[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+                  for (int k = 0; k < 4; k++) {
+                    const float lo = __uint_as_float(pk[k] << 16), hi = __uint_as_float(pk[k] & 0xffff0000u);
+                    s8[2 * k] += lo; q8[2 * k] += lo * lo; s8[2 * k + 1] += hi; q8[2 * k + 1] += hi * hi;
+                  }
+                }
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+              s8[k] += __shfl_xor_sync(0xffffffffu, s8[k], 8);  q8[k] += __shfl_xor_sync(0xffffffffu, q8[k], 8);
+              s8[k] += __shfl_xor_sync(0xffffffffu, s8[k], 16); q8[k] += __shfl_xor_sync(0xffffffffu, q8[k], 16);
+            }
+            if (lane < 8) {
+              float* sc = sscr + ((et >> 5) * 64 + ch8 * 8) * 2;
+#pragma unroll
+              for (int k = 0; k < 8; k++) { sc[2 * k] = s8[k]; sc[2 * k + 1] = q8[k]; }
+            }
+            named_bar_sync(2, kEpiThreads);
+            const int cc = et & 63, which = et >> 6;
+            const float a = sscr[cc * 2 + which] + sscr[(64 + cc) * 2 + which] + sscr[(128 + cc) * 2 + which] +
+                            sscr[(192 + cc) * 2 + which];
+            if (cc < ncol) sacc[which * P.block_n + j * 64 + cc] += a;
+          }
         }
+        if (STATS && P.stat_kind == 2) {
+          // per-sample sums: rows of one sample are contiguous in the box (n is its slowest dim).  With >= 32 rows per
+          // sample a warp's rows share the sample: shuffle reduction, then thread 0 adds the four warp sums in order;
+          // smaller samples (4^3 outputs ...) go through the per-row scratch.
+          const bool rv = clip.ok(row);
+          const int rl = P.sb_log[0] + P.sb_log[1] + P.sb_log[2];       // log2(rows per sample in the sub-tile)
+          float ws_ = rv ? rs : 0.f, wq_ = rv ? rq : 0.f;
+          if (rl >= 5) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { ws_ += __shfl_xor_sync(0xffffffffu, ws_, o); wq_ += __shfl_xor_sync(0xffffffffu, wq_, o); }
+            if (lane == 0) { sscr[grp * 2] = ws_; sscr[grp * 2 + 1] = wq_; }
+            named_bar_sync(2, kEpiThreads);
+            if (et == 0) {
+#pragma unroll
+              for (int g2 = 0; g2 < 4; g2++) {
+                const int samp = (g2 * 32) >> rl;
+                if (samp < clip.lim[0]) {
+                  sacc[q[0] + samp] += sscr[g2 * 2];
+                  sacc[P.stat_len + q[0] + samp] += sscr[g2 * 2 + 1];
+                }
+              }
+            }
+          } else {
+            sscr[row * 2] = ws_;
+            sscr[row * 2 + 1] = wq_;
+            named_bar_sync(2, kEpiThreads);
+            const int samp = et >> 1, which = et & 1;
+            if (samp < (kBlockM >> rl) && samp < clip.lim[0]) {
+              float a = 0.f;
+              for (int r = samp << rl; r < (samp + 1) << rl; r++) a += sscr[r * 2 + which];
+              sacc[which * P.stat_len + q[0] + samp] += a;
+            }
+          }
+        }
+      }
       }
       // all TMEM reads of this accumulator set are complete (tmem_ld_wait above)
       tc_fence_before();
@@ -395,6 +559,17 @@ __global__ void __launch_bounds__(kThreadsTc, 1) tc_conv_kernel(const __grid_con
       if (lane == 0) {
         if (NCTA == 2) mbar_arrive_cluster(mapa_u32(tempty_bar(acc), 0));   // the leader's barrier counts both CTAs
         else mbar_arrive(tempty_bar(acc));
+      }
+    }
+    if (STATS) {
+      if (P.swap) {
+        const int cch = grp * 32 + lane;          // swap mode has one N tile: channel = TMEM lane
+        if (cch < P.nout) { gpart[cch] = ks; gpart[P.stat_len + cch] = kq; }
+      } else if (P.stat_kind == 1) {
+        flush_nt();
+      } else {
+        named_bar_sync(1, kEpiThreads);
+        for (int i = et; i < 2 * P.stat_len; i += kEpiThreads) gpart[i] = sacc[i];
       }
     }
     if (et == 0) tma_store_wait<0>();
@@ -712,10 +887,27 @@ static int encode_map(CUtensorMap* out, const void* base, const MapDesc& m, int 
 static uint32_t tmem_cols_for(int n) { uint32_t c = 32; while ((int)c < n) c <<= 1; return c; }
 constexpr int kSmemBudget = 227 * 1024;
 
+size_t tc_conv_stats_bytes(int len) { return (size_t)num_sms() * 2 * (size_t)len * sizeof(float); }
+
+bool tc_conv_stats_supported(const ConvPlan& p, int kind, int bias_mod) {
+  // point GEMM (columns = (tap, channel)): a channel must map to ONE accumulator slot of the N tile
+  if (kind == 1) return bias_mod == 0 || (!p.swap && bias_mod >= p.block_n && bias_mod % p.block_n == 0);
+  if (kind == 2) return !p.swap && bias_mod == 0 && p.subs[0].ext[0] <= 1024;
+  return false;
+}
+
 int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, const float* bias, int bias_mod,
-                   int act, float slope, cudaStream_t st) {
+                   int act, float slope, cudaStream_t st, const TcStats* stats) {
   TcConvParams P;
   memset(&P, 0, sizeof(P));
+  size_t stat_smem = 0;
+  if (stats && stats->kind) {
+    if (!tc_conv_stats_supported(p, stats->kind, bias_mod) || !stats->part || stats->len <= 0 ||
+        stats->part_bytes < tc_conv_stats_bytes(stats->len))
+      return B2C_ERR_INVALID;
+    P.stat_kind = stats->kind; P.stat_len = stats->len; P.stat_part = stats->part;
+    stat_smem = p.swap ? 0 : stats->kind == 1 ? 4096 : (((size_t)2 * stats->len + 3) & ~(size_t)3) * sizeof(float) + 1024;
+  }
   const int abox[5] = {p.kb, p.box[3], p.box[2], p.box[1], p.box[0]};
   for (int i = 0; i < p.nmaps; i++) {
     int rc = encode_map(&P.in_maps[i], in, p.maps[i], 5, abox);
@@ -741,7 +933,9 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   for (int s2 = 1; s2 < p.nsubs; s2++)
     for (int i = 0; i < 4; i++) if (p.subs[s2].tiles[i] != p.subs[0].tiles[i]) uniform = 0;
   const int64_t sub_tiles = (int64_t)p.subs[0].tiles[0] * p.subs[0].tiles[1] * p.subs[0].tiles[2] * p.subs[0].tiles[3];
-  static const bool no_pair = getenv("B2C_PAIR") == nullptr;   // measured: no gain yet (r1e) -> opt-in
+  // measured (profiles/r02_exp_pair_tiles.log, isolated launches): D.L2 fwd 1375 -> 1485 TFLOP/s, D.L4 fwd / dgrad
+  // 1311 / 1411 -> 1457 / 1536, G.L5 dgrad 1375 -> 1465, G.L2 fwd 1246 -> 1395: on by default (B2C_NO_PAIR=1: off)
+  static const bool no_pair = getenv("B2C_NO_PAIR") != nullptr;
   const bool pair = !no_pair && !p.swap && uniform && sub_tiles >= 2 && p.block_n % 32 == 0;
   const int ncta = pair ? 2 : 1;
   MapDesc wm;
@@ -761,7 +955,13 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   P.nout = p.nout; P.block_n = p.block_n; P.tiles_n = p.tiles_n; P.kchunks = p.kchunks;
   const uint32_t stage_bytes = ((uint32_t)p.mt * kBlockM + (uint32_t)(w_rows / ncta)) * (uint32_t)p.kb * 2u;
   P.swap = p.swap; P.w_rows = w_rows; P.kb = p.kb;
-  const int fixed = 1024 /*alignment slack*/ + (int)kStagingBytes + 256 /*barriers + tmem slot*/;
+  const int fixed = 1024 /*alignment slack*/ + (int)kStagingBytes + 256 /*barriers + tmem slot*/ + (int)stat_smem;
+  {
+    int sbox2[4] = {p.box[0], p.box[1], p.box[2], p.box[3]};
+    sbox2[p.split_dim] = p.sub_ext;
+    auto lg = [](int v) { int l = 0; while ((1 << l) < v) l++; return l; };
+    P.sb_log[0] = lg(sbox2[3]); P.sb_log[1] = lg(sbox2[2]); P.sb_log[2] = lg(sbox2[1]);
+  }
   int stages = (kSmemBudget - fixed) / (int)stage_bytes;
   if (stages > 8) stages = 8;
   if (const char* e = getenv("B2C_DBG")) P.dbg = atoi(e);      // timing experiments only (8: no MMAs, 16: no loads)
@@ -782,7 +982,8 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   const int sms = num_sms();
   // the attribute is per device; set it on every call (cheap) rather than caching per device
   if (pair) {
-    if (cudaFuncSetAttribute(tc_conv_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
+    auto kern2 = P.stat_kind ? tc_conv_kernel<2, true> : tc_conv_kernel<2, false>;
+    if (cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
       return B2C_ERR_CUDA;
     const int64_t clusters = tiles < sms / 2 ? tiles : sms / 2;
     cudaLaunchConfig_t cfg = {};
@@ -794,13 +995,16 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    if (cudaLaunchKernelEx(&cfg, tc_conv_kernel<2>, P) != cudaSuccess) { cudaGetLastError(); return B2C_ERR_CUDA; }
+    if (cudaLaunchKernelEx(&cfg, kern2, P) != cudaSuccess) { cudaGetLastError(); return B2C_ERR_CUDA; }
+    if (stats) stats->nblocks = (int)(2 * clusters);
     return launched();
   }
-  if (cudaFuncSetAttribute(tc_conv_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
+  auto kern1 = P.stat_kind ? tc_conv_kernel<1, true> : tc_conv_kernel<1, false>;
+  if (cudaFuncSetAttribute(kern1, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess)
     return B2C_ERR_CUDA;
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-  tc_conv_kernel<1><<<grid, kThreadsTc, smem, st>>>(P);
+  kern1<<<grid, kThreadsTc, smem, st>>>(P);
+  if (stats) stats->nblocks = (int)grid;
   return launched();
 }
 
@@ -985,8 +1189,11 @@ static int thin_src_fill(const Geo& g, const void* big, ThinSrc* S) {
 }
 
 int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp, void* out_small, const float* bias,
-                          int act, float slope, cudaStream_t st) {
+                          int act, float slope, cudaStream_t st, const TcStats* stats) {
   if (!tc_thin_gather_supported(g) || Kp > 64 || Kp % 8 != 0) return B2C_ERR_UNSUPPORTED;
+  if (stats && stats->kind && (stats->kind != 2 || stats->len != g.n || !stats->part ||
+                               stats->part_bytes < 2 * tc_conv_stats_bytes(stats->len)))
+    return B2C_ERR_INVALID;
   if ((reinterpret_cast<uintptr_t>(wp) & 15) != 0) return B2C_ERR_UNSUPPORTED;
   ThinGatherParams P;
   memset(&P, 0, sizeof(P));
@@ -1008,12 +1215,19 @@ int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp,
   P.act = act; P.slope = slope;
   P.idesc = idesc_bf16(kBlockM, P.block_n, 0, 0);
   P.tmem_cols = tmem_cols_for(2 * P.block_n);
-  const size_t smem = 1024 + (size_t)(1 + kThinStages + 2) * kThinTile + 256;
-  if (cudaFuncSetAttribute(thin_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+  size_t smem = 1024 + (size_t)(1 + kThinStages + 2) * kThinTile + 256;
+  if (stats && stats->kind) {
+    P.stat_kind = 2; P.stat_len = stats->len; P.stat_part = stats->part;
+    P.vps = g.sd * g.sh * g.sw;
+    smem += (((size_t)2 * stats->len + 3) & ~(size_t)3) * sizeof(float) + 2048;
+  }
+  auto kern = P.stat_kind ? thin_gather_kernel<true> : thin_gather_kernel<false>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
     return B2C_ERR_CUDA;
   const int sms = num_sms();
   const int grid = P.num_tiles < 2 * sms ? P.num_tiles : 2 * sms;        // two resident CTAs per SM
-  thin_gather_kernel<<<grid, kThinThreads, smem, st>>>(P);
+  kern<<<grid, kThinThreads, smem, st>>>(P);
+  if (stats) stats->nblocks = grid;
   return launched();
 }
 

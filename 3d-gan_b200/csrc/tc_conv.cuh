@@ -5,8 +5,14 @@
 
 namespace b2c {
 // out = plan(in, w_packed); bf16 I/O, fp32 accumulate in TMEM.
+// `stats` (optional): sums of the STORED output for the normalisation layer that follows, accumulated in the epilogue:
+// kind 1 = per output channel, kind 2 = per sample; every CTA writes one row part[block][2][len] (nblocks rows are
+// written, returned in `nblocks`), summed afterwards in a fixed order (stat_finalize, norm.cu).
+struct TcStats { int kind, len; float* part; size_t part_bytes; mutable int nblocks; };
+size_t tc_conv_stats_bytes(int len);
+bool tc_conv_stats_supported(const ConvPlan& p, int kind, int bias_mod);
 int tc_conv_launch(const ConvPlan& p, const void* in, const void* w_packed, void* out, const float* bias, int bias_mod,
-                   int act, float slope, cudaStream_t st);
+                   int act, float slope, cudaStream_t st, const TcStats* stats = nullptr);
 // dW[a][b][t] (torch layout, fp32) = sum small[v,a] * big[v*s+k*dl-p, b]; split-K through `ws`.
 bool tc_wgrad_supported(const Geo& g);
 size_t tc_wgrad_workspace(const Geo& g);
@@ -16,7 +22,7 @@ int tc_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw,
 // (no im2col matrix in HBM); wp = [sc][Kp] bf16 as packed by thin_pack(gather).
 bool tc_thin_gather_supported(const Geo& g);
 int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp, void* out_small, const float* bias,
-                          int act, float slope, cudaStream_t st);
+                          int act, float slope, cudaStream_t st, const TcStats* stats = nullptr);   // stats: kind 2 only
 // fused weight gradient of the same layer class: dw[sc][T] fp32 (taps reversed when flip != 0)
 size_t tc_thin_wgrad_workspace(const Geo& g);
 int tc_thin_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw, int flip, void* ws, size_t wsb,

@@ -36,6 +36,9 @@ struct alignas(64) ThinGatherParams {
   int32_t Kp, sc, block_n, num_tiles, act;
   float slope;
   uint32_t idesc, tmem_cols;
+  // per-sample sums of the stored output for the LayerNorm that follows (dcgan.py:161-162), as in tc_conv_kernel
+  int32_t stat_kind, stat_len, vps;   // 0 / 2; samples; voxels (rows) per sample
+  float* stat_part;                   // [gridDim.x][2][stat_len]
 };
 
 // element t (0..63) of row r lives at r*128 + ((t/8) ^ (r & 7))*16 + (t % 8)*2  (SWIZZLE_128B)
@@ -138,6 +141,7 @@ __device__ __forceinline__ void thin_build_row(const ThinSrc& S, const uint16_t*
   }
 }
 
+template <bool STATS>
 __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __grid_constant__ ThinGatherParams P) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -220,10 +224,17 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
     const uint32_t lane_off = (uint32_t)(grp * 32) << 16;
     const int nslab = (P.block_n + 63) >> 6;
     uint32_t it = 0, slab_count = 0;
+    float* sacc = reinterpret_cast<float*>(sgen + (bar0 - sbase) + 256);
+    float* sscr = sacc + ((2 * P.stat_len + 3) & ~3);
+    if (STATS) {
+      for (int i = et; i < 2 * P.stat_len; i += 128) sacc[i] = 0.f;
+      named_bar_sync(2, 128);
+    }
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
       const uint32_t acc = it & 1u, aph = (it >> 1) & 1u;
       mbar_wait(tfull(acc), aph);
       tc_fence_after();
+      float rs = 0.f, rq = 0.f;
       for (int j = 0; j < nslab; j++, slab_count++) {
         const uint32_t sbuf = staging + (slab_count & 1u) * kThinTile;
         if (et == 0) tma_store_wait_read<1>();
@@ -245,12 +256,21 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
         apply_act64(v, P.act, P.slope);
 #pragma unroll
         for (int ch = 0; ch < 8; ch++)
-          if (ch * 8 < ncol)
-            st_shared_v4(sbuf + row * 128 + ((ch ^ (row & 7)) << 4),
-                         pack_bf16x2(__uint_as_float(v[ch * 8 + 0]), __uint_as_float(v[ch * 8 + 1])),
-                         pack_bf16x2(__uint_as_float(v[ch * 8 + 2]), __uint_as_float(v[ch * 8 + 3])),
-                         pack_bf16x2(__uint_as_float(v[ch * 8 + 4]), __uint_as_float(v[ch * 8 + 5])),
-                         pack_bf16x2(__uint_as_float(v[ch * 8 + 6]), __uint_as_float(v[ch * 8 + 7])));
+          if (ch * 8 < ncol) {
+            const uint32_t p0 = pack_bf16x2(__uint_as_float(v[ch * 8 + 0]), __uint_as_float(v[ch * 8 + 1])),
+                           p1 = pack_bf16x2(__uint_as_float(v[ch * 8 + 2]), __uint_as_float(v[ch * 8 + 3])),
+                           p2 = pack_bf16x2(__uint_as_float(v[ch * 8 + 4]), __uint_as_float(v[ch * 8 + 5])),
+                           p3 = pack_bf16x2(__uint_as_float(v[ch * 8 + 6]), __uint_as_float(v[ch * 8 + 7]));
+            st_shared_v4(sbuf + row * 128 + ((ch ^ (row & 7)) << 4), p0, p1, p2, p3);
+            if (STATS && j * 64 + ch * 8 < P.sc) {            // the stored (rounded) values; sc % 8 == 0
+              const uint32_t pk[4] = {p0, p1, p2, p3};
+#pragma unroll
+              for (int i = 0; i < 4; i++) {
+                const float lo = __uint_as_float(pk[i] << 16), hi = __uint_as_float(pk[i] & 0xffff0000u);
+                rs += lo + hi; rq += lo * lo + hi * hi;
+              }
+            }
+          }
         fence_proxy_async();
         named_bar_sync(2, 128);
         if (et == 0) {
@@ -258,9 +278,48 @@ __global__ void __launch_bounds__(kThinThreads, 2) thin_gather_kernel(const __gr
           tma_store_commit();
         }
       }
+      if (STATS) {
+        // rows of the tile are consecutive voxels of the flattened [n][d][h][w] lattice: sample = row / vps.  A warp
+        // whose 32 rows lie in ONE sample (always, when vps % 32 == 0) is reduced with shuffles; thread 0 then adds
+        // the four warp sums in a fixed order.  Warps that straddle a sample boundary leave their rows in the scratch.
+        const int64_t r0 = (int64_t)tile * kBlockM;
+        const bool rv = r0 + row < P.src.rows;
+        const int nrow = rv ? (int)((r0 + row) / P.vps) : -1;
+        const int nfirst = __shfl_sync(0xffffffffu, nrow, 0);
+        const bool uni = __all_sync(0xffffffffu, nrow == nfirst || nrow < 0) && nfirst >= 0;
+        float ws_ = rv ? rs : 0.f, wq_ = rv ? rq : 0.f;
+        if (uni) {
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) { ws_ += __shfl_xor_sync(0xffffffffu, ws_, o); wq_ += __shfl_xor_sync(0xffffffffu, wq_, o); }
+          if (lane == 0) { sscr[grp * 4] = ws_; sscr[grp * 4 + 1] = wq_; sscr[grp * 4 + 2] = __int_as_float(nfirst); }
+        } else {
+          if (lane == 0) sscr[grp * 4 + 2] = __int_as_float(-1);
+          sscr[16 + row * 3] = ws_; sscr[16 + row * 3 + 1] = wq_; sscr[16 + row * 3 + 2] = __int_as_float(nrow);
+        }
+        named_bar_sync(2, 128);
+        if (et == 0) {
+          for (int g2 = 0; g2 < 4; g2++) {
+            const int n = __float_as_int(sscr[g2 * 4 + 2]);
+            if (n >= 0) {
+              if (n < P.stat_len) { sacc[n] += sscr[g2 * 4]; sacc[P.stat_len + n] += sscr[g2 * 4 + 1]; }
+            } else {
+              for (int r = g2 * 32; r < g2 * 32 + 32; r++) {
+                const int nr = __float_as_int(sscr[16 + r * 3 + 2]);
+                if (nr >= 0 && nr < P.stat_len) { sacc[nr] += sscr[16 + r * 3]; sacc[P.stat_len + nr] += sscr[16 + r * 3 + 1]; }
+              }
+            }
+          }
+        }
+        // the scratch is rewritten only after the next tile's slab barriers: thread 0 passes them after its reads
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty(acc));
+    }
+    if (STATS) {
+      named_bar_sync(2, 128);
+      float* part = P.stat_part + (size_t)blockIdx.x * 2 * P.stat_len;
+      for (int i = et; i < 2 * P.stat_len; i += 128) part[i] = sacc[i];
     }
     if (et == 0) tma_store_wait<0>();
   }

@@ -454,7 +454,7 @@ static int pw_wgrad_blocks(int64_t rows) {
 }
 
 int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, const float* bias, int act,
-                float slope, void* ws, size_t wsb, cudaStream_t st) {
+                float slope, void* ws, size_t wsb, cudaStream_t st, const TcStats* stats) {
   if (is_pointwise(g)) {
     const int64_t rows = rows_of(g);
     if (rows == 0) return B2C_OK;
@@ -464,7 +464,7 @@ int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, 
     return launched();
   }
   if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
-    const int rc = tc_thin_gather_launch(g, big, wp, thin_kp(g), out_small, bias, act, slope, st);
+    const int rc = tc_thin_gather_launch(g, big, wp, thin_kp(g), out_small, bias, act, slope, st, stats);
     if (rc != B2C_ERR_UNSUPPORTED) return rc;
   }
   if (!ws || wsb < thin_workspace(g, 0)) return B2C_ERR_WORKSPACE;

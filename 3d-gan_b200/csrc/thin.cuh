@@ -21,8 +21,9 @@ size_t thin_packed_bytes(const Geo& g);
 // torch filter [sc][1][T] (conv) or [sc][1][T] (convT: [x.c][y.c=1][T]) -> gather: [sc][Kp]; scatter: [Kp][sc]
 int thin_pack(const Geo& g, bool gather, const float* w, void* wp, cudaStream_t st, bool flip);
 size_t thin_workspace(const Geo& g, int kind /*0 gather, 1 scatter, 2 wgrad*/);
+struct TcStats;
 int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, const float* bias, int act,
-                float slope, void* ws, size_t wsb, cudaStream_t st);
+                float slope, void* ws, size_t wsb, cudaStream_t st, const TcStats* stats = nullptr);
 int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big, const float* bias, int act,
                  float slope, void* ws, size_t wsb, cudaStream_t st);
 int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void* ws, size_t wsb, cudaStream_t st,

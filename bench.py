@@ -20,7 +20,6 @@ against MEASURED_PEAKS.json; `witness` = the same step on stock torch layers und
 GPU; `cpu_baseline` / `--impl reference` = the reference's CPU path (stock torch layers on the host cores).
 """
 import argparse
-import contextlib
 import json
 import os
 import sys
@@ -66,7 +65,7 @@ def parse():
             raise SystemExit("--global-batch must be a multiple of the number of ranks")
         a.batch = a.global_batch // world
     a.batch = a.batch or DEFAULT_BATCH[a.workload]
-    a.cpu_batch = a.cpu_batch or {"dcgan": 2, "biggan": 1, "stylegan2": 2, "fid": 2}[a.workload]
+    a.cpu_batch = a.cpu_batch or {"dcgan": 2, "biggan": 2, "stylegan2": 2, "fid": 2}[a.workload]
     return a
 
 

@@ -82,11 +82,29 @@ typedef struct {
   int32_t   algo;          /* B2C_ALGO_*                                    */
 } b2c_conv_desc;
 
-/* Epilogue fused into the forward kernels. */
+/* Epilogue fused into the forward kernels: bias, activation, and - for the
+ * BatchNorm3d / LayerNorm that follows the convolution in the reference's
+ * layer tables (dcgan.py:47-65 ConvT -> BatchNorm3d, dcgan.py:161-179
+ * Conv -> LayerNorm, utils.py:62-75, FID_ResNet.py:70-76) - the statistics
+ * of the STORED output y (after bias / activation, rounded to io_dtype):
+ *   B2C_STAT_CHANNEL: stat_sum[c] = sum over (n,d,h,w) of y, stat_sqsum = of y^2   [y.c]
+ *   B2C_STAT_SAMPLE : stat_sum[n] = sum over (c,d,h,w) of y, stat_sqsum = of y^2   [y.n]
+ * accumulated in the GEMM epilogue (warp-shuffle-free shared-memory trees, one
+ * partial row per CTA, fixed-order second stage: deterministic, no atomics),
+ * so the normalisation layer needs no statistics pass over y.  Kernels that
+ * cannot accumulate (fp32 / CUDA-core paths) compute the same sums with one
+ * pass over y inside the same call.  The workspace must then hold
+ * align256(b2c_conv3d_workspace(desc, FWD)) + b2c_conv3d_stats_workspace(desc, kind). */
+#define B2C_STAT_NONE    0
+#define B2C_STAT_CHANNEL 1
+#define B2C_STAT_SAMPLE  2
 typedef struct {
   const float* bias;       /* [y.c] fp32 or NULL                            */
   int32_t      act;        /* B2C_ACT_*                                     */
   float        slope;      /* LeakyReLU negative slope                      */
+  int32_t      stat_kind;  /* B2C_STAT_*                                    */
+  float*       stat_sum;   /* [y.c] or [y.n] fp32, written; or NULL         */
+  float*       stat_sqsum; /* same shape                                    */
 } b2c_fusion;
 
 /* ---- library ------------------------------------------------------- */
@@ -116,6 +134,7 @@ int    b2c_filter_pack(const b2c_conv_desc*, int pass, const float* w_torch,
  * Call sites replaced: dcgan.py:45-70,158-182; utils.py:8-14,47-132;
  * biggan.py:42,78; FID_ResNet.py:65-102,119-125; stylegan.py:164-170.     */
 size_t b2c_conv3d_workspace(const b2c_conv_desc*, int pass);
+size_t b2c_conv3d_stats_workspace(const b2c_conv_desc*, int stat_kind);
 int b2c_conv3d_fwd  (const b2c_conv_desc*, const void* x, const void* w_packed,
                      void* y, const b2c_fusion*, void* ws, size_t ws_bytes,
                      b2c_stream);
@@ -201,6 +220,14 @@ int b2c_ln_act_fwd(const void* x, void* y, int64_t N, int64_t L, int dtype,
                    const float* gamma, const float* beta, float eps, int act,
                    float slope, float* mean, float* rstd, void* ws,
                    size_t ws_bytes, b2c_stream);
+/* The same forward when the producing convolution already delivered the
+ * per-sample sums (b2c_fusion.stat_kind = B2C_STAT_SAMPLE): finalizes mean /
+ * rstd from sum / sqsum [N] and runs only the apply pass (no workspace).     */
+int b2c_ln_act_fwd_stats(const void* x, void* y, int64_t N, int64_t L, int dtype,
+                         const float* gamma, const float* beta, float eps,
+                         int act, float slope, const float* sum,
+                         const float* sqsum, float* mean, float* rstd,
+                         b2c_stream);
 /* dgamma/dbeta [L] fp32 in NDHWC order (may be NULL when the affine is
  * frozen, trainer.py:278-279); dx may be NULL when x needs no grad.         */
 int b2c_ln_act_bwd(const void* x, const void* dy, void* dx, int64_t N,
@@ -322,6 +349,17 @@ int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_t n, int d,
 int b2c_depth_to_space2(const void* src, void* dst, int64_t n, int jd, int jh,
                         int jw, int c, int od, int oh, int ow, int dtype,
                         int inverse, b2c_stream);
+
+/* ---- W-window gather on NDHWC (x [rows, W, C], rows = N*D*H) ------------------ *
+ * y [rows, W/F, (F+2*pad)*C],  y[r, j, v*C + c] = x[r, F*j + v - pad, c] (0 outside).    *
+ * Lowers the narrow stride-1 convolutions of utils.py:57-60,105-109 (32- / 64-channel  *
+ * 3^3 convs at 128^3 / 64^3) and stylegan.py:285-287 to a (F+2*pad)*C -> F*Cout conv   *
+ * with one tap along W and a block-Toeplitz filter: its output [rows, W/F, F*Cout] is  *
+ * the result [rows, W, Cout] itself, M = F*Cout = 128 fills the UMMA tile and half of   *
+ * the issued MACs are useful (a quarter with the three-tap folding).  inverse != 0:    *
+ * the adjoint (overlap-add, gather form), y -> x; used by autograd.                     */
+int b2c_window_w(const void* src, void* dst, int64_t rows, int w, int c, int f,
+                 int pad, int dtype, int inverse, b2c_stream);
 
 #ifdef __cplusplus
 }

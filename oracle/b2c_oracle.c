@@ -245,8 +245,31 @@ int b2c_conv3d_fwd(const b2c_conv_desc* c, const void* x, const void* wp, void* 
   if (!x || !wp || !y) return B2C_ERR_INVALID;
   if (!c->transposed) conv_gather(c, mk(c->x), mk(c->y), x, wp, y, f);
   else                conv_scatter(c, mk(c->y), mk(c->x), x, wp, y, f);
+  /* b2c_fusion.stat_*: sums of the STORED output for the normalisation layer that follows - what
+   * F.batch_norm / F.layer_norm compute first (torch.nn.functional.batch_norm, layer_norm) */
+  if (f && f->stat_kind != B2C_STAT_NONE) {
+    if ((f->stat_kind != B2C_STAT_CHANNEL && f->stat_kind != B2C_STAT_SAMPLE) || !f->stat_sum || !f->stat_sqsum)
+      return B2C_ERR_INVALID;
+    const int64_t vox = (int64_t)c->y.d * c->y.h * c->y.w, C = c->y.c, N = c->y.n;
+    if (f->stat_kind == B2C_STAT_CHANNEL) {
+#pragma omp parallel for schedule(static)
+      for (int64_t ch = 0; ch < C; ch++) {
+        double a = 0, b = 0;
+        for (int64_t r = 0; r < N * vox; r++) { double v = ld(y, r * C + ch, c->io_dtype); a += v; b += v * v; }
+        f->stat_sum[ch] = (float)a; f->stat_sqsum[ch] = (float)b;
+      }
+    } else {
+#pragma omp parallel for schedule(static)
+      for (int64_t n = 0; n < N; n++) {
+        double a = 0, b = 0;
+        for (int64_t e = 0; e < vox * C; e++) { double v = ld(y, n * vox * C + e, c->io_dtype); a += v; b += v * v; }
+        f->stat_sum[n] = (float)a; f->stat_sqsum[n] = (float)b;
+      }
+    }
+  }
   return B2C_OK;
 }
+size_t b2c_conv3d_stats_workspace(const b2c_conv_desc* c, int kind) { (void)c; (void)kind; return 0; }
 
 int b2c_conv3d_dgrad(const b2c_conv_desc* c, const void* dy, const void* wp, void* dx,
                      void* ws, size_t wsb, b2c_stream s) {
@@ -419,6 +442,25 @@ int b2c_bn_act_bwd_apply(const void* x, const void* dy, const void* res, void* d
 
 /* ---- LayerNorm over the whole sample + activation ---------------------- */
 size_t b2c_ln_workspace(int64_t N, int64_t L) { (void)N; (void)L; return 0; }
+/* LayerNorm forward from per-sample sums delivered by the producing convolution (same formula) */
+int b2c_ln_act_fwd_stats(const void* x, void* y, int64_t N, int64_t L, int dt, const float* gamma,
+                         const float* beta, float eps, int act, float slope, const float* sum,
+                         const float* sqsum, float* mean, float* rstd, b2c_stream s) {
+  (void)s;
+  if (!x || !y || !sum || !sqsum || !mean || !rstd || !dt_ok(dt) || N <= 0 || L <= 0) return B2C_ERR_INVALID;
+#pragma omp parallel for schedule(static)
+  for (int64_t n = 0; n < N; n++) {
+    double m = (double)sum[n] / L, var = (double)sqsum[n] / L - m * m; if (var < 0) var = 0;
+    double rs = 1.0 / sqrt(var + (double)eps);
+    mean[n] = (float)m; rstd[n] = (float)rs;
+    for (int64_t e = 0; e < L; e++) {
+      double z = (ld(x, n * L + e, dt) - m) * rs;
+      z = z * (gamma ? gamma[e] : 1.0) + (beta ? beta[e] : 0.0);
+      st(y, n * L + e, dt, act_f(z, act, slope));
+    }
+  }
+  return B2C_OK;
+}
 int b2c_ln_act_fwd(const void* x, void* y, int64_t N, int64_t L, int dt, const float* gamma,
                    const float* beta, float eps, int act, float slope, float* mean, float* rstd,
                    void* ws, size_t wsb, b2c_stream s) {
@@ -852,6 +894,39 @@ int b2c_maxpool3d_bwd(const void* x, const void* dy, void* dx, int64_t n, int d,
           }
   for (int64_t i = 0; i < total; i++) st(dx, i, dt, acc[i]);
   free(acc);
+  return B2C_OK;
+}
+
+/* ---- W-window gather (include/b2c.h b2c_window_w): the im2col of F.conv3d restricted to the W axis and to
+ * F-voxel groups - y[r, j, v*C + c] = x[r, F*j + v - pad, c]; inverse: the adjoint overlap-add ---- */
+int b2c_window_w(const void* src, void* dst, int64_t rows, int w, int c, int f, int pad, int dt, int inverse,
+                 b2c_stream s) {
+  (void)s;
+  if (!src || !dst || !dt_ok(dt) || rows < 0 || w <= 0 || c <= 0 || f <= 0 || pad < 0 || w % f != 0) return B2C_ERR_INVALID;
+  const int win = f + 2 * pad, groups = w / f;
+  if (!inverse) {
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < rows; r++)
+      for (int j = 0; j < groups; j++)
+        for (int v = 0; v < win; v++) {
+          const int wi = f * j + v - pad;
+          for (int ch = 0; ch < c; ch++)
+            st(dst, ((r * groups + j) * (int64_t)win + v) * c + ch, dt,
+               (wi >= 0 && wi < w) ? ld(src, (r * w + wi) * (int64_t)c + ch, dt) : 0.0);
+        }
+  } else {
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < rows; r++)
+      for (int wi = 0; wi < w; wi++)
+        for (int ch = 0; ch < c; ch++) {
+          double a = 0;
+          for (int j = 0; j < groups; j++) {
+            const int v = wi - f * j + pad;
+            if (v >= 0 && v < win) a += ld(src, ((r * groups + j) * (int64_t)win + v) * c + ch, dt);
+          }
+          st(dst, (r * w + wi) * (int64_t)c + ch, dt, a);
+        }
+  }
   return B2C_OK;
 }
 

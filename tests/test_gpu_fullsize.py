@@ -151,6 +151,60 @@ def test_conv_layer_values_at_headline_size(product_path, case):
     assert not bad, bad
 
 
+# name, transposed, cin, cout, in-spatial, batch, kind (1 = per channel for BatchNorm3d, 2 = per sample for LayerNorm)
+STAT_CASES = [
+    ("G.L1", True, 512, 2048, 1, 32, 1),       # dcgan.py:47-48   point GEMM: columns are (tap, channel)
+    ("G.L2", True, 2048, 1024, 4, 32, 1),      # dcgan.py:51-52
+    ("G.L5", True, 256, 128, 32, 32, 1),       # dcgan.py:63-64   swapped epilogue, 8.4 M voxels per channel
+    ("D.L1", False, 1, 128, 128, 64, 2),       # dcgan.py:161-162 one-channel gather kernel, 33.5 M values per sample
+    ("D.L2", False, 128, 256, 64, 64, 2),      # dcgan.py:165-166 CTA pairs
+    ("D.L5", False, 1024, 2048, 8, 64, 2),     # dcgan.py:177-178 two samples per 128-row tile
+]
+
+
+@pytest.mark.parametrize("case", STAT_CASES, ids=lambda c: c[0])
+def test_epilogue_statistics_at_headline_size(product_path, case):
+    """b2c_fusion.stat_*: the BatchNorm3d / LayerNorm statistics a conv accumulates in its GEMM epilogue equal the sums
+    of the tensor it stored, at BASELINE sizes (fp64 reference over the stored bf16 values)."""
+    import ctypes as C
+    from b200conv3d._lib import Fusion
+    name, tr, cin, cout, sp, n, kind = case
+    gpu = Abi(product_path, DEV)
+    L = gpu.lib
+    torch.manual_seed(len(name) + n)
+    k, s_, p_ = (4, 1, 0) if sp == 1 else (4, 2, 1)
+    osp = (sp - 1) * s_ - 2 * p_ + k if tr else (sp + 2 * p_ - k) // s_ + 1
+    desc = make_desc(tr, (n, cin, sp, sp, sp), (n, cout, osp, osp, osp), (k,) * 3, (s_,) * 3, (p_,) * 3, (1,) * 3, BF)
+    x = torch.randn(n, sp, sp, sp, cin, device=DEV, dtype=BF)
+    wshape = (cin, cout, 4, 4, 4) if tr else (cout, cin, 4, 4, 4)
+    w = torch.randn(wshape, device=DEV) / (cin * (8 if tr and sp > 1 else 1 if tr else 64)) ** 0.5
+    bias = torch.randn(cout, device=DEV) * 0.3 if tr else None
+    wp = gpu.pack(desc, 0, w)
+    y = torch.empty(n, osp, osp, osp, cout, dtype=BF, device=DEV)
+    st = torch.full((2, cout if kind == 1 else n), float("nan"), device=DEV)
+    core = (L.b2c_conv3d_workspace(C.byref(desc), 0) + 255) & ~255
+    ws = torch.empty(max(core + L.b2c_conv3d_stats_workspace(C.byref(desc), kind), 16), dtype=torch.uint8, device=DEV)
+    fu = Fusion(gpu._p(bias), 0, 0.0, kind, st[0].data_ptr(), st[1].data_ptr())
+    rc = L.b2c_conv3d_fwd(C.byref(desc), gpu._p(x), gpu._p(wp), gpu._p(y), C.byref(fu), gpu._p(ws), ws.numel(), gpu._st())
+    assert rc == 0, L.b2c_strerror(rc)
+    torch.cuda.synchronize()
+    rs = torch.zeros(st.shape[1], dtype=torch.float64, device=DEV)
+    rq = torch.zeros_like(rs)
+    for i in range(n):                      # fp64 over the stored values, one sample at a time
+        yi = y[i].double()
+        if kind == 1:
+            rs += yi.sum(dim=(0, 1, 2)); rq += (yi * yi).sum(dim=(0, 1, 2))
+        else:
+            rs[i] = yi.sum(); rq[i] = (yi * yi).sum()
+    count = y.numel() // st.shape[1]
+    mean_o, mean_r = st[0].double() / count, rs / count
+    var_o, var_r = st[1].double() / count - mean_o ** 2, rq / count - mean_r ** 2
+    e = {"mean_err_over_std": ((mean_o - mean_r).abs() / var_r.sqrt()).max().item(),
+         "var_rel_err": ((var_o - var_r).abs() / var_r).max().item()}
+    _note("epilogue stats %s b%d" % (name, n), **e)
+    assert e["mean_err_over_std"] < 1e-5 and e["var_rel_err"] < 2e-5, e
+
+
 @pytest.mark.parametrize("n,c,s", [(32, 128, 64), (64, 128, 64), (32, 256, 32), (64, 2048, 4)])
 def test_layernorm_lrelu_values_at_headline_size(n, c, s):
     """dcgan.py:162-179 LayerNorm([C,D,H,W]) + LeakyReLU(0.2), forward and backward (dx, full-shape dgamma / dbeta)
@@ -251,7 +305,9 @@ def _grad_report(tag, ours, ref, wit=None):
         if b.norm().item() < 1e-4 * gmax * b.numel() ** 0.5:
             rows[k] = ("zero", a.norm().item(), w.norm().item() if w is not None else float("nan"))
         else:
-            rows[k] = ("l2", ((a - b).norm() / b.norm()).item(), ((w - b).norm() / b.norm()).item() if w is not None else float("nan"))
+            # fewer than 64 elements (dcgan.py:67: the one bias of ConvT(128 -> 1)): the "norm" is a handful of draws
+            rows[k] = ("l2" if b.numel() >= 64 else "few", ((a - b).norm() / b.norm()).item(),
+                       ((w - b).norm() / b.norm()).item() if w is not None else float("nan"))
     _note(tag, **{k: v[1] for k, v in rows.items()})
     if wit is not None:
         _note(tag + " (witness)", **{k: v[2] for k, v in rows.items()})
@@ -259,7 +315,13 @@ def _grad_report(tag, ours, ref, wit=None):
 
 
 def _assert_grads(rows):
-    bad = {k: v for k, v in rows.items() if not (v[1] <= max(TOL, WIT * v[2]) if v[0] == "l2" else v[1] <= 2 * v[2] + 1e-30)}
+    def ok(v):
+        if v[0] == "l2":
+            return v[1] <= max(TOL, WIT * v[2])
+        if v[0] == "few":                      # a scalar's error is one sample of the rounding noise, not a statistic
+            return v[1] <= max(2.5 * TOL, 3 * v[2])
+        return v[1] <= 2 * v[2] + 1e-30
+    bad = {k: v for k, v in rows.items() if not ok(v)}
     assert not bad, bad
 
 
