@@ -27,10 +27,11 @@ class _timed:
     """Bracket one C-ABI conv launch with CUDA events on its stream when bench.py has
     switched per-launch profiling on (PROFILE is a list)."""
 
-    def __init__(self, pas, desc, fold=1):
+    def __init__(self, pas, desc, fold=1, orig=None):
         self.on = PROFILE is not None
         if self.on:       # W-folded launches are reported with the ORIGINAL channel counts (useful FLOPs)
-            self.key = (pas, bool(desc.transposed), desc.x.n, desc.x.c // fold, desc.x.d, desc.y.c // fold, desc.y.d,
+            xc, yc = orig if orig is not None else (desc.x.c // fold, desc.y.c // fold)
+            self.key = (pas, bool(desc.transposed), desc.x.n, xc, desc.x.d, yc, desc.y.d,
                         desc.k[0], desc.stride[0], desc.pad[0], desc.dil[0])
 
     def __enter__(self):
@@ -175,10 +176,11 @@ def _triple(v):
 
 class Geom:
     """Static geometry of one conv / conv-transpose call."""
-    __slots__ = ("transposed", "k", "stride", "pad", "dil", "out_pad", "fold")
+    __slots__ = ("transposed", "k", "stride", "pad", "dil", "out_pad", "fold", "orig")
 
     def __init__(self, transposed, k, stride, pad, dil, out_pad=(0, 0, 0)):
-        self.fold = 1                 # W-folding factor of the launch (profiling only)
+        self.fold = 1                 # W-folding factor of the launch (output channels = fold x the layer's)
+        self.orig = None              # (Cin, Cout) of the layer when the launch runs a re-shaped problem (profiling)
         self.transposed, self.k = bool(transposed), tuple(k)
         self.stride, self.pad, self.dil = _triple(stride), _triple(pad), _triple(dil)
         self.out_pad = _triple(out_pad)
@@ -337,7 +339,7 @@ class _ConvFn(Function):
             nws = ((nws + 255) & ~255) + L.b2c_conv3d_stats_workspace(C.byref(desc), stats["kind"])
             stats["sum"], stats["sqsum"] = st_buf[0], st_buf[1]
         ws = _ws(nws, x)
-        with _dev(x), _timed("fwd", desc, g.fold):
+        with _dev(x), _timed("fwd", desc, g.fold, g.orig):
             check(L.b2c_conv3d_fwd(C.byref(desc), _ptr(xb), _ptr(wp), _ptr(y), C.byref(fu),
                                    _ptr(ws), ws.numel(), _stream(x)), "conv3d_fwd")
         ctx.g, ctx.act, ctx.slope, ctx.cd = g, int(act), float(slope), cd
@@ -369,7 +371,7 @@ class _ConvFn(Function):
                 wp = _packed_filter(w, desc, PASS_DGRAD, cd)
                 dxb = torch.empty_like(xb)
                 ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_DGRAD), xb)
-                with _dev(xb), _timed("dgrad", desc, g.fold):
+                with _dev(xb), _timed("dgrad", desc, g.fold, g.orig):
                     check(L.b2c_conv3d_dgrad(C.byref(desc), _ptr(gyb), _ptr(wp), _ptr(dxb), _ptr(ws),
                                              ws.numel(), _stream(xb)), "conv3d_dgrad")
             dx = from_ndhwc(dxb)
@@ -383,7 +385,7 @@ class _ConvFn(Function):
             dw = slot if slot is not None else (torch.empty(w.shape, dtype=torch.float32, device=w.device) if need_w else None)
             db = torch.empty(cout, dtype=torch.float32, device=w.device) if need_b else None
             ws = _ws(L.b2c_conv3d_workspace(C.byref(desc), PASS_WGRAD), xb)
-            with _dev(xb), _timed("wgrad", desc, g.fold):
+            with _dev(xb), _timed("wgrad", desc, g.fold, g.orig):
                 check(L.b2c_conv3d_wgrad(C.byref(desc), _ptr(xb), _ptr(gyb), _ptr(dw), _ptr(db),
                                          _ptr(ws), ws.numel(), _stream(xb)), "conv3d_wgrad")
             if dw is not None and w.dtype != torch.float32:
@@ -438,6 +440,9 @@ def conv3d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, act=
     g = Geom(False, tuple(weight.shape[2:]), stride, padding, dilation)
     if _s2d_applies(x, weight, g):
         return _conv3d_s2d(x, weight, bias, g, _act_id(act), slope, stats)
+    win = _window_factor(x, weight, g)
+    if win > 1:
+        return _conv3d_windowed(x, weight, bias, g, _act_id(act), slope, win, stats)
     fold = _fold_factor(x, weight, g)
     if fold > 1:
         return _conv3d_folded(x, weight, bias, g, _act_id(act), slope, fold, stats)
@@ -618,6 +623,90 @@ def _conv3d_folded(x, weight, bias, g, act, slope, f, stats=None):
     g2 = Geom(False, tuple(w2.shape[2:]), 1, (g.pad[0], g.pad[1], 1 if w2.shape[4] == 3 else 0), 1)
     g2.fold = f
     return _with_stats(_ConvFn.apply, (_fold_w(x, f), w2, b2, g2, act, slope), stats, f)   # unfolded by _ConvFn
+
+
+# ---- W-window lowering of narrow 3-tap convolutions (second generation of the folding above) -------------------
+# Folding F voxels into the channel axis keeps THREE taps along W, of which the outer two use one of their F
+# voxel blocks: 1/2 (F = 2) or 1/4 (F = 4) of the issued MACs are useful, and with F*Cout = 64 half of the 128-row
+# UMMA tile is padding.  Gathering, per group of F output voxels, the F + 2 input voxels it needs
+# (b2c_window_w: [rows, W, C] -> [rows, W/F, (F+2)*C], one extra HBM pass over 1.5x the input) leaves ONE tap along W:
+# a (F+2)*Cin -> F*Cout convolution with a block-Toeplitz filter, 3 / (F + 2) of its MACs useful, and F = 128 / Cout
+# fills the tile: 32 -> 32 at 128^3 becomes 192 -> 128 with 9 taps (half of the MACs useful, 6.75 row requests per
+# output voxel instead of 13.5), 64 -> 64 at 64^3 becomes 256 -> 128 (three quarters useful).  The weight gradient
+# comes back through the index_select that builds the filter, the data gradient through the adjoint gather.
+WINDOW = [True]
+
+
+def _window_factor(x, weight, g):
+    if not WINDOW[0] or g.transposed or x.dim() != 5:
+        return 1
+    cout, cin, kd, kh, kw = weight.shape
+    if g.stride != (1, 1, 1) or g.dil != (1, 1, 1) or kw != 3 or g.pad[2] != 1 or cout not in (32, 64):
+        return 1
+    f = 128 // cout
+    if cin % 8 or cin < 16 or (f + 2) * cin > 512 or x.shape[4] % f or x.shape[4] // f < 2:
+        return 1
+    if compute_dtype(x) != torch.bfloat16 or not (x.is_cuda or _lib.is_host()):
+        return 1
+    return f
+
+
+_win_index_cache = {}
+
+
+def _win_index(f, device):
+    """idx[vo, vi] = tap kw = vi - vo that connects window voxel vi to output voxel vo of the group, or 3 (a zero slot)."""
+    key = (f, str(device))
+    if key not in _win_index_cache:
+        idx = torch.full((f, f + 2), 3, dtype=torch.long)
+        for vo in range(f):
+            for k in range(3):
+                idx[vo, vo + k] = k
+        _win_index_cache[key] = idx.reshape(-1).to(device)
+    return _win_index_cache[key]
+
+
+def window_filter(weight, f):
+    """[Cout, Cin, kd, kh, 3] -> block-Toeplitz [F*Cout, (F+2)*Cin, kd, kh, 1] (differentiable)."""
+    cout, cin, kd, kh, _ = weight.shape
+    wz = torch.cat([weight, weight.new_zeros(cout, cin, kd, kh, 1)], dim=4)
+    wf = wz.index_select(4, _win_index(f, weight.device)).reshape(cout, cin, kd, kh, f, f + 2)
+    return wf.permute(4, 0, 5, 1, 2, 3).reshape(f * cout, (f + 2) * cin, kd, kh, 1)
+
+
+class _WindowWFn(Function):
+    """x [N,C,D,H,W] -> [N,(F+2)*C,D,H,W/F]: the F+2 input voxels of every group of F output voxels (b2c_window_w)."""
+
+    @staticmethod
+    def forward(ctx, x, f):
+        _check_device(x)
+        cd = compute_dtype(x)
+        xb = to_ndhwc(x.detach(), cd)
+        n, d, h, w, c = xb.shape
+        yl, y = alloc_out(n, d, h, w // f, (f + 2) * c, cd, x.device)
+        with _dev(x):
+            check(_lib.lib().b2c_window_w(_ptr(xb), _ptr(y), n * d * h, w, c, f, 1, _dt(cd), 0, _stream(x)), "window_w")
+        ctx.meta = (n, d, h, w, c, f, cd, x.dtype)
+        return yl
+
+    @staticmethod
+    def backward(ctx, gy):
+        n, d, h, w, c, f, cd, x_dtype = ctx.meta
+        g = to_ndhwc(gy, cd)
+        dxl, dx = alloc_out(n, d, h, w, c, cd, gy.device)
+        with _dev(gy):
+            check(_lib.lib().b2c_window_w(_ptr(g), _ptr(dx), n * d * h, w, c, f, 1, _dt(cd), 1, _stream(gy)), "window_w")
+        return (dxl if x_dtype == cd else dxl.to(x_dtype)), None
+
+
+def _conv3d_windowed(x, weight, bias, g, act, slope, f, stats=None):
+    cout, cin = weight.shape[0], weight.shape[1]
+    w2 = window_filter(weight, f)
+    b2 = None if bias is None else bias.repeat(f)
+    g2 = Geom(False, tuple(w2.shape[2:]), 1, (g.pad[0], g.pad[1], 0), 1)
+    g2.fold, g2.orig = f, (cin, cout)
+    xw = _WindowWFn.apply(x, f)
+    return _with_stats(_ConvFn.apply, (xw, w2, b2, g2, act, slope), stats, f)        # unfolded by _ConvFn (same storage)
 
 
 def conv_transpose3d(x, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1,
