@@ -46,7 +46,9 @@ def grad_slot(p):
     if not red.armed or red.taken[i] or not p.requires_grad or p.grad is not None:
         return None
     red.taken[i] = True
-    return red.slots[i]
+    # a FRESH view object: autograd adopts a returned gradient without a copy only when nobody else holds that tensor
+    # object (AccumulateGrad's use_count test) - the reducer keeps `slots[i]`, so the kernel gets its own alias
+    return red.slots[i].view(red.slots[i].shape)
 
 
 class GradReducer:
@@ -87,6 +89,7 @@ class GradReducer:
         self.inflight = {}                      # bucket index -> work handle
         self.deferred = False                   # a second backward() was seen: reduce everything in finish()
         self.armed = False
+        self.copied = 0
         self.stream = torch.cuda.Stream(device=dev) if self.cuda else None
         self.handles = [p.register_post_accumulate_grad_hook(self._hook) for p in self.params]
         for i, p in enumerate(self.params):
@@ -99,6 +102,7 @@ class GradReducer:
         every trainable parameter (StyleGAN2Loss.step_D: 2) - a bucket is reduced when the last one has written it."""
         self.inflight, self.deferred = {}, False
         self.taken = [False] * len(self.params)
+        self.copied = 0                               # gradients that had to be copied into their slot this pass
         self.active = [[i for i in b if self.params[i].requires_grad] for b in self.buckets]
         self.pending = [len(a) * int(backwards) for a in self.active]
         self.armed = self.world > 1
@@ -112,6 +116,7 @@ class GradReducer:
             # a gradient that was not written into its slot (dtype / layout / produced by a stock torch op)
             slot.copy_(p.grad)
             p.grad = slot
+            self.copied += 1
         bi = self.bucket_of[i]
         self.pending[bi] -= 1
         if self.pending[bi] == 0 and not self.deferred and self.overlap:

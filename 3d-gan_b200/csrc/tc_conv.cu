@@ -1178,6 +1178,9 @@ static int thin_src_fill(const Geo& g, const void* big, ThinSrc* S) {
   for (int i = 0; i < 3; i++) k4s2 = k4s2 && g.k[i] == 4 && g.s[i] == 2 && g.p[i] == 1 && g.dl[i] == 1;
   k4s2 = k4s2 && g.bd == 2 * g.sd && g.bh == 2 * g.sh && g.bw == 2 * g.sw;
   S->fast_k4s2 = (k4s2 && g.sw % 32 == 0) ? 2 : 0;
+  bool k3s1 = g.bd == g.sd && g.bh == g.sh && g.bw == g.sw && g.sw % 32 == 0;
+  for (int i = 0; i < 3; i++) k3s1 = k3s1 && g.k[i] == 3 && g.s[i] == 1 && g.p[i] == 1 && g.dl[i] == 1;
+  if (k3s1) S->fast_k4s2 = 3;           // thin_build_row: 3 = the k3 / s1 / p1 line loader
   for (int kd = 0, t = 0; kd < g.k[0]; kd++)
     for (int kh = 0; kh < g.k[1]; kh++)
       for (int kw = 0; kw < g.k[2]; kw++, t++) {

@@ -117,6 +117,53 @@ __device__ __forceinline__ void thin_build_row(const ThinSrc& S, const uint16_t*
         if (l & 1) st_shared_v4(thin_chunk(dst, r, l >> 1), w4[0], w4[1], w4[2], w4[3]);
       }
     }
+  } else if (S.fast_k4s2 == 3) {
+    // k = 3, stride 1, pad 1, sw % 32 == 0 (biggan.py:78 input conv, the data gradient of biggan.py:42): the 32 lanes
+    // of a warp are 32 consecutive ow of ONE (n, od, oh) line.  Taps (kd, kh, 0..2) = input elements ow-1 .. ow+1:
+    // each lane loads its own element of the nine (kd, kh) lines - nine coalesced 64-byte warp loads instead of 27
+    // predicated scalar ones - and takes the outer two from its neighbours through warp shuffles.
+    const uint32_t v0 = (uint32_t)tile * kBlockM + (uint32_t)(warp * 32);
+    if (v0 >= (uint32_t)S.rows) {
+#pragma unroll
+      for (int c = 0; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);
+    } else {
+      uint32_t t = v0 / (uint32_t)g.sw;
+      const int ow = (int)(v0 - t * (uint32_t)g.sw) + lane;
+      const uint32_t t2 = t / (uint32_t)g.sh;
+      const int oh = (int)(t - t2 * (uint32_t)g.sh);
+      const uint32_t n = t2 / (uint32_t)g.sd;
+      const int od = (int)(t2 - n * (uint32_t)g.sd);
+      const int sH = g.bw, sD = g.bh * g.bw;
+      const int base = ((int)n * g.bd + od - 1) * sD + (oh - 1) * sH + ow;
+      const bool left = lane == 0 && ow > 0, right = lane == 31 && ow + 1 < g.bw;
+      uint32_t mid[9], edge[9];
+#pragma unroll
+      for (int l = 0; l < 9; l++) {
+        const int id = od - 1 + l / 3, ih = oh - 1 + l % 3;
+        const bool ok = id >= 0 && id < g.bd && ih >= 0 && ih < g.bh;     // warp-uniform
+        const uint16_t* px = xb + base + (l / 3) * sD + (l % 3) * sH;
+        mid[l] = ok ? (uint32_t)__ldg(px) : 0u;
+        edge[l] = 0u;
+        if (ok && left) edge[l] = (uint32_t)__ldg(px - 1);
+        if (ok && right) edge[l] = (uint32_t)__ldg(px + 1);
+      }
+      uint32_t e[32];
+#pragma unroll
+      for (int l = 0; l < 9; l++) {
+        uint32_t e0 = __shfl_up_sync(0xffffffffu, mid[l], 1), e2 = __shfl_down_sync(0xffffffffu, mid[l], 1);
+        if (lane == 0) e0 = edge[l];
+        if (lane == 31) e2 = edge[l];
+        e[3 * l] = e0; e[3 * l + 1] = mid[l]; e[3 * l + 2] = e2;
+      }
+#pragma unroll
+      for (int i = 27; i < 32; i++) e[i] = 0u;
+#pragma unroll
+      for (int c = 0; c < 4; c++)
+        st_shared_v4(thin_chunk(dst, r, c), e[8 * c] | (e[8 * c + 1] << 16), e[8 * c + 2] | (e[8 * c + 3] << 16),
+                     e[8 * c + 4] | (e[8 * c + 5] << 16), e[8 * c + 6] | (e[8 * c + 7] << 16));
+#pragma unroll
+      for (int c = 4; c < 8; c++) st_shared_v4(thin_chunk(dst, r, c), 0u, 0u, 0u, 0u);    // the weight gradient reads 64 taps
+    }
   } else
   if (v >= S.rows) {
 #pragma unroll

@@ -48,6 +48,9 @@ THIN_CASES = [
     (False, 1, 64, 4, 2, 1, 1, (8, 10, 12), 3),     # ragged spatial extents
     (False, 1, 32, 7, 2, 3, 1, (12, 12, 12), 2),    # FID_ResNet.py:119 stem (Kp = 344)
     (False, 1, 64, 3, 1, 1, 1, (6, 7, 8), 2),       # biggan.py:78 input conv (Kp = 32)
+    (False, 1, 64, 3, 1, 1, 1, (4, 5, 32), 2),      # same, W % 32 == 0: the k3 / s1 line loader (shuffled neighbours)
+    (False, 1, 32, 3, 1, 1, 1, (3, 3, 64), 3),      # two warps per W line
+    (False, 64, 1, 3, 1, 1, 1, (4, 5, 32), 2),      # biggan.py:42 output conv: its data gradient takes the line loader
     (True, 16, 1, 4, 2, 1, 1, (8, 8, 8), 2),        # dcgan.py:67 G head
     (True, 128, 1, 4, 2, 1, 1, (6, 6, 6), 2),       # dcgan.py:67 at full width
     # SMALL side has one channel, stride 1: mirrored problem (thin_mode == 2)

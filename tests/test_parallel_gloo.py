@@ -155,9 +155,14 @@ def _worker_slots(rank, world, port, q, oracle):
     lo, hi = rank * 2, rank * 2 + 2
     step.noise = lambda n: zs[lo:hi]
     step.D_step(reals[lo:hi])
+    copied_d = rd.copied
     adopted_d = [p.grad.data_ptr() == rd.slots[i].data_ptr() for i, p in enumerate(d.parameters())]
     gd = [p.grad.clone() for p in d.parameters()]
     step.G_step(2)
+    # G: the two filters were WRITTEN into their slots by the weight-gradient kernel and adopted by autograd without a
+    # copy; only the two biases and the BatchNorm affine pair (tiny) go through the hook's copy.  D ran D(real) and
+    # D(fake) as two passes here (CPU), so autograd summed two contributions per parameter before accumulating.
+    assert rg.copied == 4 and copied_d <= 4, (copied_d, rg.copied)
     adopted_g = [p.grad.data_ptr() == rg.slots[i].data_ptr() for i, p in enumerate(g.parameters())]
     gg = [p.grad.clone() for p in g.parameters()]
     npy = lambda ts: [t.detach().numpy().copy() for t in ts]
