@@ -103,6 +103,12 @@ _SIGNATURES = {
     "b2c_maxpool3d_fwd": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_maxpool3d_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b2c_window_w": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b2c_peer_alloc": (_i32, [_sz, C.POINTER(_vp), C.c_char_p]),
+    "b2c_peer_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),
+    "b2c_peer_close": (_i32, [_vp]),
+    "b2c_peer_free": (_i32, [_vp]),
+    "b2c_peer_allreduce_avg": (_i32, [C.POINTER(_vp), C.POINTER(_vp), _i32, _i32, _i64, C.c_uint32, _i32, _vp]),
+    "b2c_peer_error": (C.c_uint, []),
     "b2c_depth_to_space2": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
 EXPORTS = tuple(_SIGNATURES)

@@ -399,14 +399,16 @@ def _act_id(act):
     return ACT_IDS[act]
 
 
-STATS = [True]      # False: never ask the conv epilogue for statistics (the norm layers run their own pass)
+# True: ask the conv epilogue for statistics wherever a layer wants them; False: never (the norm layers run their own
+# pass); "channel" / "sample": only that kind (measurement switch, bench.py --fused-stats)
+STATS = [True]
 _STAT_IDS = {"channel": STAT_CHANNEL, "sample": STAT_SAMPLE}
 
 
 def _with_stats(fn_apply, y_args, stats, fold=1):
     """Run a conv Function; attach the statistics its epilogue accumulated to the output tensor (consumed by
     batch_norm_act / layer_norm_act when the tensor reaches them unmodified)."""
-    if stats is None or not STATS[0]:
+    if stats is None or not STATS[0] or (STATS[0] is not True and STATS[0] != stats):
         return fn_apply(*y_args)
     holder = {"kind": _STAT_IDS[stats]}
     y = fn_apply(*y_args, holder)

@@ -83,8 +83,9 @@ class GanStep:
                 errD = errD_fake - errD_real
             errD.backward()
         if self.reducer_d is not None:
-            self.reducer_d.finish()
-        self.optimizerD.step()
+            self.reducer_d.step(self.optimizerD)      # the update follows the averaged buckets one by one
+        else:
+            self.optimizerD.step()
         for p in self.netD.parameters():
             p.requires_grad = False
         return errD_real.detach(), errD_fake.detach()
@@ -101,8 +102,9 @@ class GanStep:
             errG = -self.netD(fake).mean()
             errG.backward()
         if self.reducer_g is not None:
-            self.reducer_g.finish()
-        self.optimizerG.step()
+            self.reducer_g.step(self.optimizerG)
+        else:
+            self.optimizerG.step()
         for p in self.netG.parameters():
             p.requires_grad = False
         return errG.detach(), fake.detach()

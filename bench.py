@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--z", type=int, default=512)
     ap.add_argument("--two-pass-d", action="store_true",
                     help="dcgan: D(real), D(fake) as two passes, the reference's own schedule (trainer.py:239-241)")
+    ap.add_argument("--fused-stats", default="all", choices=["all", "none", "channel", "sample"],
+                    help="which norm statistics ride in the conv epilogue (measurement switch; default all)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--witness", dest="witness", action="store_true", default=None,
@@ -328,6 +330,12 @@ class GanWorkload:
     def finish(self):
         pass
 
+    def nets(self):
+        return [self.step.netG, self.step.netD]
+
+    def reducer(self):
+        return self.step.reducer_d
+
     def extra_config(self):
         return {"d_step": ("D(real) and D(fake) of trainer.py:222-241 run as one pass over the concatenated batch "
                            "(no batch-coupled or per-call state in D: same per-sample arithmetic)"
@@ -388,12 +396,13 @@ class StyleGan2Workload:
             q.requires_grad = True
         self.D.zero_grad()
         if self.red_d is not None:
-            self.red_d.begin()
+            self.red_d.begin(backwards=2)       # step_D calls backward() for the generated and for the real logits
         with torch.autocast("cuda", dtype=torch.bfloat16):
             out = self.step_D(1, real, self._noise())
         if self.red_d is not None:
-            self.red_d.finish()
-        self.optD.step()
+            self.red_d.step(self.optD)
+        else:
+            self.optD.step()
         for q in self.D.parameters():
             q.requires_grad = False
         return out
@@ -408,8 +417,9 @@ class StyleGan2Workload:
         with torch.autocast("cuda", dtype=torch.bfloat16):
             out = self.step_G(1, self._noise())
         if self.red_g is not None:
-            self.red_g.finish()
-        self.optG.step()
+            self.red_g.step(self.optG)
+        else:
+            self.optG.step()
         for q in self.G.parameters():
             q.requires_grad = False
         return out
@@ -439,6 +449,12 @@ class StyleGan2Workload:
 
     def finish(self):
         pass
+
+    def nets(self):
+        return [self.G, self.D]
+
+    def reducer(self):
+        return self.red_d
 
     def extra_config(self):
         return {"losses": "StyleGAN2Loss.step_D / step_G (stylegan.py:39-99), style_mixing_prob 0.9, step index 1"}
@@ -523,6 +539,7 @@ def run_ours(a):
     import b200conv3d as B  # noqa: F401
     from b200conv3d import _lib, functional as BF
 
+    BF.STATS[0] = {"all": True, "none": False}.get(a.fused_stats, a.fused_stats)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -645,6 +662,20 @@ def run_ours(a):
         json.dump({"ms_per_step": ms_step, "conv_ms_profiled_step": conv_ms, "rows": rows},
                   open(a.profile_json, "w"), indent=1)
     extra = wl.extra_config()
+    if world > 1 and hasattr(wl, "nets"):
+        # data-parallel invariants after the timed steps: every replica holds the same, finite parameters (the
+        # averaging is deterministic and identical on all ranks), and which transport averaged the gradients
+        chk = torch.stack([torch.stack([q.detach().double().sum(), q.detach().double().abs().sum()])
+                           for net in wl.nets() for q in net.parameters()]).sum(0)
+        allc = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        extra["replicas_identical"] = bool(all(torch.equal(c, allc[0]) for c in allc)) and \
+            bool(torch.isfinite(chk).all().item())
+        red = wl.reducer()
+        extra["gradient_averaging"] = ("b2c_peer_allreduce_avg over NVLink peer memory, %d blocks" % red.comm.CTAS
+                                       if red is not None and red.comm is not None else "NCCL all-reduce (AVG)")
+        if _lib.lib().b2c_peer_error() != 0:
+            raise SystemExit("bench.py: a peer all-reduce timed out (b2c_peer_error)")
     del wl
     torch.cuda.empty_cache()
 
@@ -684,6 +715,8 @@ def run_ours(a):
                   "l2": "inputs larger than L2: distinct input batches of %d MB rotate, per-step activations > 10 GB"
                         % (b * VOX * 4 >> 20)}
         config.update(extra)
+        if a.fused_stats != "all":
+            config["fused_stats"] = a.fused_stats
         line = {
             "metric": metric, "value": value, "unit": unit, "n_gpus": world,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "steps_per_sec": 1e3 / ms_step,

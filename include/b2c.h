@@ -361,6 +361,45 @@ int b2c_depth_to_space2(const void* src, void* dst, int64_t n, int jd, int jh,
 int b2c_window_w(const void* src, void* dst, int64_t rows, int w, int c, int f,
                  int pad, int dtype, int inverse, b2c_stream);
 
+/* ---- gradient averaging over NVLink peer memory ----------------------- *
+ * Replaces the gradient reduction of nn.DataParallel (trainer.py:70-72: the replicas'      *
+ * gradients are summed onto GPU 0; with batch-mean losses, trainer.py:228-241,272, that is *
+ * the average over the global batch).  One process per GPU; every rank keeps its gradient  *
+ * buckets in memory its peers can address (CUDA IPC over NVLink / NVSwitch):               *
+ *   b2c_peer_alloc  cudaMalloc + zero fill + export handle (64 bytes, to be sent to peers) *
+ *   b2c_peer_open   map a peer's allocation from its handle (enables peer access)          *
+ *   b2c_peer_close / b2c_peer_free   undo the above                                        *
+ * b2c_peer_allreduce_avg averages `count` fp32 values IN PLACE over `world` ranks with ONE *
+ * kernel per rank (two-shot over peer pointers): rank r waits until every peer's kernel    *
+ * has started (their gradients are then complete: stream order), reads slice r of every    *
+ * rank's bucket over NVLink, adds the `world` values in rank order 0, 1, ... (every rank   *
+ * therefore ends with bit-identical values, and the same values run after run), scales by  *
+ * 1 / world and writes the result into slice r of EVERY rank's bucket; a second flag       *
+ * exchange tells each rank that all of its slices have landed.  The kernel is small on     *
+ * purpose - `ctas` blocks (<= B2C_PEER_MAX_CTAS) of 192 threads, <= 80 registers, no      *
+ * shared memory - so that its blocks fit on an SM NEXT TO a resident block of the          *
+ * persistent convolution kernels of the backward pass it overlaps (a collective that       *
+ * takes whole SMs makes the statically scheduled 148-block conv grids wait for it).        *
+ *   bufs[i]   (host array, `world` entries) device address of the bucket on rank i, as     *
+ *             mapped in THIS process (bufs[rank] = the local allocation)                   *
+ *   flags[i]  likewise: rank i's flag block, B2C_PEER_FLAG_BYTES, zero at start, never     *
+ *             reset: `seq` must be 1, 2, 3, ... over the calls that share the flag blocks, *
+ *             the same sequence (and the same `ctas`) on every rank                        *
+ * Calls that share flag blocks must be ordered on one stream per rank.  A peer that does   *
+ * not arrive within ~10 s makes the kernel give up (result undefined) and                  *
+ * b2c_peer_error() return nonzero from then on.                                            */
+#define B2C_PEER_MAX_WORLD 8
+#define B2C_PEER_MAX_CTAS 160
+#define B2C_PEER_FLAG_BYTES (B2C_PEER_MAX_CTAS * 16 * 4)
+#define B2C_PEER_HANDLE_BYTES 64
+int b2c_peer_alloc(size_t bytes, void** ptr, unsigned char* handle /*[B2C_PEER_HANDLE_BYTES]*/);
+int b2c_peer_open(const unsigned char* handle, void** ptr);
+int b2c_peer_close(void* ptr);
+int b2c_peer_free(void* ptr);
+int b2c_peer_allreduce_avg(void* const* bufs, void* const* flags, int rank, int world,
+                           int64_t count, uint32_t seq, int ctas, b2c_stream);
+unsigned b2c_peer_error(void);
+
 #ifdef __cplusplus
 }
 #endif

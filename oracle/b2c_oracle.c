@@ -953,3 +953,49 @@ int b2c_depth_to_space2(const void* src, void* dst, int64_t n, int jd, int jh, i
           }
   return B2C_OK;
 }
+
+/* ---- gradient averaging over peer memory (include/b2c.h b2c_peer_*): host stand-in.  The "ranks" are buffers of ONE
+ * process; a call does rank `rank`'s share of the two-shot scheme - slice `rank` of every buffer is summed in rank
+ * order (fp32, like the kernel), scaled by 1 / world and written back into every buffer - so calling it once per rank
+ * (any order: the slices are disjoint) averages the buckets.  No flags are needed on the host. ---- */
+int b2c_peer_alloc(size_t bytes, void** ptr, unsigned char* handle) {
+  if (!ptr || !handle || bytes == 0) return B2C_ERR_INVALID;
+  void* p = calloc(1, bytes);
+  if (!p) return B2C_ERR_CUDA;
+  memset(handle, 0, B2C_PEER_HANDLE_BYTES);
+  memcpy(handle, &p, sizeof(p));              /* same-process "handle": the address itself */
+  *ptr = p;
+  return B2C_OK;
+}
+int b2c_peer_open(const unsigned char* handle, void** ptr) {
+  if (!ptr || !handle) return B2C_ERR_INVALID;
+  memcpy(ptr, handle, sizeof(*ptr));
+  return *ptr ? B2C_OK : B2C_ERR_INVALID;
+}
+int b2c_peer_close(void* ptr) { return ptr ? B2C_OK : B2C_ERR_INVALID; }
+int b2c_peer_free(void* ptr) {
+  if (!ptr) return B2C_ERR_INVALID;
+  free(ptr);
+  return B2C_OK;
+}
+int b2c_peer_allreduce_avg(void* const* bufs, void* const* flags, int rank, int world, int64_t count, uint32_t seq,
+                           int ctas, b2c_stream s) {
+  (void)s;
+  if (!bufs || !flags || world < 1 || world > B2C_PEER_MAX_WORLD || rank < 0 || rank >= world || count < 0 || seq == 0 ||
+      seq > 0x3fffffffu || ctas < 1 || ctas > B2C_PEER_MAX_CTAS)
+    return B2C_ERR_INVALID;
+  for (int i = 0; i < world; i++)
+    if (!bufs[i] || !flags[i]) return B2C_ERR_INVALID;
+  if (world == 1 || count == 0) return B2C_OK;
+  const int64_t per = ((count + world - 1) / world + 3) & ~(int64_t)3;
+  const int64_t lo = rank * per, hi = lo + per < count ? lo + per : count;
+  const float scale = 1.f / (float)world;
+  for (int64_t i = lo; i < hi; i++) {
+    float a = ((const float*)bufs[0])[i];
+    for (int r = 1; r < world; r++) a += ((const float*)bufs[r])[i];
+    a *= scale;
+    for (int r = 0; r < world; r++) ((float*)bufs[r])[i] = a;
+  }
+  return B2C_OK;
+}
+unsigned b2c_peer_error(void) { return 0; }

@@ -22,6 +22,8 @@ def main():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--width", type=int, default=128)
     ap.add_argument("--two-pass", action="store_true", help="D(real), D(fake) as two passes (the reference's schedule)")
+    ap.add_argument("--profile-steps", type=int, default=1,
+                    help="profile this many back-to-back steps (> 1: steady state, no synchronisation in front)")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -61,8 +63,11 @@ def main():
     host_ms = (time.perf_counter() - t0) * 1e3 / 3
     torch.cuda.synchronize()
     dev_ms = e0.elapsed_time(e1) / 3
+    if a.profile_steps > 1:
+        one(3)                                    # the profiled steps start with the GPU busy
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-        one(0)
+        for i in range(a.profile_steps):
+            one(i)
         torch.cuda.synchronize()
     evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
     ks = sorted(((e.time_range.start, e.time_range.end, e.name) for e in evs), key=lambda t: t[0])
@@ -77,8 +82,12 @@ def main():
             busy += e - cur_end
             cur_end = e
     # compute kernels only (NCCL runs on its side stream): idle time of the compute stream = exposed communication
-    comp = [k for k in ks if "nccl" not in k[2].lower()]
-    nccl_ms = sum(k[1] - k[0] for k in ks if "nccl" in k[2].lower()) / 1e3
+    def is_comm(n):
+        return "nccl" in n.lower() or "peer_allreduce" in n
+
+    comp = [k for k in ks if not is_comm(k[2])]
+    nccl_ms = sum(k[1] - k[0] for k in ks if is_comm(k[2]) and not k[2].startswith("nccl:")) / 1e3
+    comm_rows = sorted(((k[1] - k[0]) / 1e3 for k in ks if is_comm(k[2]) and not k[2].startswith("nccl:")), reverse=True)
     cbusy, cend = 0.0, comp[0][0]
     cgaps = []
     for s, e, n in comp:
@@ -101,7 +110,8 @@ def main():
     out = {"ms_per_step_events": dev_ms, "host_enqueue_ms_per_step": host_ms,
            "profiled_step_span_ms": (t_last - t_first) / 1e3, "gpu_busy_ms": busy / 1e3,
            "gpu_idle_ms": (t_last - t_first - busy) / 1e3, "kernels": len(ks),
-           "world": world, "nccl_kernel_ms": nccl_ms, "compute_busy_ms": cbusy / 1e3,
+           "world": world, "profiled_steps": a.profile_steps, "comm_kernel_ms": nccl_ms,
+           "longest_comm_kernels_ms": [round(v, 3) for v in comm_rows[:12]], "compute_busy_ms": cbusy / 1e3,
            "compute_idle_ms": (comp[-1][1] - comp[0][0] - cbusy) / 1e3 if comp else None,
            "largest_compute_gaps_us": [[round(gg[0], 1), gg[1][:60]] for gg in cgaps[:12]],
            "idle_gaps_over_20us": sum(1 for gg in gaps if gg[0] > 20), "largest_gaps_us": [[round(gg[0], 1), gg[1][:60]] for gg in gaps[:15]],
