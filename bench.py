@@ -528,8 +528,9 @@ def make_workload(a, dev, rank, world, stock=False):
 
 # ncu `--set full` captures of the dominant launch of each workload (dram__bytes_read.sum + dram__bytes_write.sum)
 TRAFFIC = {
-    ("dcgan", 32, 128): (2.842e9, "profiles/r01_prof_conv_DL2fwd_summary.txt: dram__bytes_read.sum 2.316 GB + "
-                                  "dram__bytes_write.sum 0.525 GB per launch (algorithmic 2.69 GB)"),
+    ("dcgan", 32, 128): (3.272e9, "profiles/r02_prof_conv_DL2fwd_summary.txt (tc_conv_kernel<2, false>, CTA pairs): "
+                                  "dram__bytes_read.sum 2.743 GB + dram__bytes_write.sum 0.528 GB per launch "
+                                  "(algorithmic 2.69 GB); L2 -> SM 25.8 GB (34.4 GB before the pairs)"),
 }
 
 
