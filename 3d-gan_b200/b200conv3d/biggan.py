@@ -64,11 +64,16 @@ class Attention(tnn.Module):
     def forward(self, x, y=None):
         n, _, d, h, w = x.shape
         vox = d * h * w
-        f = self.f(x).reshape(n, self.ch_, vox)
-        g = F.max_pool3d(self.g(x), [2, 2, 2], stride=2).reshape(n, self.ch_, vox // 8)
-        beta = F.softmax(torch.bmm(f.permute(0, 2, 1), g), -1)
-        hh = F.max_pool3d(self.h(x), [2, 2, 2], stride=2).reshape(n, self.ch_, vox // 8)
-        o = self.v(torch.bmm(hh, beta.permute(0, 2, 1)).reshape(n, self.ch_, d, h, w))
+        # utils.py:33-43 is single-head attention without the 1/sqrt(E) scale: queries = f(x) at every voxel, keys =
+        # max-pooled g(x), values = max-pooled h(x).  softmax(q k^T) v goes through ONE fused library kernel
+        # (scaled_dot_product_attention, scale = 1): the [n, vox, vox / 8] score tensor of the reference's two bmm +
+        # softmax (8.6 GB in fp32 at the 32^3 site, batch 16) is never written.  In NDHWC memory the three
+        # [n, voxels, channels] operands are views of the conv outputs.
+        q = self.f(x).reshape(n, self.ch_, vox).permute(0, 2, 1)
+        k = F.max_pool3d(self.g(x), [2, 2, 2], stride=2).reshape(n, self.ch_, vox // 8).permute(0, 2, 1)
+        v = F.max_pool3d(self.h(x), [2, 2, 2], stride=2).reshape(n, self.ch_, vox // 8).permute(0, 2, 1)
+        o = F.scaled_dot_product_attention(q.unsqueeze(1), k.unsqueeze(1), v.unsqueeze(1), scale=1.0).squeeze(1)
+        o = self.v(o.permute(0, 2, 1).reshape(n, self.ch_, d, h, w))
         return self.gamma * o + x
 
 

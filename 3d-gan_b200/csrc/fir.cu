@@ -9,6 +9,7 @@
 // insertion are index arithmetic: one read of x, one write of y.  The backward pass w.r.t. x
 // is the adjoint gather (the filter is a constant buffer in the reference, it has no gradient).
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace b2c {
 namespace {
@@ -297,6 +298,253 @@ __global__ void __launch_bounds__(kThr) fir_sep_kernel(const __grid_constant__ F
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Unit-rate 4x4x4 rank-1 FIR, shared-memory tiled (the 128^3 / 64^3 / 32^3 sites of stylegan.py:427-432 and their
+// adjoints: 33 of the 47 FIR milliseconds of a BASELINE config 4 step ran in fir_sep_kernel<.., 1>, whose threads
+// each pull a 4 x 5 window per plane through L1: 10 loads per output, 20 % of the copy peak).
+//
+// A CTA of 256 threads owns a 16 x 16 (h, w) tile of CG = 4 channel vectors (32 bf16 channels) and marches along d
+// over `dch` outputs.  Every input plane of the tile (19 x 19 voxels x 64 B = 23 KB) is copied ONCE into shared memory
+// with cp.async (three buffers: two planes in flight while one is filtered; out-of-range voxels are stored as zeros,
+// padding is never materialised), then a thread = (4 outputs along h, one w, one channel vector) reads 7 rows x 4
+// columns as conflict-free LDS.128 (a warp reads 512 contiguous bytes), filters along w, then h, in registers
+// (15 multiply-adds per output element instead of 64) and scatters the plane into the rolling window of 4 output
+// accumulators along d.  HBM sees each input byte 1.4 times (tile halo) and each output byte once.
+constexpr int kFtT = 16, kFtR = kFtT + 3, kFtCG = 4, kFtThreads = 256, kFtBufs = 3;
+constexpr int kFtVecs = kFtR * kFtR * kFtCG;                       // 16-byte vectors per plane buffer
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <typename T>
+__global__ void __launch_bounds__(kFtThreads, 1) fir_tile_kernel(const __grid_constant__ FirP P, const __grid_constant__ FirSep S,
+                                                                  const T* __restrict__ x, T* __restrict__ y,
+                                                                  int htiles, int wtiles, int cgroups, int dchunks) {
+  constexpr int VEC = Vec<T>::N, K = 4;
+  extern __shared__ uint4 ft_smem[];
+  int b = blockIdx.x;
+  const int cgi = b % cgroups; b /= cgroups;
+  const int wt = b % wtiles; b /= wtiles;
+  const int ht = b % htiles; b /= htiles;
+  const int dc = b % dchunks;
+  const int64_t n = b / dchunks;
+  const int tid = threadIdx.x;
+  const int cv = tid % kFtCG, wl = (tid / kFtCG) % kFtT, hb = tid / (kFtCG * kFtT);
+  const int oh0 = ht * kFtT, ow0 = wt * kFtT, od0 = dc * S.dch, c0 = cgi * kFtCG * VEC;
+  const int nout = min(S.dch, P.od - od0);
+  const int nplanes = nout - 1 + K;
+  const uint32_t sbase = ptx::smem_u32(ft_smem);
+
+  auto load_plane = [&](int r) {
+    if (r < nplanes) {
+      const int jd = od0 + r - P.pad[0];
+      const bool dok = jd >= 0 && jd < P.id;
+      const uint32_t dst0 = sbase + (uint32_t)(r % kFtBufs) * (kFtVecs * 16u);
+      const T* plane = x + (n * P.id + (dok ? jd : 0)) * (int64_t)P.ih * P.iw * P.c + c0;
+      for (int i = tid; i < kFtVecs; i += kFtThreads) {
+        const int cvv = i % kFtCG, col = (i / kFtCG) % kFtR, row = i / (kFtCG * kFtR);
+        const int jh = oh0 + row - P.pad[1], jw = ow0 + col - P.pad[2];
+        if (dok && jh >= 0 && jh < P.ih && jw >= 0 && jw < P.iw)
+          cp_async16(dst0 + (uint32_t)i * 16u, plane + ((int64_t)jh * P.iw + jw) * P.c + cvv * VEC);
+        else
+          ft_smem[(r % kFtBufs) * kFtVecs + i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    cp_async_commit();                                  // one group per call, empty or not: wait counts stay uniform
+  };
+
+  float acc[K][4][VEC];
+#pragma unroll
+  for (int s = 0; s < K; s++)
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+#pragma unroll
+      for (int i = 0; i < VEC; i++) acc[s][q][i] = 0.f;
+  const int oh = oh0 + hb * 4, ow = ow0 + wl;
+  T* dst = y + (((n * P.od + od0) * P.oh + oh) * (int64_t)P.ow + ow) * P.c + c0 + cv * VEC;
+  const int64_t dst_plane = (int64_t)P.oh * P.ow * P.c, dst_row = (int64_t)P.ow * P.c;
+  const bool wok = ow < P.ow;
+
+  load_plane(0);
+  load_plane(1);
+  for (int base = 0; base < nplanes; base += K) {
+#pragma unroll
+    for (int s = 0; s < K; s++) {
+      const int r = base + s;
+      load_plane(r + 2);                                // buffer (r + 2) % 3 was released by the barrier that ended plane r - 1
+      cp_async_wait<2>();                               // this thread's copies of plane r have landed
+      __syncthreads();                                  // ... and everybody else's (and the zero stores)
+      if (r < nplanes) {
+        const uint4* pl = ft_smem + (r % kFtBufs) * kFtVecs;
+        float p[4][VEC];
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+#pragma unroll
+          for (int i = 0; i < VEC; i++) p[q][i] = 0.f;
+#pragma unroll
+        for (int bb = 0; bb < 4 + K - 1; bb++) {
+          const uint4* rowp = pl + ((hb * 4 + bb) * kFtR + wl) * kFtCG + cv;
+          float t[VEC];
+#pragma unroll
+          for (int e = 0; e < K; e++) {
+            Vec<T> raw;
+            *reinterpret_cast<uint4*>(&raw.raw) = rowp[e * kFtCG];
+            float in[VEC];
+            raw.unpack(in);
+#pragma unroll
+            for (int i = 0; i < VEC; i++) t[i] = e == 0 ? S.fw[0] * in[i] : fmaf(S.fw[e], in[i], t[i]);
+          }
+#pragma unroll
+          for (int q = 0; q < 4; q++)
+            if (bb - q >= 0 && bb - q < K) {
+#pragma unroll
+              for (int i = 0; i < VEC; i++) p[q][i] = fmaf(S.fh[bb - q], t[i], p[q][i]);
+            }
+        }
+        // plane r feeds output o = r - j through tap j; output o lives in slot o % K
+#pragma unroll
+        for (int j = 0; j < K; j++)
+#pragma unroll
+          for (int q = 0; q < 4; q++)
+#pragma unroll
+            for (int i = 0; i < VEC; i++)
+              acc[(s - j + K) % K][q][i] = fmaf(S.fd[j], p[q][i], acc[(s - j + K) % K][q][i]);
+      }
+      // output o = r + 1 - K is complete after plane r: slot (s + 1) % K
+      {
+        const int o = r + 1 - K;
+        if (o >= 0 && o < nout && wok) {
+#pragma unroll
+          for (int q = 0; q < 4; q++)
+            if (oh + q < P.oh) fir_st<T, VEC>(dst + o * dst_plane + q * dst_row, acc[(s + 1) % K][q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+#pragma unroll
+          for (int i = 0; i < VEC; i++) acc[(s + 1) % K][q][i] = 0.f;
+      }
+      __syncthreads();                                  // plane r's buffer may be overwritten (by load_plane(r + 3))
+    }
+  }
+  cp_async_wait<0>();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Adjoint of the decimating (down = 2) 4x4x4 rank-1 FIR: the gradient of the discriminator's skip path
+// (stylegan.py:244-247).  dx[i] = sum over (o, k) with 2 o + k - pad == i of f[k] dy[o]: per dimension a fine sample
+// sees the two taps of its parity.  A thread owns a 2 x 2 x 2 block of fine outputs of one channel vector: the 8
+// outputs read the same 3 x 3 x 3 coarse neighbourhood (27 loads instead of 8 x 8), filtered separably in registers
+// with the per-dimension coefficient table cf[dim][fine parity][coarse offset] built on the host (one of the three
+// entries is zero).  Writes (8/9 of the bytes) are 16-byte vectors, two adjacent voxels per thread.
+struct FirUp2 { float cf[3][2][3]; int ob[3]; };       // ob: coarse index of offset 0 for fine index 0, per dim
+
+template <typename T, int VEC>
+__global__ void __launch_bounds__(kThr) fir_adj2_kernel(const __grid_constant__ FirP P, const __grid_constant__ FirUp2 U,
+                                                         const T* __restrict__ dy, T* __restrict__ dx, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * kThr + threadIdx.x;
+  if (idx >= total) return;
+  const int cv = P.c / VEC;
+  const int c = (int)(idx % cv) * VEC;
+  int64_t v = idx / cv;
+  const int mw_n = (P.iw + 1) / 2, mh_n = (P.ih + 1) / 2, md_n = (P.id + 1) / 2;
+  const int mw = (int)(v % mw_n); v /= mw_n;
+  const int mh = (int)(v % mh_n); v /= mh_n;
+  const int md = (int)(v % md_n);
+  const int64_t n = v / md_n;
+  float out[2][2][2][VEC];
+#pragma unroll
+  for (int a = 0; a < 2; a++)
+#pragma unroll
+    for (int b = 0; b < 2; b++)
+#pragma unroll
+      for (int e = 0; e < 2; e++)
+#pragma unroll
+        for (int i = 0; i < VEC; i++) out[a][b][e][i] = 0.f;
+  const int od0 = md + U.ob[0], oh0 = mh + U.ob[1], ow0 = mw + U.ob[2];
+#pragma unroll
+  for (int jd = 0; jd < 3; jd++) {
+    const int od = od0 + jd - 1;
+    if (od < 0 || od >= P.od) continue;
+    float ph[2][2][VEC];
+#pragma unroll
+    for (int b = 0; b < 2; b++)
+#pragma unroll
+      for (int e = 0; e < 2; e++)
+#pragma unroll
+        for (int i = 0; i < VEC; i++) ph[b][e][i] = 0.f;
+#pragma unroll
+    for (int jh = 0; jh < 3; jh++) {
+      const int oh = oh0 + jh - 1;
+      if (oh < 0 || oh >= P.oh) continue;
+      const T* row = dy + ((n * P.od + od) * P.oh + oh) * (int64_t)P.ow * P.c + c;
+      float tw[2][VEC];
+#pragma unroll
+      for (int e = 0; e < 2; e++)
+#pragma unroll
+        for (int i = 0; i < VEC; i++) tw[e][i] = 0.f;
+#pragma unroll
+      for (int jw = 0; jw < 3; jw++) {
+        const int ow = ow0 + jw - 1;
+        if (ow < 0 || ow >= P.ow) continue;
+        float in[VEC];
+        fir_ld<T, VEC>(row + (int64_t)ow * P.c, in);
+#pragma unroll
+        for (int e = 0; e < 2; e++)
+#pragma unroll
+          for (int i = 0; i < VEC; i++) tw[e][i] = fmaf(U.cf[2][e][jw], in[i], tw[e][i]);
+      }
+#pragma unroll
+      for (int b = 0; b < 2; b++)
+#pragma unroll
+        for (int e = 0; e < 2; e++)
+#pragma unroll
+          for (int i = 0; i < VEC; i++) ph[b][e][i] = fmaf(U.cf[1][b][jh], tw[e][i], ph[b][e][i]);
+    }
+#pragma unroll
+    for (int a = 0; a < 2; a++)
+#pragma unroll
+      for (int b = 0; b < 2; b++)
+#pragma unroll
+        for (int e = 0; e < 2; e++)
+#pragma unroll
+          for (int i = 0; i < VEC; i++) out[a][b][e][i] = fmaf(U.cf[0][a][jd], ph[b][e][i], out[a][b][e][i]);
+  }
+#pragma unroll
+  for (int a = 0; a < 2; a++) {
+    const int id = 2 * md + a;
+    if (id >= P.id) continue;
+#pragma unroll
+    for (int b = 0; b < 2; b++) {
+      const int ih = 2 * mh + b;
+      if (ih >= P.ih) continue;
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        const int iw = 2 * mw + e;
+        if (iw < P.iw) fir_st<T, VEC>(dx + (((n * P.id + id) * P.ih + ih) * (int64_t)P.iw + iw) * P.c + c, out[a][b][e]);
+      }
+    }
+  }
+}
+
+// coefficient table of fir_adj2_kernel for one dimension: fine index i = 2 m + a, q = i + pad, tap parity par = q & 1,
+// taps k = par (coarse (q - par) / 2) and k = par + 2 (one coarse sample lower)
+static void adj2_dim(const float* f, int pad, float cf[2][3], int* ob) {
+  auto fdiv2 = [](int v) { return v >= 0 ? v / 2 : -((-v + 1) / 2); };
+  const int par0 = ((pad % 2) + 2) % 2;
+  const int base = fdiv2(pad - par0);               // coarse index of the high tap for i = 0; offset 0 = base
+  *ob = base;
+  for (int a = 0; a < 2; a++) {
+    for (int j = 0; j < 3; j++) cf[a][j] = 0.f;
+    const int q = a + pad, par = ((q % 2) + 2) % 2, hi = fdiv2(q - par);      // relative to m = 0
+    const int off = hi - base;                      // 0 or 1
+    cf[a][off + 1] += f[par];                       // table index j = offset + 1
+    cf[a][off] += f[par + 2];
+  }
+}
+
 // f[a][b][e] == fd[a] * fh[b] * fw[e]?  (host; 64 taps)
 bool factor_rank1(const float* f, FirSep* S) {
   int pa = 0, pb = 0, pe = 0;
@@ -346,6 +594,20 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
     }
     FirSep S;
     if (Q.kd == 4 && Q.kh == 4 && Q.kw == 4 && factor_rank1(Q.f, &S)) {
+      if (Q.c % (kFtCG * V) == 0 && Q.oh >= kFtT && Q.ow >= kFtT && Q.od >= 8) {
+        // shared-memory tiled march (see fir_tile_kernel); small volumes keep the register-window kernel below
+        S.dch = Q.od >= 64 ? 32 : Q.od;
+        const int ht = (Q.oh + kFtT - 1) / kFtT, wt = (Q.ow + kFtT - 1) / kFtT, cg = Q.c / (kFtCG * V),
+                  dc = (Q.od + S.dch - 1) / S.dch;
+        const int64_t blk = Q.n * dc * ht * wt * cg;
+        if (blk == 0) return B2C_OK;
+        if (blk > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+        constexpr int smem = kFtBufs * kFtVecs * 16;
+        if (cudaFuncSetAttribute(fir_tile_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+          return B2C_ERR_CUDA;
+        fir_tile_kernel<T><<<(unsigned)blk, kFtThreads, smem, st>>>(Q, S, ap, bp, ht, wt, cg, dc);
+        return launched();
+      }
       S.dch = Q.od >= 64 ? 32 : 16;
       const int64_t tot = Q.n * ((Q.od + S.dch - 1) / S.dch) * Q.oh * ((Q.ow + 1) / 2) * cvn;
       if (tot == 0) return B2C_OK;
@@ -360,6 +622,21 @@ int fir_run(bool bwd, const FirP& P, const void* a, void* b, cudaStream_t st) {
     if (blocks > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
     fir_fwd_w4_kernel<T, V><<<(unsigned)blocks, kThr, 0, st>>>(Q, ap, bp, total);
     return launched();
+  }
+  if (bwd && P.up == 1 && P.down == 2 && vec && P.kd == 4 && P.kh == 4 && P.kw == 4) {
+    FirSep S;
+    if (factor_rank1(P.f, &S)) {
+      FirUp2 U;
+      adj2_dim(S.fd, P.pad[0], U.cf[0], &U.ob[0]);
+      adj2_dim(S.fh, P.pad[1], U.cf[1], &U.ob[1]);
+      adj2_dim(S.fw, P.pad[2], U.cf[2], &U.ob[2]);
+      const int64_t tot = P.n * ((P.id + 1) / 2) * ((P.ih + 1) / 2) * ((P.iw + 1) / 2) * cvn;
+      if (tot == 0) return B2C_OK;
+      const int64_t blk = cdiv(tot, (int64_t)kThr);
+      if (blk > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+      fir_adj2_kernel<T, V><<<(unsigned)blk, kThr, 0, st>>>(P, U, ap, bp, tot);
+      return launched();
+    }
   }
   const int64_t total = (bwd ? P.n * P.id * P.ih * P.iw : P.n * P.od * P.oh * P.ow) * cvn;
   if (total == 0) return B2C_OK;

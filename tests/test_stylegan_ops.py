@@ -122,9 +122,14 @@ FIR_SHAPES = (
     # name, (n, c, d, h, w), kwargs of upfirdn3d  -- ragged extents: odd w, d not a multiple of the 16 / 32 chunk
     ("unit_up_conv", (2, 32, 33, 17, 19), dict(padding=[1, 1, 1, 1, 1, 1], gain=4)),        # after an up conv (:281)
     ("unit_pre_down", (1, 16, 70, 12, 9), dict(padding=[2, 2, 2, 2, 2, 2])),               # before a stride-2 conv (:258)
+    # the shared-memory tiled march (16 x 16 tiles, 32-plane chunks): ragged tiles, three d chunks, two channel groups
+    ("unit_tiled", (1, 64, 70, 37, 41), dict(padding=[2, 2, 2, 2, 2, 2])),
+    ("unit_tiled_crop", (2, 32, 21, 24, 35), dict(padding=[-1, -1, -1, -1, -1, -1])),
     ("unit_crop", (2, 8, 21, 10, 11), dict(padding=[-1, -1, -1, -1, -1, -1])),
     ("unit_odd_channels", (1, 3, 9, 8, 7), dict(padding=[2, 1, 2, 1, 2, 1])),
     ("decimate", (2, 16, 18, 14, 10), dict(down=2, padding=[1, 1, 1, 1, 1, 1])),             # skip path (:246)
+    ("decimate_odd", (1, 32, 19, 13, 11), dict(down=2, padding=[2, 1, 2, 1, 2, 1])),        # odd extents, even low pad
+    ("decimate_nopad", (1, 8, 12, 10, 9), dict(down=2, padding=[0, 0, 0, 0, 0, 0])),
     ("zero_insert", (2, 8, 6, 5, 7), dict(up=2, padding=[2, 1, 2, 1, 2, 1], gain=8)),        # image up-sampling (:634)
     ("zero_insert_1ch", (2, 1, 8, 8, 8), dict(up=2, padding=[2, 1, 2, 1, 2, 1], gain=8)),
 )
