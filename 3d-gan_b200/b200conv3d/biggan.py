@@ -16,8 +16,9 @@ What runs where:
   * the pre-activation ReLUs of DBlockDeep (utils.py:120-125) -> b2c_act;
   * channel drop + nearest x2 (utils.py:76-80) -> b2c_upsample2x; AvgPool3d(2) -> b2c_avgpool2
     (ATen has no channels-last 3-D kernels for either: it would convert to NCDHW and back);
-  * residual adds, the shortcut cat, the attention bmm / softmax / max-pool and the two linears
-    stay ATen ops on NDHWC tensors ("next").
+  * the attention core (utils.py:33-43) is ONE fused library call, scaled_dot_product_attention with scale 1, on
+    views of the NDHWC projections; residual adds, the shortcut cat, the attention max-pools
+    and the two linears stay ATen ops on NDHWC tensors.
 """
 import functools
 
