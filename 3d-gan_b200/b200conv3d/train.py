@@ -18,6 +18,21 @@ import torch.nn.utils.parametrize  # noqa: F401  (tnn.utils.parametrize.is_param
 import torch.optim as optim
 
 
+def per_sample_stateless(netD):
+    """True when one D pass over cat(real, fake) is the same arithmetic as the two passes of trainer.py:228-241: no
+    layer couples the samples of a batch (BatchNorm, minibatch-std), draws random numbers or changes state per call
+    (dropout, random crops, noise injection, spectral norm - one power iteration per forward).  An allow-list: every
+    leaf module must be a layer known to be per-sample and stateless, without buffers or parametrisations."""
+    from . import nn as BN
+    ok = (tnn.Conv3d, tnn.ConvTranspose3d, tnn.Linear, tnn.LayerNorm, tnn.LeakyReLU, tnn.ReLU, tnn.Tanh, tnn.Sigmoid,
+          tnn.Identity, tnn.Flatten, BN.FusedAway)
+    if any(tnn.utils.parametrize.is_parametrized(m) for m in netD.modules()):
+        return False
+    leaves = [m for m in netD.modules() if not list(m.children())]
+    return all(isinstance(m, ok) and not hasattr(m, "weight_u") and not hasattr(m, "weight_orig") and
+               not list(m.buffers(recurse=False)) for m in leaves)
+
+
 class GanStep:
     def __init__(self, netG, netD, z_size=512, lrG=5e-5, lrD=1e-4, hinge=False, iterD=2,
                  autocast_dtype=torch.bfloat16, reducer_g=None, reducer_d=None, seed=None, batch_real_fake=True):
@@ -31,14 +46,7 @@ class GanStep:
         self.optimizerG = optim.Adam(netG.parameters(), lr=lrG, betas=(0.0, 0.9), fused=fused)
         self.autocast_dtype = autocast_dtype
         self.reducer_g, self.reducer_d = reducer_g, reducer_d
-        # one D pass over cat(real, fake) is the same arithmetic as two passes only when no layer couples the
-        # samples of a batch (BatchNorm, minibatch-std) or changes state per call (spectral norm runs one power
-        # iteration per forward: the reference's second pass sees the updated u)
-        coupled = (tnn.modules.batchnorm._BatchNorm,)
-        stateful = any(isinstance(m, coupled) or "MinibatchStd" in type(m).__name__ or
-                       tnn.utils.parametrize.is_parametrized(m) or hasattr(m, "weight_u") or hasattr(m, "weight_orig")
-                       for m in netD.modules())
-        self.batch_real_fake = bool(batch_real_fake) and self.device.type == "cuda" and not stateful
+        self.batch_real_fake = bool(batch_real_fake) and self.device.type == "cuda" and per_sample_stateless(netD)
         self.gen = None
         if seed is not None:
             self.gen = torch.Generator(device=self.device)

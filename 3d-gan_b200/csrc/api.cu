@@ -1,4 +1,5 @@
 // api.cu — library-level entry points, descriptor validation and geometry.
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -20,6 +21,18 @@ int num_sms() {
     sms[dev] = v;
   }
   return sms[dev];
+}
+
+const Knobs& knobs() {
+  static Knobs k;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    auto num = [](const char* n) { const char* e = getenv(n); return e ? atoi(e) : 0; };
+    auto set = [](const char* n) { return getenv(n) != nullptr; };
+    k.swap_min = num("B2C_SWAP_MIN"); k.mt1 = set("B2C_MT1"); k.no_pair = set("B2C_NO_PAIR"); k.dbg = num("B2C_DBG");
+    k.stages = num("B2C_STAGES"); k.wg_mt1 = set("B2C_WG_MT1"); k.thin_unfused = set("B2C_THIN_UNFUSED");
+  });
+  return k;
 }
 
 static int out_extent(int in, int k, int s, int p, int d) { return (in + 2 * p - d * (k - 1) - 1) / s + 1; }

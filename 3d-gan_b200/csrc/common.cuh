@@ -24,6 +24,19 @@ inline int esize(int dt) { return dt == B2C_BF16 ? 2 : 4; }
 inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 int num_sms();
 
+// Experiment switches (include/b2c_debug.h lists them).  Read from the environment ONCE, when the library first needs
+// them - never on the launch path: getenv is not safe against a concurrent setenv from another Python thread.
+struct Knobs {
+  int swap_min;        // B2C_SWAP_MIN   : smallest Cout that takes the swapped (channels on M) epilogue
+  bool mt1;            // B2C_MT1        : never use 256 x 256 tiles
+  bool no_pair;        // B2C_NO_PAIR    : no CTA pairs (cta_group::2)
+  int dbg;             // B2C_DBG        : timing experiments (8: no MMAs, 16: no loads)
+  int stages;          // B2C_STAGES     : cap of the smem pipeline depth (0 = no cap)
+  bool wg_mt1;         // B2C_WG_MT1     : weight-gradient kernel with one M sub-tile
+  bool thin_unfused;   // B2C_THIN_UNFUSED: one-channel layers through im2col + GEMM + col2im
+};
+const Knobs& knobs();
+
 // ---- element access -------------------------------------------------------
 __device__ __forceinline__ float ldf(const __nv_bfloat16* p, int64_t i) { return __bfloat162float(p[i]); }
 __device__ __forceinline__ float ldf(const float* p, int64_t i) { return p[i]; }

@@ -935,7 +935,7 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   const int64_t sub_tiles = (int64_t)p.subs[0].tiles[0] * p.subs[0].tiles[1] * p.subs[0].tiles[2] * p.subs[0].tiles[3];
   // measured (profiles/r02_exp_pair_tiles.log, isolated launches): D.L2 fwd 1375 -> 1485 TFLOP/s, D.L4 fwd / dgrad
   // 1311 / 1411 -> 1457 / 1536, G.L5 dgrad 1375 -> 1465, G.L2 fwd 1246 -> 1395: on by default (B2C_NO_PAIR=1: off)
-  static const bool no_pair = getenv("B2C_NO_PAIR") != nullptr;
+  const bool no_pair = knobs().no_pair;
   const bool pair = !no_pair && !p.swap && uniform && sub_tiles >= 2 && p.block_n % 32 == 0;
   const int ncta = pair ? 2 : 1;
   MapDesc wm;
@@ -964,8 +964,8 @@ int tc_conv_launch(const ConvPlan& p, const void* in, const void* w, void* out, 
   }
   int stages = (kSmemBudget - fixed) / (int)stage_bytes;
   if (stages > 8) stages = 8;
-  if (const char* e = getenv("B2C_DBG")) P.dbg = atoi(e);      // timing experiments only (8: no MMAs, 16: no loads)
-  if (const char* e = getenv("B2C_STAGES")) { const int v = atoi(e); if (v >= 2 && v < stages) stages = v; }   // experiments
+  P.dbg = knobs().dbg;                                         // timing experiments only (8: no MMAs, 16: no loads)
+  if (knobs().stages >= 2 && knobs().stages < stages) stages = knobs().stages;                               // experiments
   if (stages < 2) return B2C_ERR_UNSUPPORTED;
   P.stages = stages;
   P.idesc = p.swap ? idesc_bf16(128, 128 * p.mt, 0, 0) : idesc_bf16(kBlockM * ncta, p.block_n, 0, 0);
@@ -1055,7 +1055,7 @@ static int wgrad_cfg(const Geo& g, WgradCfg* c) {
   // with the small tensor on M the pair must be two channel tiles of one tap.
   c->mt = 1;
   if (c->tpack == 1 && 2 * bn <= 512 && c->plan.ntaps_total * c->a_tiles >= 2 && (c->m_big || c->a_tiles % 2 == 0) &&
-      !getenv("B2C_WG_MT1")) {
+      !knobs().wg_mt1) {
     c->mt = 2;
     c->ngroups = (c->plan.ntaps_total * c->a_tiles + 1) / 2;
   }

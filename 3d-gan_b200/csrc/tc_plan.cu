@@ -34,8 +34,7 @@ static int finish(ConvPlan* p, int kin, int nout) {
   // keep the direct epilogue.)
   int min_taps = p->nsubs > 0 ? p->subs[0].ntaps : 0;
   for (int s = 1; s < p->nsubs; s++) if (p->subs[s].ntaps < min_taps) min_taps = p->subs[s].ntaps;
-  int swap_min = 0;
-  if (const char* e = getenv("B2C_SWAP_MIN")) swap_min = atoi(e);
+  const int swap_min = knobs().swap_min;
   p->swap = (bn <= 128 && nout >= swap_min && (int64_t)min_taps * p->kchunks >= 8) ? 1 : 0;
   if (p->swap) bn = 128;
   p->block_n = bn;
@@ -77,7 +76,7 @@ static int finish(ConvPlan* p, int kin, int nout) {
   // price of an exposed epilogue and half as many tiles: taken when the reduction is long and the
   // last wave of the persistent grid does not get much emptier (measured gain ~1.2x per tile).
   if (bn == 256 && mt == 1 && !p->swap && (int64_t)min_taps * p->kchunks >= 32 && vox >= 2 * kBlockM &&
-      !getenv("B2C_MT1")) {
+      !knobs().mt1) {
     const int sms = num_sms();
     auto eff = [&](int64_t t) { return (double)t / (double)(((t + sms - 1) / sms) * sms); };
     const int64_t tiles1 = (int64_t)p->m_tiles * p->tiles_n;

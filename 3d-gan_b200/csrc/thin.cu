@@ -463,7 +463,7 @@ int thin_gather(const Geo& g, const void* big, const void* wp, void* out_small, 
                                         static_cast<bf16*>(out_small), g.sc, act, slope, rows, cdiv(rows, (int64_t)nb));
     return launched();
   }
-  if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
+  if (tc_thin_gather_supported(g) && !knobs().thin_unfused) {
     const int rc = tc_thin_gather_launch(g, big, wp, thin_kp(g), out_small, bias, act, slope, st, stats);
     if (rc != B2C_ERR_UNSUPPORTED) return rc;
   }
@@ -527,7 +527,7 @@ int thin_wgrad(const Geo& g, const void* small, const void* big, float* dw, void
     return launched();
   }
   const int Kp = thin_kp(g), T = g.taps();
-  if (tc_thin_gather_supported(g) && !getenv("B2C_THIN_UNFUSED")) {
+  if (tc_thin_gather_supported(g) && !knobs().thin_unfused) {
     const int frc = tc_thin_wgrad_launch(g, small, big, dw, flip ? 1 : 0, ws, wsb, st);
     if (frc != B2C_ERR_UNSUPPORTED) return frc;
   }

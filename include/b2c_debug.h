@@ -23,6 +23,18 @@ unsigned b2c_debug_tc_error(void);
 int b2c_debug_plan_run(const b2c_conv_desc* desc, int pass, const float* in,
                        const float* w_packed, float* out, int32_t* info);
 
+/* Experiment switches of the tensor-core kernels, read from the ENVIRONMENT once, when the library first plans a
+ * launch (csrc/common.cuh `Knobs`; changing them later in the process has no effect).  They change tile plans, hence
+ * summation order and speed, never the arithmetic contract; the product path sets none of them.
+ *   B2C_SWAP_MIN=n      smallest Cout that takes the swapped (channels on UMMA M) epilogue (default 0: all <= 128)
+ *   B2C_MT1=1           never use the 256 x 256 single-accumulator tiles
+ *   B2C_NO_PAIR=1       no CTA pairs (tcgen05 cta_group::2)
+ *   B2C_STAGES=n        cap of the shared-memory pipeline depth
+ *   B2C_WG_MT1=1        weight-gradient kernel with one M sub-tile per CTA
+ *   B2C_THIN_UNFUSED=1  one-channel layers through im2col + GEMM + col2im instead of the fused gather kernels
+ *   B2C_DBG=bits        timing experiments that BREAK the result (1 no TMA store, 2 no tcgen05.ld, 4 no st.shared,
+ *                       8 no MMAs, 16 no loads)                                                                  */
+
 #ifdef __cplusplus
 }
 #endif

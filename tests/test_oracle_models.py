@@ -166,3 +166,18 @@ def test_biggan_hinge_phases_match_reference(gold_big):
     for pre, m in (("g1.", g), ("d1.", d)):
         for k, v in m.state_dict().items():
             np.testing.assert_allclose(v.numpy(), gold_big[pre + k], rtol=2e-4, atol=2e-6, err_msg=k)
+
+
+def test_batched_discriminator_pass_is_allow_listed():
+    """GanStep runs D(real), D(fake) as ONE pass only for discriminators made of per-sample, stateless layers
+    (trainer.py:228-241 semantics): anything with batch coupling, per-call state or RNG keeps the two passes."""
+    import torch.nn as tnn
+    import b200conv3d as B
+    from b200conv3d.train import per_sample_stateless
+    _, d = B.dcgan.build(16, 8, 8, 128, torch.device("cpu"))
+    assert per_sample_stateless(d)
+    _, d_sn = B.biggan.build(16, 8, 8, torch.device("cpu"))
+    assert not per_sample_stateless(d_sn)                                             # spectral norm
+    assert not per_sample_stateless(tnn.Sequential(tnn.Conv3d(1, 4, 3), tnn.BatchNorm3d(4)))
+    assert not per_sample_stateless(tnn.Sequential(tnn.Conv3d(1, 4, 3), tnn.Dropout(0.1)))
+    assert not per_sample_stateless(tnn.Sequential(tnn.Conv3d(1, 4, 3), tnn.RReLU()))  # unknown layer: not batched
