@@ -1,0 +1,100 @@
+"""The data-parallel path on REAL devices (needs >= 2 GPUs in the box; skipped otherwise - the driver's single-GPU tier
+sees the kernel itself through tests/test_peer_reduce.py): two processes, one GPU each, NCCL for the plumbing, the
+gradient buckets in CUDA-IPC peer memory, b2c_peer_allreduce_avg for the average (the reference's
+counterpart is nn.DataParallel, trainer.py:70-72).
+
+Checks: the peer transport came up (no NCCL fall-back), the reduced gradients equal the mean of the per-rank gradients,
+the conv filters' .grad ARE their bucket slots, and after two optimizer steps through GradReducer.step() both replicas
+hold bit-identical parameters."""
+import os
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, out):
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "3d-gan_b200"))
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        import torch.distributed as dist
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        import b200conv3d as B
+        from b200conv3d import _lib, parallel
+        torch.manual_seed(7)
+        g, d = B.dcgan.build(16, 8, 8, 128, dev)
+        for p in list(g.parameters()) + list(d.parameters()):
+            dist.broadcast(p.data, 0)
+        B.functional.invalidate_packs()
+        real = torch.rand(2, 1, 128, 128, 128, device=dev, generator=torch.Generator(device=dev).manual_seed(100 + rank)) * 2 - 1
+
+        # per-rank gradients of one D pass without any reducer -> expected mean
+        def d_grads():
+            for p in d.parameters():
+                p.requires_grad = True
+            d.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                (d(real).mean()).backward()
+            return [p.grad.detach().clone() for p in d.parameters()]
+
+        local = d_grads()
+        want = []
+        for t in local:
+            parts = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(parts, t.contiguous())
+            want.append(torch.stack(parts).sum(0) / world)
+        rd = parallel.GradReducer(d)
+        assert rd.comm is not None, "peer transport did not come up (fell back to NCCL)"
+        d.zero_grad()
+        rd.begin()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            (d(real).mean()).backward()
+        rd.finish()
+        torch.cuda.synchronize()
+        assert _lib.lib().b2c_peer_error() == 0
+        for p, w in zip(d.parameters(), want):
+            # the two backward passes may differ in the last bit of a sum (different launch history of the split
+            # reductions); the average itself is exact for two ranks
+            torch.testing.assert_close(p.grad, w, rtol=1e-5, atol=2e-6 * max(1e-30, w.abs().max().item()))
+        convs = [p for p in d.parameters() if p.dim() == 5]
+        assert all(p.grad.data_ptr() == rd.slots[rd.index[id(p)]].data_ptr() for p in convs)
+        # two full steps through the public step API; replicas must stay bit-identical
+        rg = parallel.GradReducer(g)
+        step = B.train.GanStep(g, d, 16, iterD=1, reducer_g=rg, reducer_d=rd, seed=5 + rank)
+        for _ in range(2):
+            step.step(iter([real]))
+        torch.cuda.synchronize()
+        chk = torch.stack([torch.stack([q.detach().double().sum(), q.detach().double().abs().sum()])
+                           for net in (g, d) for q in net.parameters()]).sum(0)
+        allc = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        assert all(torch.equal(c, allc[0]) for c in allc) and bool(torch.isfinite(chk).all())
+        assert _lib.lib().b2c_peer_error() == 0
+        dist.barrier()
+        dist.destroy_process_group()
+        out.put((rank, "ok"))
+    except Exception as e:       # noqa: BLE001
+        import traceback
+        out.put((rank, "FAIL: %s\n%s" % (e, traceback.format_exc())))
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_two_gpu_peer_reducer():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one box")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = 29000 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [out.get(timeout=540) for _ in procs]
+    for p in procs:
+        p.join(60)
+    assert all(r[1] == "ok" for r in res), res
