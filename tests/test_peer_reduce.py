@@ -5,7 +5,8 @@ CPU: the host stand-in (one call per "rank" over buffers of one process) gives t
 world size / count, every buffer ends identical, and elements beyond `count` are untouched.  GPU (one device): the
 kernel with its `world` ranks played by `world` streams of one process - flags, slices, tail - against the host
 stand-in bit for bit, several calls in a row on the same flag blocks, plus the IPC handle round trip that a second
-process would do.  The N-process path itself is covered by `bench.py --gpus N` / tools/run_r02_8gpu.sh."""
+process would do.  The N-process path itself is covered by `bench.py --gpus N` (tools/scale_round2.sh) and, on
+a box with two GPUs, by tests/test_gpu_multi.py."""
 import ctypes as C
 
 import pytest
