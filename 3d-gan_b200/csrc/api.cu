@@ -31,6 +31,7 @@ const Knobs& knobs() {
     auto set = [](const char* n) { return getenv(n) != nullptr; };
     k.swap_min = num("B2C_SWAP_MIN"); k.mt1 = set("B2C_MT1"); k.no_pair = set("B2C_NO_PAIR"); k.dbg = num("B2C_DBG");
     k.stages = num("B2C_STAGES"); k.wg_mt1 = set("B2C_WG_MT1"); k.thin_unfused = set("B2C_THIN_UNFUSED");
+    k.col2im_ldg = set("B2C_COL2IM_LDG");
   });
   return k;
 }

@@ -34,6 +34,7 @@ struct Knobs {
   int stages;          // B2C_STAGES     : cap of the smem pipeline depth (0 = no cap)
   bool wg_mt1;         // B2C_WG_MT1     : weight-gradient kernel with one M sub-tile
   bool thin_unfused;   // B2C_THIN_UNFUSED: one-channel layers through im2col + GEMM + col2im
+  bool col2im_ldg;     // B2C_COL2IM_LDG : k4 / s2 col2im with global 16-byte loads instead of the TMA-staged kernel
 };
 const Knobs& knobs();
 

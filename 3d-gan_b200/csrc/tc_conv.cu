@@ -1234,6 +1234,38 @@ int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp,
   return launched();
 }
 
+int tc_col2im1_k4s2_launch(const Geo& g, const void* col, void* big, const float* bias, int act, float slope,
+                           cudaStream_t st) {
+  Col2imK4S2Params P;
+  memset(&P, 0, sizeof(P));
+  MapDesc m;
+  m.base = 0;
+  m.dims[0] = 64; m.dims[1] = g.sw; m.dims[2] = g.sh; m.dims[3] = g.sd; m.dims[4] = g.n;
+  m.strides[0] = 1; m.strides[1] = 64; m.strides[2] = (int64_t)g.sw * 64; m.strides[3] = (int64_t)g.sh * g.sw * 64;
+  m.strides[4] = (int64_t)g.sd * g.sh * g.sw * 64;
+  const int box[5] = {64, kC2RW, kC2RH, 1, 1};
+  int rc = encode_map(&P.col_map, col, m, 5, box);
+  if (rc) return rc;
+  P.big = static_cast<__nv_bfloat16*>(big); P.bias = bias; P.act = act; P.slope = slope;
+  P.n = g.n; P.sd = g.sd; P.sh = g.sh; P.sw = g.sw;
+  P.htiles = (g.sh + kC2H - 1) / kC2H; P.wtiles = (g.sw + kC2W - 1) / kC2W;
+  // d chunks: enough CTAs for ~4 waves of one-CTA-per-SM blocks, at least 8 output planes per chunk (2 halo planes each)
+  const int64_t tiles = (int64_t)g.n * P.htiles * P.wtiles;
+  int chunks = (int)cdiv((int64_t)4 * num_sms(), tiles > 0 ? tiles : 1);
+  if (chunks > (g.sd + 7) / 8) chunks = (g.sd + 7) / 8;
+  if (chunks < 1) chunks = 1;
+  P.dch = (g.sd + chunks - 1) / chunks;
+  P.dchunks = (g.sd + P.dch - 1) / P.dch;
+  const int64_t grid = tiles * P.dchunks;
+  if (grid == 0) return B2C_OK;
+  if (grid > 0x7fffffffLL) return B2C_ERR_UNSUPPORTED;
+  const size_t smem = 1024 + (size_t)kC2Ring * kC2PlaneStride + 64;
+  if (cudaFuncSetAttribute(col2im1_k4s2_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    return B2C_ERR_CUDA;
+  col2im1_k4s2_tma_kernel<<<(unsigned)grid, kC2Threads, smem, st>>>(P);
+  return launched();
+}
+
 // split-K over 128-voxel tiles: one CTA (= one fp32 partial) per contiguous tile range, two CTAs per SM
 static void thin_wgrad_split(const Geo& g, int* tiles, int* per_cta, int* splits) {
   const int64_t rows = (int64_t)g.n * g.sd * g.sh * g.sw;

@@ -27,6 +27,9 @@ int tc_thin_gather_launch(const Geo& g, const void* big, const void* wp, int Kp,
 size_t tc_thin_wgrad_workspace(const Geo& g);
 int tc_thin_wgrad_launch(const Geo& g, const void* small, const void* big, float* dw, int flip, void* ws, size_t wsb,
                          cudaStream_t st);
+// col2im of the k4 / s2 / p1 one-channel layers (thin.cu), TMA-staged: col = [n*sd*sh*sw][64] bf16 in k4s2_perm order
+int tc_col2im1_k4s2_launch(const Geo& g, const void* col, void* big, const float* bias, int act, float slope,
+                           cudaStream_t st);
 // Sticky device error word of the tensor-core kernels (synchronises the device).
 unsigned tc_error_fetch_clear();
 }  // namespace b2c

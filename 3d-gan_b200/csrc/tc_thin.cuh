@@ -523,3 +523,105 @@ thin_wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, i
   for (; s < splits; s++) acc += p[s * pitch];
   dw[idx] = acc;
 }
+
+
+// =============================================================================
+// col2im onto a ONE-channel tensor for k = 4, stride 2, pad 1 (dcgan.py:67 ConvTranspose3d(ngf, 1) and the data
+// gradient of dcgan.py:161), TMA-staged.  The GEMM in front leaves col[small voxel][64] (128 B rows, columns in the
+// order t' = a*8 + r of thin.cu:k4s2_perm); output voxel block 2j + r gathers, per (dd, dh) neighbour line, group
+// a0 = (dd != 0, dh != 0, 0) of row jw and group a0 + 1 of rows jw - 1 / jw + 1.
+//
+// The first version read those 16-byte groups straight from global memory, a warp = 32 consecutive jw: every load
+// instruction touched 32 different 128-byte lines (one L1 tag lookup each) and the kernel ran at 1.6 TB/s of
+// algorithmic bytes.  Here a CTA owns a 4 (h) x 64 (w) tile of small voxels and marches along d (4 x 32 tiles with two
+// CTAs per SM measured 2 % slower): each col plane of the tile plus its halo (6 x 66 rows x 128 B) arrives by ONE TMA
+// box copy (out-of-range rows / lines / planes are
+// zero-filled by TMA: the padding logic disappears) into a ring of four 128-byte-swizzled planes - three in use, one
+// in flight - and the 27 groups a thread needs per output plane are conflict-free LDS.128 (8 consecutive rows of one
+// chunk column hit 8 different bank groups under the swizzle).  HBM sees each col row 1.55x (h / w halo) instead of
+// nine sector requests per row through L1.
+// =============================================================================
+constexpr int kC2H = 4, kC2W = 64, kC2RH = kC2H + 2, kC2RW = kC2W + 2, kC2Ring = 4, kC2Threads = kC2H * kC2W;
+constexpr uint32_t kC2PlaneBytes = kC2RH * kC2RW * 128;                 // 50688: what one TMA box delivers
+constexpr uint32_t kC2PlaneStride = (kC2PlaneBytes + 1023u) & ~1023u;   // ring slots stay 1024-byte aligned (swizzle atom)
+
+struct alignas(64) Col2imK4S2Params {
+  CUtensorMap col_map;                // [n][sd][sh][sw][64] bf16, box {64, kC2RW, kC2RH, 1, 1}
+  __nv_bfloat16* big;
+  const float* bias;
+  int32_t n, sd, sh, sw, dch, htiles, wtiles, dchunks, act;
+  float slope;
+};
+
+__global__ void __launch_bounds__(kC2Threads, 1) col2im1_k4s2_tma_kernel(const __grid_constant__ Col2imK4S2Params P) {
+  extern __shared__ uint8_t c2_smem_raw[];
+  const uint32_t base = (smem_u32(c2_smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = base + kC2Ring * kC2PlaneStride;
+  auto full_bar = [&](int s) { return bars + (uint32_t)s * 8u; };
+  int b = blockIdx.x;
+  const int wt = b % P.wtiles; b /= P.wtiles;
+  const int ht = b % P.htiles; b /= P.htiles;
+  const int dc = b % P.dchunks;
+  const int in = b / P.dchunks;
+  const int d0 = dc * P.dch;
+  const int nout = min(P.dch, P.sd - d0);
+  const int tid = threadIdx.x, jwl = tid % kC2W, jhl = tid / kC2W;
+  const int jw = wt * kC2W + jwl, jh = ht * kC2H + jhl;
+  const bool live = jw < P.sw && jh < P.sh;
+  if (tid == 0) {
+    prefetch_tmap(&P.col_map);
+    for (int s = 0; s < kC2Ring; s++) mbar_init(full_bar(s), 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  auto load_plane = [&](int q) {                       // q: plane index relative to d0 - 1 (thread 0 only)
+    const int slot = q & (kC2Ring - 1);
+    mbar_arrive_expect_tx(full_bar(slot), kC2PlaneBytes);
+    tma_load_5d(base + (uint32_t)slot * kC2PlaneStride, &P.col_map, full_bar(slot), 0, wt * kC2W - 1, ht * kC2H - 1,
+                d0 - 1 + q, in);
+  };
+  if (tid == 0) { load_plane(0); load_plane(1); load_plane(2); }
+  const float b0 = P.bias ? P.bias[0] : 0.f;
+  const int bh = 2 * P.sh, bw = 2 * P.sw;
+  for (int o = 0; o < nout; o++) {
+    if (tid == 0 && o + 3 < nout + 2) load_plane(o + 3);     // its slot was released by the barrier that ended o - 1
+    if (o == 0) { mbar_wait(full_bar(0), 0); mbar_wait(full_bar(1), 0); }
+    mbar_wait(full_bar((o + 2) & (kC2Ring - 1)), ((o + 2) >> 2) & 1);
+    float acc[8];
+#pragma unroll
+    for (int r = 0; r < 8; r++) acc[r] = b0;
+#pragma unroll
+    for (int dd = -1; dd <= 1; dd++) {
+      const uint32_t plane = base + (uint32_t)((o + 1 + dd) & (kC2Ring - 1)) * kC2PlaneStride;
+#pragma unroll
+      for (int dh = -1; dh <= 1; dh++) {
+        const int a0 = ((dd != 0) << 2) | ((dh != 0) << 1);
+        const int lin = (jhl + 1 + dh) * kC2RW + jwl + 1;        // own row in the box; neighbours lin -+ 1
+        const uint4 A0 = ld_shared_v4(plane + (uint32_t)lin * 128u + (uint32_t)((a0 ^ (lin & 7)) << 4));
+        const uint4 L = ld_shared_v4(plane + (uint32_t)(lin - 1) * 128u + (uint32_t)(((a0 + 1) ^ ((lin - 1) & 7)) << 4));
+        const uint4 R = ld_shared_v4(plane + (uint32_t)(lin + 1) * 128u + (uint32_t)(((a0 + 1) ^ ((lin + 1) & 7)) << 4));
+        const uint32_t a0v[4] = {A0.x, A0.y, A0.z, A0.w}, lv[4] = {L.x, L.y, L.z, L.w}, rv[4] = {R.x, R.y, R.z, R.w};
+#pragma unroll
+        for (int m = 0; m < 4; m++) {                 // m = rd*2 + rh; register m holds (rw = 0 | rw = 1)
+          const bool ok = (dd == 0 || ((m >> 1) & 1) == (dd > 0)) && (dh == 0 || (m & 1) == (dh > 0));
+          if (ok) {
+            acc[2 * m] += __uint_as_float(a0v[m] << 16) + __uint_as_float(lv[m] << 16);                  // rw = 0
+            acc[2 * m + 1] += __uint_as_float(a0v[m] & 0xffff0000u) + __uint_as_float(rv[m] & 0xffff0000u);   // rw = 1
+          }
+        }
+      }
+    }
+    if (live) {
+      const int jd = d0 + o;
+#pragma unroll
+      for (int rd = 0; rd < 2; rd++)
+#pragma unroll
+        for (int rh = 0; rh < 2; rh++) {
+          const float v0 = act_f(acc[rd * 4 + rh * 2], P.act, P.slope), v1 = act_f(acc[rd * 4 + rh * 2 + 1], P.act, P.slope);
+          __nv_bfloat16* dst = P.big + (((int64_t)in * 2 * P.sd + 2 * jd + rd) * bh + 2 * jh + rh) * bw + 2 * jw;
+          *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(v0, v1);
+        }
+    }
+    __syncthreads();                                   // plane o (slot o & 3) is free for plane o + 4
+  }
+}

@@ -498,6 +498,8 @@ int thin_scatter(const Geo& g, const void* small, const void* wp, void* out_big,
   if (rc) return rc;
   const int64_t total = (int64_t)g.n * g.bd * g.bh * g.bw;
   if (total == 0) return B2C_OK;
+  if (is_k4s2(g) && !knobs().col2im_ldg)
+    return tc_col2im1_k4s2_launch(g, ws, out_big, bias, act, slope, st);      // TMA-staged (tc_thin.cuh)
   if (is_k4s2(g)) {
     dim3 grid((unsigned)cdiv(g.sw, 64), (unsigned)cdiv(g.sh, 4), (unsigned)(g.n * g.sd));
     col2im1_k4s2_kernel<<<grid, 256, 0, st>>>(static_cast<const bf16*>(ws), static_cast<bf16*>(out_big), g.n, g.sd,

@@ -32,6 +32,7 @@ int b2c_debug_plan_run(const b2c_conv_desc* desc, int pass, const float* in,
  *   B2C_STAGES=n        cap of the shared-memory pipeline depth
  *   B2C_WG_MT1=1        weight-gradient kernel with one M sub-tile per CTA
  *   B2C_THIN_UNFUSED=1  one-channel layers through im2col + GEMM + col2im instead of the fused gather kernels
+ *   B2C_COL2IM_LDG=1    k4 / s2 one-channel col2im with global loads (round-1 kernel) instead of the TMA-staged one
  *   B2C_DBG=bits        timing experiments that BREAK the result (1 no TMA store, 2 no tcgen05.ld, 4 no st.shared,
  *                       8 no MMAs, 16 no loads)                                                                  */
 

@@ -53,6 +53,8 @@ THIN_CASES = [
     (False, 64, 1, 3, 1, 1, 1, (4, 5, 32), 2),      # biggan.py:42 output conv: its data gradient takes the line loader
     (True, 16, 1, 4, 2, 1, 1, (8, 8, 8), 2),        # dcgan.py:67 G head
     (True, 128, 1, 4, 2, 1, 1, (6, 6, 6), 2),       # dcgan.py:67 at full width
+    (True, 16, 1, 4, 2, 1, 1, (20, 9, 70), 2),      # TMA-staged col2im: three d chunks, ragged h tiles, two w tiles
+    (False, 1, 16, 4, 2, 1, 1, (18, 10, 132), 1),   # its data-gradient twin (dcgan.py:161), small side 9 x 5 x 66
     # SMALL side has one channel, stride 1: mirrored problem (thin_mode == 2)
     (False, 64, 1, 3, 1, 1, 1, (6, 7, 8), 2),       # biggan.py:42 output conv f -> 1
     (False, 16, 1, 3, 1, 1, 1, (9, 8, 10), 3),      # stylegan.py:1038 Conv3d(16 -> 1)
