@@ -181,3 +181,20 @@ def test_batched_discriminator_pass_is_allow_listed():
     assert not per_sample_stateless(tnn.Sequential(tnn.Conv3d(1, 4, 3), tnn.BatchNorm3d(4)))
     assert not per_sample_stateless(tnn.Sequential(tnn.Conv3d(1, 4, 3), tnn.Dropout(0.1)))
     assert not per_sample_stateless(tnn.Sequential(tnn.Conv3d(1, 4, 3), tnn.RReLU()))  # unknown layer: not batched
+
+
+def test_loss_curve_criterion_on_recorded_curves():
+    """tools/loss_curves.py judges the recorded 100-step curves (profiles/) over the horizon where stock bf16 still
+    tracks fp32; the recorded run must pass and a curve that leaves the envelope must fail."""
+    import copy
+    import json
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import loss_curves
+    d = json.load(open(os.path.join(ROOT, "profiles", "r02_loss_curves_100steps.json")))
+    res = loss_curves.evaluate(d["ref"], d["ours"], d["witness"])
+    assert res["pass"] and 20 <= res["horizon_steps"] <= 100
+    assert all(c["window_rel"] < 0.05 for c in res["curves"].values())
+    bad = copy.deepcopy(d["ours"])
+    k = next(iter(bad))
+    bad[k] = [v + 0.2 * res["curves"][k]["window_range"] for v in bad[k]]        # a constant 20 % offset from step 0
+    assert not loss_curves.evaluate(d["ref"], bad, d["witness"])["pass"]
